@@ -1,0 +1,108 @@
+"""In-tree builds: the C-ABI library (nvcc, sm_100a only) and the torch binding (g++).
+
+Everything lands next to the sources so that `gpurun` ships the built `.so` files to the
+GPU box (they are git-ignored, not gpurun-ignored).
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+import sysconfig
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+REPO_DIR = os.path.dirname(PKG_DIR)
+CSRC = os.path.join(PKG_DIR, "csrc")
+LIB_PATH = os.path.join(PKG_DIR, "libntxent_b200.so")
+BINDING_PATH = os.path.join(PKG_DIR, "ntxent_cuda.so")
+
+KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu"]
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-Xcompiler", "-fPIC", "-Xptxas", "-v",
+]
+# No --use_fast_math: it would change expf/exp2f/division accuracy in the fp32 tolerance path;
+# the kernels call the fast intrinsics they want explicitly instead.
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", shutil.which("nvcc")):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found: the ntxent_b200 kernels cannot be built")
+
+
+def _stale(target: str, sources) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    """nvcc -> libntxent_b200.so (all kernels + the extern "C" boundary)."""
+    srcs = [os.path.join(CSRC, s) for s in KERNEL_SOURCES]
+    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    deps.append(os.path.join(REPO_DIR, "include", "ntxent_b200.h"))
+    if force or _stale(LIB_PATH, deps):
+        objs = []
+        procs = []
+        for s in srcs:
+            o = os.path.join(CSRC, os.path.basename(s)[:-3] + ".o")
+            objs.append(o)
+            cmd = [_nvcc(), *NVCC_FLAGS, "-I", os.path.join(REPO_DIR, "include"), "-c", s, "-o", o]
+            procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                                                text=True)))
+        log = []
+        for cmd, p in procs:
+            out, _ = p.communicate()
+            log.append(out)
+            if p.returncode != 0:
+                raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
+        link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH, *objs]  # static cudart
+        subprocess.run(link, check=True)
+        with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
+            f.write("\n".join(log))
+        if verbose:
+            print("\n".join(log))
+    return LIB_PATH
+
+
+def build_binding(force: bool = False) -> str:
+    """g++ -> ntxent_cuda.so, the torch extension with the reference's operator surface.
+
+    Links against libntxent_b200.so through an $ORIGIN rpath; only this TU sees torch headers.
+    """
+    import torch
+    from torch.utils import cpp_extension
+
+    src = os.path.join(CSRC, "binding.cpp")
+    deps = [src, os.path.join(REPO_DIR, "include", "ntxent_b200.h"),
+            os.path.join(REPO_DIR, "include", "ntxent_kernel.cuh")]
+    build_library()
+    if force or _stale(BINDING_PATH, deps + [LIB_PATH]):
+        inc = []
+        for p in cpp_extension.include_paths("cuda"):
+            inc += ["-isystem", p]
+        inc += ["-isystem", sysconfig.get_paths()["include"]]
+        torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
+        abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+        cmd = [
+            "/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=ntxent_cuda",
+            "-DTORCH_API_INCLUDE_EXTENSION_H", f"-D_GLIBCXX_USE_CXX11_ABI={abi}",
+            "-I", os.path.join(REPO_DIR, "include"), *inc, src, "-o", BINDING_PATH,
+            "-L", PKG_DIR, "-lntxent_b200", "-L", torch_lib, "-ltorch", "-ltorch_cpu", "-lc10",
+            "-ltorch_cuda", "-lc10_cuda", "-ltorch_python", "-L", "/usr/local/cuda/lib64", "-lcudart",
+            "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{torch_lib}",
+        ]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("binding build failed:\n" + r.stdout[-4000:])
+    return BINDING_PATH
+
+
+if __name__ == "__main__":
+    build_library(force="--force" in sys.argv, verbose=True)
+    if "--binding" in sys.argv:
+        build_binding(force="--force" in sys.argv)

@@ -1,0 +1,281 @@
+"""ctypes face of the C-ABI in include/ntxent_b200.h.
+
+torch is used only for device memory and streams: every call below hands raw device
+pointers, sizes and the current CUDA stream to `libntxent_b200.so`.  There is no fallback
+of any kind: a missing library or a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+from . import _build
+
+F32, BF16 = 0, 1
+FLAG_MIXED_PRECISION = 1
+FLAG_FORCE_SIMT = 2
+FLAG_ONLINE_MAX = 4
+BWD_SYMMETRIC, BWD_CONTRACT = 0, 1
+
+EXPORTS = [
+    "ntxent_b200_device_supported", "ntxent_b200_strerror", "ntxent_b200_version",
+    "ntxent_b200_workspace_bytes", "ntxent_b200_forward", "ntxent_b200_backward",
+    "ntxent_b200_forward_backward", "ntxent_b200_operand_size", "ntxent_b200_normalize",
+    "ntxent_b200_rows_workspace_bytes", "ntxent_b200_forward_rows", "ntxent_b200_backward_rows",
+    "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
+    "ntxent_b200_plan_info",
+]
+
+_lib = None
+
+
+class NTXentError(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load libntxent_b200.so (building it in-tree if the sources are newer)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        path = _build.build_library()
+    L = ctypes.CDLL(path)
+    vp, i64, u32, f32, sz, ci = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint, ctypes.c_float,
+                                 ctypes.c_size_t, ctypes.c_int)
+    L.ntxent_b200_device_supported.restype = ci
+    L.ntxent_b200_strerror.restype = ctypes.c_char_p
+    L.ntxent_b200_strerror.argtypes = [ci]
+    L.ntxent_b200_version.restype = ctypes.c_char_p
+    L.ntxent_b200_workspace_bytes.restype = sz
+    L.ntxent_b200_workspace_bytes.argtypes = [i64, i64, ci, u32]
+    L.ntxent_b200_forward.restype = ci
+    L.ntxent_b200_forward.argtypes = [vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
+    L.ntxent_b200_backward.restype = ci
+    L.ntxent_b200_backward.argtypes = [vp, vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
+    L.ntxent_b200_forward_backward.restype = ci
+    L.ntxent_b200_forward_backward.argtypes = [vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
+                                               vp, vp]
+    L.ntxent_b200_operand_size.restype = ci
+    L.ntxent_b200_operand_size.argtypes = [ci, u32]
+    L.ntxent_b200_normalize.restype = ci
+    L.ntxent_b200_normalize.argtypes = [vp, i64, i64, ci, u32, vp, vp, vp]
+    L.ntxent_b200_rows_workspace_bytes.restype = sz
+    L.ntxent_b200_rows_workspace_bytes.argtypes = [i64, i64, i64, ci, u32]
+    L.ntxent_b200_forward_rows.restype = ci
+    L.ntxent_b200_forward_rows.argtypes = [vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
+    L.ntxent_b200_backward_rows.restype = ci
+    L.ntxent_b200_backward_rows.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, ci, u32, vp, sz,
+                                            vp, vp, vp]
+    L.ntxent_b200_finalize_dz.restype = ci
+    L.ntxent_b200_finalize_dz.argtypes = [vp, vp, vp, vp, i64, i64, ci, vp, vp]
+    ip, fp = ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_float)
+    L.ntxent_b200_profile_begin.restype = ci
+    L.ntxent_b200_profile_end.restype = ci
+    L.ntxent_b200_profile_end.argtypes = [fp, ip, fp, ip]
+    L.ntxent_b200_plan_info.restype = ci
+    L.ntxent_b200_plan_info.argtypes = [i64, i64, i64, ci, u32, ip, ip, ip]
+    _lib = L
+    return L
+
+
+def profile_begin() -> None:
+    check(lib().ntxent_b200_profile_begin())
+
+
+def profile_end():
+    """-> dict(fwd_ms, fwd_launches, bwd_ms, bwd_launches) summed since profile_begin()."""
+    fm, bm, fn, bn = ctypes.c_float(), ctypes.c_float(), ctypes.c_int(), ctypes.c_int()
+    check(lib().ntxent_b200_profile_end(ctypes.byref(fm), ctypes.byref(fn), ctypes.byref(bm),
+                                        ctypes.byref(bn)))
+    return dict(fwd_ms=fm.value, fwd_launches=fn.value, bwd_ms=bm.value, bwd_launches=bn.value)
+
+
+def plan_info(M: int, D: int, row_count: int, dtype_code: int, flags: int = 0):
+    tc, fs, bs = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    check(lib().ntxent_b200_plan_info(M, D, row_count, dtype_code, flags, ctypes.byref(tc),
+                                      ctypes.byref(fs), ctypes.byref(bs)))
+    return dict(tcgen05=bool(tc.value), fwd_splits=fs.value, bwd_splits=bs.value)
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise NTXentError(f"ntxent_b200 error {rc}: {lib().ntxent_b200_strerror(rc).decode()}")
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise NTXentError(f"unsupported dtype {t.dtype}: NT-Xent embeddings must be float32 or bfloat16")
+
+
+def _require_cuda(*tensors) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NTXentError("ntxent_b200 runs on CUDA tensors only (there is no CPU path)")
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _flags(use_mixed_precision: bool, extra: int) -> int:
+    return (FLAG_MIXED_PRECISION if use_mixed_precision else 0) | int(extra)
+
+
+def operand_dtype(z_dtype: torch.dtype, flags: int) -> torch.dtype:
+    code = BF16 if z_dtype == torch.bfloat16 else F32
+    return torch.bfloat16 if lib().ntxent_b200_operand_size(code, flags) == 2 else torch.float32
+
+
+def workspace(M: int, D: int, z: torch.Tensor, flags: int) -> torch.Tensor:
+    n = lib().ntxent_b200_workspace_bytes(M, D, _dtype_code(z), flags)
+    if n == 0:
+        raise NTXentError(f"unsupported NT-Xent shape M={M}, D={D} (need even M >= 2, D % 8 == 0, "
+                          f"8 <= D <= 1024)")
+    return torch.empty(n, dtype=torch.uint8, device=z.device)
+
+
+def forward(z: torch.Tensor, tau: float, use_mixed_precision: bool = False, flags: int = 0,
+            ws: torch.Tensor | None = None):
+    """-> (loss[1] fp32, lse[M] fp32), both on z's device; asynchronous."""
+    _require_cuda(z)
+    z = z.contiguous()
+    M, D = z.shape
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        ws = workspace(M, D, z, fl) if ws is None else ws
+        loss = torch.empty(1, dtype=torch.float32, device=z.device)
+        lse = torch.empty(M, dtype=torch.float32, device=z.device)
+        check(lib().ntxent_b200_forward(_ptr(z), M, D, float(tau), _dtype_code(z), fl, _ptr(ws),
+                                        ws.numel(), _ptr(loss), _ptr(lse), _stream()))
+    return loss, lse
+
+
+def backward(z: torch.Tensor, lse: torch.Tensor, grad_out: torch.Tensor | None, tau: float,
+             use_mixed_precision: bool = False, flags: int = 0, ws: torch.Tensor | None = None,
+             want_pos_prob: bool = True):
+    """-> (dz[M,D] in z's dtype, pos_prob[M] fp32 or None)."""
+    _require_cuda(z, lse, grad_out)
+    z = z.contiguous()
+    lse = lse.contiguous().float()
+    M, D = z.shape
+    if lse.numel() != M:
+        raise NTXentError(f"backward expects the forward's row log-sum-exp of {M} entries, got a "
+                          f"tensor of shape {tuple(lse.shape)} (an [M,M] softmax is never formed)")
+    if grad_out is not None:
+        grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        ws = workspace(M, D, z, fl) if ws is None else ws
+        dz = torch.empty_like(z)
+        pp = torch.empty(M, dtype=torch.float32, device=z.device) if want_pos_prob else None
+        check(lib().ntxent_b200_backward(_ptr(z), _ptr(lse), _ptr(grad_out), M, D, float(tau),
+                                         _dtype_code(z), fl, _ptr(ws), ws.numel(), _ptr(dz), _ptr(pp),
+                                         _stream()))
+    return dz, pp
+
+
+def forward_backward(z: torch.Tensor, tau: float, grad_out: torch.Tensor | None = None,
+                     use_mixed_precision: bool = False, flags: int = 0,
+                     ws: torch.Tensor | None = None, out=None):
+    """Fused call -> (loss[1], lse[M], dz[M,D]).  `out` may carry preallocated (loss, lse, dz)."""
+    _require_cuda(z, grad_out)
+    z = z.contiguous()
+    M, D = z.shape
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        ws = workspace(M, D, z, fl) if ws is None else ws
+        if out is None:
+            loss = torch.empty(1, dtype=torch.float32, device=z.device)
+            lse = torch.empty(M, dtype=torch.float32, device=z.device)
+            dz = torch.empty_like(z)
+        else:
+            loss, lse, dz = out
+        check(lib().ntxent_b200_forward_backward(_ptr(z), _ptr(grad_out), M, D, float(tau),
+                                                 _dtype_code(z), fl, _ptr(ws), ws.numel(), _ptr(loss),
+                                                 _ptr(lse), _ptr(dz), None, _stream()))
+    return loss, lse, dz
+
+
+# ---- row-partitioned building blocks -----------------------------------------------
+def normalize(z_rows: torch.Tensor, flags: int = 0):
+    """-> (u[rows,D] in the operand dtype, inv_norm[rows] fp32)."""
+    _require_cuda(z_rows)
+    z_rows = z_rows.contiguous()
+    rows, D = z_rows.shape
+    with torch.cuda.device(z_rows.device):
+        u = torch.empty(rows, D, dtype=operand_dtype(z_rows.dtype, flags), device=z_rows.device)
+        inv = torch.empty(rows, dtype=torch.float32, device=z_rows.device)
+        check(lib().ntxent_b200_normalize(_ptr(z_rows), rows, D, _dtype_code(z_rows), flags, _ptr(u),
+                                          _ptr(inv), _stream()))
+    return u, inv
+
+
+def _op_code(u_all: torch.Tensor) -> int:
+    return BF16 if u_all.dtype == torch.bfloat16 else F32
+
+
+def rows_workspace(M: int, D: int, row_count: int, u_all: torch.Tensor, flags: int) -> torch.Tensor:
+    n = lib().ntxent_b200_rows_workspace_bytes(M, D, row_count, _op_code(u_all), flags)
+    if n == 0:
+        raise NTXentError(f"unsupported NT-Xent row block M={M}, D={D}, rows={row_count}")
+    return torch.empty(n, dtype=torch.uint8, device=u_all.device)
+
+
+def forward_rows(u_all: torch.Tensor, row_begin: int, row_count: int, tau: float, flags: int = 0,
+                 ws: torch.Tensor | None = None):
+    """-> (lse_rows[row_count], loss_partial[1]) for rows [row_begin, row_begin+row_count)."""
+    _require_cuda(u_all)
+    u_all = u_all.contiguous()
+    M, D = u_all.shape
+    with torch.cuda.device(u_all.device):
+        ws = rows_workspace(M, D, row_count, u_all, flags) if ws is None else ws
+        lse = torch.empty(row_count, dtype=torch.float32, device=u_all.device)
+        lp = torch.empty(1, dtype=torch.float32, device=u_all.device)
+        check(lib().ntxent_b200_forward_rows(_ptr(u_all), M, D, row_begin, row_count, float(tau),
+                                             _op_code(u_all), flags, _ptr(ws), ws.numel(), _ptr(lse),
+                                             _ptr(lp), _stream()))
+    return lse, lp
+
+
+def backward_rows(u_all: torch.Tensor, lse_all: torch.Tensor, row_begin: int, row_count: int,
+                  tau: float, mode: int = BWD_SYMMETRIC, flags: int = 0,
+                  ws: torch.Tensor | None = None):
+    """-> (du_rows[row_count,D] fp32, du_cols[M,D] fp32 or None)."""
+    _require_cuda(u_all, lse_all)
+    u_all = u_all.contiguous()
+    M, D = u_all.shape
+    with torch.cuda.device(u_all.device):
+        ws = rows_workspace(M, D, row_count, u_all, flags) if ws is None else ws
+        du_rows = torch.empty(row_count, D, dtype=torch.float32, device=u_all.device)
+        du_cols = (torch.empty(M, D, dtype=torch.float32, device=u_all.device)
+                   if mode == BWD_CONTRACT else None)
+        check(lib().ntxent_b200_backward_rows(_ptr(u_all), _ptr(lse_all), M, D, row_begin, row_count,
+                                              float(tau), mode, _op_code(u_all), flags, _ptr(ws),
+                                              ws.numel(), _ptr(du_rows), _ptr(du_cols), _stream()))
+    return du_rows, du_cols
+
+
+def finalize_dz(du_rows: torch.Tensor, z_rows: torch.Tensor, inv_norm: torch.Tensor,
+                grad_out: torch.Tensor | None = None) -> torch.Tensor:
+    _require_cuda(du_rows, z_rows, inv_norm, grad_out)
+    z_rows = z_rows.contiguous()
+    rows, D = z_rows.shape
+    if grad_out is not None:
+        grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+    with torch.cuda.device(z_rows.device):
+        dz = torch.empty_like(z_rows)
+        check(lib().ntxent_b200_finalize_dz(_ptr(du_rows.contiguous()), _ptr(z_rows), _ptr(inv_norm),
+                                            _ptr(grad_out), rows, D, _dtype_code(z_rows), _ptr(dz),
+                                            _stream()))
+    return dz

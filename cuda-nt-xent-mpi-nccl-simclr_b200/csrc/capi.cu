@@ -1,0 +1,435 @@
+// capi.cu -- the extern "C" boundary declared in include/ntxent_b200.h: argument checks,
+// workspace carving, kernel-family dispatch.  Nothing here allocates or synchronises.
+#include "../../include/ntxent_b200.h"
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+#include "tc_kernels.cuh"
+
+namespace ntxent_b200 {
+
+int device_sm_count() {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+        (void)cudaGetLastError();
+        return 148;
+    }
+    return sms;
+}
+
+SplitPlan plan_splits(int64_t a_count, int64_t b_count, int row_tile, int col_tile, int slots,
+                      int max_split) {
+    SplitPlan best{};
+    best.row_tiles = (int)((a_count + row_tile - 1) / row_tile);
+    const int64_t col_tiles = std::max<int64_t>(1, (b_count + col_tile - 1) / col_tile);
+    double best_cost = 1e300;
+    const int lim = (int)std::min<int64_t>(max_split, col_tiles);
+    for (int ns = 1; ns <= lim; ++ns) {
+        const int64_t tiles_per = (col_tiles + ns - 1) / ns;
+        const int64_t real_ns = (col_tiles + tiles_per - 1) / tiles_per;
+        if (real_ns != ns) continue;
+        const int64_t ctas = (int64_t)best.row_tiles * ns;
+        const int64_t waves = (ctas + slots - 1) / slots;
+        // per-CTA cost: its column tiles plus ~1.5 tiles of prologue/epilogue; a small
+        // per-split charge for the partial that the epilogue has to re-read
+        const double cost = (double)waves * ((double)tiles_per + 1.5) + 0.02 * ns;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best.nsplit = ns;
+            best.cols_per_split = tiles_per * col_tile;
+        }
+    }
+    return best;
+}
+
+namespace {
+
+// Optional per-kernel timing for the benchmark (ntxent_b200_profile_begin/_end): CUDA events
+// recorded on the launching stream around the two tile kernels.  Off by default; not
+// thread-safe; the only place in the library that creates CUDA objects.
+struct KernelTimer {
+    bool on = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[2];
+    void start(int which, cudaStream_t st) {
+        if (!on) return;
+        cudaEvent_t a, b;
+        if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+        ev[which].push_back({a, b});
+        cudaEventRecord(a, st);
+    }
+    void stop(int which, cudaStream_t st) {
+        if (!on || ev[which].empty()) return;
+        cudaEventRecord(ev[which].back().second, st);
+    }
+};
+KernelTimer g_timer;
+
+constexpr int kMaxSplit = 32;
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+inline bool op_is_bf16(int dtype, unsigned flags) {
+    return dtype == NTXENT_BF16 || (flags & NTXENT_FLAG_MIXED_PRECISION);
+}
+inline bool want_tc(int64_t D, bool op_bf16, unsigned flags) {
+    return !(flags & NTXENT_FLAG_FORCE_SIMT) && tc_supported(D, op_bf16);
+}
+
+struct Plans {
+    SplitPlan fwd, bwd_rows, bwd_cols;
+    bool tc;
+};
+
+// All split decisions in one place so that sizing and launching can never disagree.
+Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned flags) {
+    Plans p;
+    p.tc = want_tc(D, op_bf16, flags);
+    const int sms = device_sm_count();
+    if (p.tc) {
+        p.fwd = tc_plan_fwd(M, D, row_count, sms);
+        p.bwd_rows = tc_plan_bwd(M, D, row_count, M, sms);
+        p.bwd_cols = tc_plan_bwd(M, D, M, row_count, sms);
+    } else {
+        p.fwd = plan_splits(row_count, M, 64, 64, sms * 4, kMaxSplit);
+        p.bwd_rows = plan_splits(row_count, M, 64, 64, sms * 2, kMaxSplit);
+        p.bwd_cols = plan_splits(M, row_count, 64, 64, sms * 2, kMaxSplit);
+    }
+    return p;
+}
+
+struct RowsWs {
+    unsigned* counter;
+    float* block_partials;
+    float* part_m;
+    float* part_s;
+    float* acc_rows;
+    float* acc_cols;
+    size_t bytes;
+};
+
+RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Plans& p,
+                  bool with_cols) {
+    RowsWs w{};
+    size_t off = 0;
+    auto take = [&](size_t n) {
+        char* ptr = base ? base + off : nullptr;
+        off += align_up(n);
+        return ptr;
+    };
+    w.counter = (unsigned*)take(kAlign);
+    w.block_partials = (float*)take(sizeof(float) * (size_t)((row_count + 7) / 8));
+    w.part_m = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
+    w.part_s = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
+    w.acc_rows = (float*)take(sizeof(float) * (size_t)p.bwd_rows.nsplit * row_count * D);
+    if (with_cols) w.acc_cols = (float*)take(sizeof(float) * (size_t)p.bwd_cols.nsplit * M * D);
+    w.bytes = off;
+    return w;
+}
+
+struct DeviceWs {
+    void* U;
+    float* inv_norm;
+    RowsWs rows;
+    size_t bytes;
+};
+
+DeviceWs carve_device(char* base, int64_t M, int64_t D, bool op_bf16, const Plans& p) {
+    DeviceWs w{};
+    size_t off = 0;
+    w.U = base;
+    off += align_up((size_t)M * D * (op_bf16 ? 2 : 4));
+    w.inv_norm = (float*)(base ? base + off : nullptr);
+    off += align_up(sizeof(float) * (size_t)M);
+    w.rows = carve_rows(base ? base + off : nullptr, M, D, M, p, false);
+    w.bytes = off + w.rows.bytes;
+    return w;
+}
+
+int check_shape(int64_t M, int64_t D, float tau, int dtype) {
+    if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (M < 2 || (M & 1) || !(tau > 0.f) || !(tau < INFINITY)) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    if (M > (int64_t)1 << 24) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    return NTXENT_OK;
+}
+
+#define NTX_TRY(expr)                                  \
+    do {                                               \
+        cudaError_t e__ = (expr);                      \
+        if (e__ != cudaSuccess) return (int)e__;       \
+    } while (0)
+
+int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
+                     int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
+                     float* loss_out, float loss_scale, cudaStream_t st) {
+    g_timer.start(0, st);
+    if (p.tc)
+        NTX_TRY(tc_launch_fwd(u_all, M, D, row_begin, row_count, tau, p.fwd, w.part_m, w.part_s,
+                              w.counter, st));
+    else
+        NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
+                                w.part_s, w.counter, st));
+    g_timer.stop(0, st);
+    NTX_TRY(launch_fwd_finalize(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
+                                w.part_m, w.part_s, lse_rows, w.block_partials, w.counter, loss_out,
+                                loss_scale, st));
+    return NTXENT_OK;
+}
+
+int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
+                  int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float tau,
+                  int mode, bool tc, const SplitPlan& plan, float* acc, cudaStream_t st) {
+    g_timer.start(1, st);
+    if (tc)
+        NTX_TRY(tc_launch_bwd(u_all, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau, mode,
+                              plan, acc, st));
+    else
+        NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
+                                tau, mode, plan, acc, st));
+    g_timer.stop(1, st);
+    return NTXENT_OK;
+}
+
+int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_bf16, const float* lse,
+                        const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
+                        void* dz_out, float* pos_prob_out, cudaStream_t st) {
+    int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p.tc, p.bwd_rows,
+                           w.rows.acc_rows, st);
+    if (rc != NTXENT_OK) return rc;
+    BwdEpilogueArgs e{};
+    e.acc = w.rows.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = w.U; e.op_bf16 = op_bf16;
+    e.M = M; e.D = D; e.a_begin = 0; e.a_count = M;
+    e.pos_coeff = 2.f; e.pos_lo = 0; e.pos_hi = M;
+    e.scale = 1.0f / (tau * (float)M);
+    e.du_out = nullptr; e.z_rows = z; e.z_bf16 = z_bf16; e.inv_norm = w.inv_norm;
+    e.grad_out = grad_out; e.dz_out = dz_out;
+    e.lse_all = lse; e.inv_tau = 1.0f / tau; e.pos_prob_out = pos_prob_out;
+    NTX_TRY(launch_bwd_epilogue(e, st));
+    return NTXENT_OK;
+}
+
+}  // namespace
+}  // namespace ntxent_b200
+
+using namespace ntxent_b200;
+
+extern "C" {
+
+int ntxent_b200_device_supported(void) {
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return major == 10 ? 1 : 0;
+}
+
+const char* ntxent_b200_version(void) { return "ntxent_b200 0.1 (sm_100a)"; }
+
+const char* ntxent_b200_strerror(int code) {
+    switch (code) {
+        case NTXENT_OK: return "ok";
+        case NTXENT_ERR_INVALID_ARGUMENT:
+            return "invalid argument (null pointer, odd or too small M, tau <= 0, unknown dtype/mode)";
+        case NTXENT_ERR_UNSUPPORTED_DEVICE: return "device is not sm_100 (B200)";
+        case NTXENT_ERR_WORKSPACE_TOO_SMALL:
+            return "workspace smaller than ntxent_b200_*workspace_bytes()";
+        case NTXENT_ERR_UNSUPPORTED_SHAPE:
+            return "unsupported shape (need 8 <= D <= 1024, D % 8 == 0, M <= 2^24)";
+        default: break;
+    }
+    if (code > 0) return cudaGetErrorString((cudaError_t)code);
+    return "unknown ntxent_b200 error";
+}
+
+int ntxent_b200_profile_begin(void) {
+    g_timer.on = true;
+    return NTXENT_OK;
+}
+
+int ntxent_b200_profile_end(float* fwd_ms, int* fwd_launches, float* bwd_ms, int* bwd_launches) {
+    g_timer.on = false;
+    float* ms[2] = {fwd_ms, bwd_ms};
+    int* cnt[2] = {fwd_launches, bwd_launches};
+    int rc = NTXENT_OK;
+    for (int k = 0; k < 2; ++k) {
+        float total = 0.f;
+        int n = 0;
+        for (auto& pr : g_timer.ev[k]) {
+            float t = 0.f;
+            cudaError_t e = cudaEventSynchronize(pr.second);
+            if (e == cudaSuccess) e = cudaEventElapsedTime(&t, pr.first, pr.second);
+            if (e == cudaSuccess) { total += t; ++n; } else rc = (int)e;
+            cudaEventDestroy(pr.first);
+            cudaEventDestroy(pr.second);
+        }
+        g_timer.ev[k].clear();
+        if (ms[k]) *ms[k] = total;
+        if (cnt[k]) *cnt[k] = n;
+    }
+    return rc;
+}
+
+int ntxent_b200_plan_info(int64_t M, int64_t D, int64_t row_count, int dtype, unsigned flags,
+                          int* uses_tcgen05, int* fwd_splits, int* bwd_splits) {
+    if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK || row_count < 1 || row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const Plans p = make_plans(M, D, row_count, op_is_bf16(dtype, flags), flags);
+    if (uses_tcgen05) *uses_tcgen05 = p.tc ? 1 : 0;
+    if (fwd_splits) *fwd_splits = p.fwd.nsplit;
+    if (bwd_splits) *bwd_splits = p.bwd_rows.nsplit;
+    return NTXENT_OK;
+}
+
+int ntxent_b200_operand_size(int dtype, unsigned flags) { return op_is_bf16(dtype, flags) ? 2 : 4; }
+
+size_t ntxent_b200_workspace_bytes(int64_t M, int64_t D, int dtype, unsigned flags) {
+    if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK) return 0;
+    const bool opb = op_is_bf16(dtype, flags);
+    return carve_device(nullptr, M, D, opb, make_plans(M, D, M, opb, flags)).bytes;
+}
+
+size_t ntxent_b200_rows_workspace_bytes(int64_t M, int64_t D, int64_t row_count, int dtype,
+                                        unsigned flags) {
+    if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK || row_count < 1 || row_count > M) return 0;
+    const bool opb = op_is_bf16(dtype, flags);
+    return carve_rows(nullptr, M, D, row_count, make_plans(M, D, row_count, opb, flags), true).bytes;
+}
+
+int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
+                          void* u_out, float* inv_norm_out, ntxent_stream_t stream) {
+    if (!z || !u_out || rows < 0) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, rows, D, u_out, op_is_bf16(dtype, flags),
+                             inv_norm_out, stream));
+    return NTXENT_OK;
+}
+
+int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,
+                        void* workspace, size_t workspace_bytes, float* loss_out, float* lse_out,
+                        ntxent_stream_t stream) {
+    if (!z || !workspace || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags);
+    const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
+                            1.0f / (float)M, stream);
+}
+
+int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out, int64_t M,
+                         int64_t D, float tau, int dtype, unsigned flags, void* workspace,
+                         size_t workspace_bytes, void* dz_out, float* pos_prob_out,
+                         ntxent_stream_t stream) {
+    if (!z || !lse || !workspace || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags);
+    const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
+                               pos_prob_out, stream);
+}
+
+int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M, int64_t D,
+                                 float tau, int dtype, unsigned flags, void* workspace,
+                                 size_t workspace_bytes, float* loss_out, float* lse_out,
+                                 void* dz_out, float* pos_prob_out, ntxent_stream_t stream) {
+    if (!z || !workspace || !loss_out || !lse_out || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags);
+    const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    rc = run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out, 1.0f / (float)M,
+                          stream);
+    if (rc != NTXENT_OK) return rc;
+    return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p,
+                               dz_out, pos_prob_out, stream);
+}
+
+int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+                             int64_t row_count, float tau, int dtype, unsigned flags,
+                             void* workspace, size_t workspace_bytes, float* lse_rows_out,
+                             float* loss_partial_out, ntxent_stream_t stream) {
+    if (!u_all || !workspace || !lse_rows_out || !loss_partial_out)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags);
+    const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    return run_forward_rows(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_rows_out,
+                            loss_partial_out, 1.0f, stream);
+}
+
+int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                              int64_t row_begin, int64_t row_count, float tau, int mode, int dtype,
+                              unsigned flags, void* workspace, size_t workspace_bytes,
+                              float* du_rows_out, float* du_cols_out, ntxent_stream_t stream) {
+    if (!u_all || !lse_all || !workspace || !du_rows_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (mode != NTXENT_BWD_SYMMETRIC && mode != NTXENT_BWD_CONTRACT)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (mode == NTXENT_BWD_CONTRACT && !du_cols_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags);
+    const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    const bool sym = (mode == NTXENT_BWD_SYMMETRIC);
+    rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau,
+                       sym ? kSym : kRow, p.tc, p.bwd_rows, w.acc_rows, stream);
+    if (rc != NTXENT_OK) return rc;
+    BwdEpilogueArgs e{};
+    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = u_all; e.op_bf16 = opb;
+    e.M = M; e.D = D; e.a_begin = row_begin; e.a_count = row_count;
+    e.pos_coeff = sym ? 2.f : 1.f; e.pos_lo = 0; e.pos_hi = M;
+    e.scale = 1.0f / (tau * (float)M);
+    e.du_out = du_rows_out;
+    NTX_TRY(launch_bwd_epilogue(e, stream));
+    if (!sym) {
+        rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p.tc,
+                           p.bwd_cols, w.acc_cols, stream);
+        if (rc != NTXENT_OK) return rc;
+        BwdEpilogueArgs c{};
+        c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit; c.u_all = u_all; c.op_bf16 = opb;
+        c.M = M; c.D = D; c.a_begin = 0; c.a_count = M;
+        c.pos_coeff = 1.f; c.pos_lo = row_begin; c.pos_hi = row_begin + row_count;
+        c.scale = e.scale;
+        c.du_out = du_cols_out;
+        NTX_TRY(launch_bwd_epilogue(c, stream));
+    }
+    return NTXENT_OK;
+}
+
+int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,
+                            const float* grad_out, int64_t rows, int64_t D, int dtype, void* dz_out,
+                            ntxent_stream_t stream) {
+    if (!du_rows || !z_rows || !inv_norm_rows || !dz_out || rows < 0)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    NTX_TRY(launch_finalize_dz(du_rows, z_rows, dtype == NTXENT_BF16, inv_norm_rows, grad_out, rows,
+                               D, dz_out, stream));
+    return NTXENT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,131 @@
+// common.cuh -- shared declarations of the ntxent_b200 library (no torch, no CUTLASS).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ntxent_b200 {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kNormEps = 1e-12f;  // torch.nn.functional.normalize's default eps
+
+// Which weights the backward tile pass forms for a row a (of the A range) and a
+// column b (of the B range); S_ab = u_a.u_b/tau, diagonal a == b always masked.
+//   kSym : W_ab = exp(S_ab - l_a) + exp(S_ab - l_b)   (G + G^T, single device / symmetric form)
+//   kRow : W_ab = exp(S_ab - l_a)                     (row term G_{I,:} U)
+//   kCol : W_ab = exp(S_ab - l_b)                     (column term G_{I,:}^T U_I, a over all rows)
+enum BwdMode : int { kSym = 0, kRow = 1, kCol = 2 };
+
+struct SplitPlan {
+    int row_tiles;       // tiles over the A range
+    int nsplit;          // column splits (grid.y)
+    int64_t cols_per_split;  // multiple of the column tile
+};
+
+// Column-split heuristic shared by the workspace sizing and the launchers: pick the
+// split count whose last wave wastes the least, given `num_sms` concurrently running CTAs.
+SplitPlan plan_splits(int64_t a_count, int64_t b_count, int row_tile, int col_tile, int num_sms,
+                      int max_split);
+
+int device_sm_count();  // SM count of the current device; 148 when there is none
+
+// ---- launchers (all asynchronous on `stream`; return the launch status) ----------
+cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
+                             bool op_bf16, float* inv_norm, cudaStream_t stream);
+
+// SIMT (fp32 FMA) tile kernels.
+cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                            int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
+                            float* part_m, float* part_s, unsigned* counter, cudaStream_t stream);
+cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
+                            int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
+                            int64_t b_count, float tau, int mode, const SplitPlan& plan, float* acc,
+                            cudaStream_t stream);
+
+// Forward finalize: combine the split partials into l_i, add the positive logit, reduce the loss.
+cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                                int64_t row_begin, int64_t row_count, float tau, int nsplit,
+                                const float* part_m, const float* part_s, float* lse_rows,
+                                float* block_partials, unsigned* counter, float* loss_out,
+                                float loss_scale, cudaStream_t stream);
+
+struct BwdEpilogueArgs {
+    const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
+    int nsplit;
+    const void* u_all;       // [M, D] operands
+    bool op_bf16;
+    int64_t M, D, a_begin, a_count;
+    float pos_coeff;         // multiple of u_pos(a) to subtract (2 sym, 1 row/col)
+    int64_t pos_lo, pos_hi;  // subtract only when pos(a) lies in [pos_lo, pos_hi)
+    float scale;             // 1 / (tau * M)
+    // output A: plain dU rows
+    float* du_out;           // [a_count, D] or nullptr
+    // output B: Jacobian applied (du_out == nullptr)
+    const void* z_rows;      // [a_count, D] in z dtype
+    bool z_bf16;
+    const float* inv_norm;   // [a_count]
+    const float* grad_out;   // device scalar or nullptr
+    void* dz_out;            // [a_count, D] in z dtype
+    // optional P_{a,pos(a)}
+    const float* lse_all;    // [M] (needed only with pos_prob_out)
+    float inv_tau;
+    float* pos_prob_out;     // [a_count] or nullptr
+};
+cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& args, cudaStream_t stream);
+
+cudaError_t launch_finalize_dz(const float* du_rows, const void* z_rows, bool z_bf16,
+                               const float* inv_norm, const float* grad_out, int64_t rows, int64_t D,
+                               void* dz_out, cudaStream_t stream);
+
+// ---- element access helpers ---------------------------------------------------
+template <typename T>
+struct Elem;
+template <>
+struct Elem<float> {
+    static __device__ __forceinline__ float4 ld4(const float* p) {
+        return *reinterpret_cast<const float4*>(p);
+    }
+    static __device__ __forceinline__ void st4(float* p, float4 v) {
+        *reinterpret_cast<float4*>(p) = v;
+    }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+    static __device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+        uint2 raw = *reinterpret_cast<const uint2*>(p);
+        __nv_bfloat162 lo = *reinterpret_cast<__nv_bfloat162*>(&raw.x);
+        __nv_bfloat162 hi = *reinterpret_cast<__nv_bfloat162*>(&raw.y);
+        float2 a = __bfloat1622float2(lo), b = __bfloat1622float2(hi);
+        return make_float4(a.x, a.y, b.x, b.y);
+    }
+    static __device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);
+        __nv_bfloat162 hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 raw;
+        raw.x = *reinterpret_cast<uint32_t*>(&lo);
+        raw.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(p) = raw;
+    }
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Merge two (max, sum) pairs of a base-2 logsumexp; safe for empty (-inf, 0) partials.
+__device__ __forceinline__ void lse2_merge(float& m, float& s, float m2, float s2) {
+    float mn = fmaxf(m, m2);
+    if (mn == -INFINITY) { m = mn; s = 0.f; return; }
+    s = s * exp2f(m - mn) + s2 * exp2f(m2 - mn);
+    m = mn;
+}
+
+}  // namespace ntxent_b200

@@ -1,0 +1,266 @@
+// epilogue_kernels.cu -- the small HBM-bound kernels either side of the tile passes:
+//   fwd_finalize : split partials -> l_i, positive logit, deterministic loss reduction
+//                  (replaces compute_loss_kernel, src/ntxent_kernel.cu:105-134, and its
+//                   single-block diagonal walk);
+//   bwd_epilogue : split partials -> dU (positive term, 1/(tau M)), optionally the
+//                  normalisation Jacobian -> dz and P_{i,pos(i)};
+//   finalize_dz  : the Jacobian alone (multi-GPU path, after the reduce-scatter).
+#include "common.cuh"
+
+namespace ntxent_b200 {
+
+constexpr int kMaxDChunks = 8;  // D <= 1024: each lane holds 4 floats per 128-wide chunk
+
+// -------------------------------------------------------------- fwd finalize ---
+template <typename T>
+__global__ void __launch_bounds__(256)
+fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
+                    float inv_tau, int nsplit, const float* __restrict__ part_m,
+                    const float* __restrict__ part_s, float* __restrict__ lse_rows,
+                    float* __restrict__ block_partials, unsigned* __restrict__ counter,
+                    float* __restrict__ loss_out, float loss_scale) {
+    __shared__ float warp_contrib[8];
+    __shared__ double red[256];
+    __shared__ bool is_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+    float contrib = 0.f;
+    if (r < row_count) {
+        float m = -INFINITY, s = 0.f;
+        for (int sp = lane; sp < nsplit; sp += 32)
+            lse2_merge(m, s, part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+            const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+            lse2_merge(m, s, m2, s2);
+        }
+        const float l = (m + log2f(s)) * kLn2;
+        const int64_t row = row_begin + r;
+        const int64_t pos = (row + M / 2) % M;
+        const T* ui = U + row * D;
+        const T* up = U + pos * D;
+        float dot = 0.f;
+        for (int k = lane * 4; k < D; k += 128) {
+            const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
+            dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        }
+        dot = warp_sum(dot);
+        if (lane == 0) lse_rows[r] = l;
+        contrib = l - dot * inv_tau;
+    }
+    if (lane == 0) warp_contrib[warp] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float bsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) bsum += warp_contrib[w];
+        block_partials[blockIdx.x] = bsum;
+        __threadfence();
+        const unsigned done = atomicAdd(counter, 1u);
+        is_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // the last CTA reduces the per-CTA partials in a fixed order (run-to-run deterministic)
+    double acc = 0.0;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += 256) acc += (double)block_partials[b];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        *loss_out = (float)(red[0] * (double)loss_scale);
+        *counter = 0u;
+    }
+}
+
+cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                                int64_t row_begin, int64_t row_count, float tau, int nsplit,
+                                const float* part_m, const float* part_s, float* lse_rows,
+                                float* block_partials, unsigned* counter, float* loss_out,
+                                float loss_scale, cudaStream_t stream) {
+    dim3 grid((unsigned)((row_count + 7) / 8)), block(256);
+    if (op_bf16)
+        fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
+            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
+            part_s, lse_rows, block_partials, counter, loss_out, loss_scale);
+    else
+        fwd_finalize_kernel<float><<<grid, block, 0, stream>>>(
+            (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m, part_s,
+            lse_rows, block_partials, counter, loss_out, loss_scale);
+    return cudaGetLastError();
+}
+
+// -------------------------------------------------------------- bwd epilogue ---
+struct BwdEpiDev {
+    const float* acc;
+    int nsplit;
+    int64_t M, a_begin, a_count;
+    int D;
+    float pos_coeff;
+    int64_t pos_lo, pos_hi;
+    float scale;
+    float* du_out;
+    const float* inv_norm;
+    const float* grad_out;
+    const float* lse_all;
+    float inv_tau;
+    float* pos_prob_out;
+};
+
+template <typename TOp, typename TZ>
+__global__ void __launch_bounds__(256)
+bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict__ z_rows,
+                    TZ* __restrict__ dz_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= p.a_count) return;
+    const int D = p.D;
+    const int64_t row = p.a_begin + r;
+    const int64_t pos = (row + p.M / 2) % p.M;
+    const float pc = (pos >= p.pos_lo && pos < p.pos_hi) ? p.pos_coeff : 0.f;
+    const TOp* up = U + pos * D;
+    float4 du[kMaxDChunks];
+#pragma unroll
+    for (int c = 0; c < kMaxDChunks; ++c) {
+        const int k = c * 128 + lane * 4;
+        if (k >= D) break;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int sp = 0; sp < p.nsplit; ++sp) {
+            const float4 t =
+                *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+        }
+        if (pc != 0.f) {
+            const float4 q = Elem<TOp>::ld4(up + k);
+            v.x -= pc * q.x; v.y -= pc * q.y; v.z -= pc * q.z; v.w -= pc * q.w;
+        }
+        v.x *= p.scale; v.y *= p.scale; v.z *= p.scale; v.w *= p.scale;
+        du[c] = v;
+    }
+    if (p.pos_prob_out) {
+        const TOp* ui = U + row * D;
+        float dot = 0.f;
+        for (int k = lane * 4; k < D; k += 128) {
+            const float4 a = Elem<TOp>::ld4(ui + k), b = Elem<TOp>::ld4(up + k);
+            dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        }
+        dot = warp_sum(dot);
+        if (lane == 0) p.pos_prob_out[r] = expf(dot * p.inv_tau - p.lse_all[row]);
+    }
+    if (p.du_out) {
+#pragma unroll
+        for (int c = 0; c < kMaxDChunks; ++c) {
+            const int k = c * 128 + lane * 4;
+            if (k >= D) break;
+            *reinterpret_cast<float4*>(p.du_out + r * D + k) = du[c];
+        }
+        return;
+    }
+    // normalisation Jacobian with the exact fp32 direction u = z * inv_norm
+    const float inv = p.inv_norm[r];
+    const float g = p.grad_out ? *p.grad_out : 1.0f;
+    float4 u[kMaxDChunks];
+    float dot = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxDChunks; ++c) {
+        const int k = c * 128 + lane * 4;
+        if (k >= D) break;
+        float4 zz = Elem<TZ>::ld4(z_rows + r * D + k);
+        zz.x *= inv; zz.y *= inv; zz.z *= inv; zz.w *= inv;
+        u[c] = zz;
+        dot += du[c].x * zz.x + du[c].y * zz.y + du[c].z * zz.z + du[c].w * zz.w;
+    }
+    dot = warp_sum(dot);
+    const float gi = g * inv;
+#pragma unroll
+    for (int c = 0; c < kMaxDChunks; ++c) {
+        const int k = c * 128 + lane * 4;
+        if (k >= D) break;
+        float4 o;
+        o.x = gi * (du[c].x - dot * u[c].x);
+        o.y = gi * (du[c].y - dot * u[c].y);
+        o.z = gi * (du[c].z - dot * u[c].z);
+        o.w = gi * (du[c].w - dot * u[c].w);
+        Elem<TZ>::st4(dz_out + r * D + k, o);
+    }
+}
+
+cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
+    if (a.a_count == 0) return cudaSuccess;
+    BwdEpiDev p;
+    p.acc = a.acc; p.nsplit = a.nsplit; p.M = a.M; p.a_begin = a.a_begin; p.a_count = a.a_count;
+    p.D = (int)a.D; p.pos_coeff = a.pos_coeff; p.pos_lo = a.pos_lo; p.pos_hi = a.pos_hi;
+    p.scale = a.scale; p.du_out = a.du_out; p.inv_norm = a.inv_norm; p.grad_out = a.grad_out;
+    p.lse_all = a.lse_all; p.inv_tau = a.inv_tau; p.pos_prob_out = a.pos_prob_out;
+    dim3 grid((unsigned)((a.a_count + 7) / 8)), block(256);
+    if (a.op_bf16) {
+        if (a.z_bf16)
+            bwd_epilogue_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, stream>>>(
+                p, (const __nv_bfloat16*)a.u_all, (const __nv_bfloat16*)a.z_rows,
+                (__nv_bfloat16*)a.dz_out);
+        else
+            bwd_epilogue_kernel<__nv_bfloat16, float><<<grid, block, 0, stream>>>(
+                p, (const __nv_bfloat16*)a.u_all, (const float*)a.z_rows, (float*)a.dz_out);
+    } else {
+        if (a.z_bf16)
+            bwd_epilogue_kernel<float, __nv_bfloat16><<<grid, block, 0, stream>>>(
+                p, (const float*)a.u_all, (const __nv_bfloat16*)a.z_rows, (__nv_bfloat16*)a.dz_out);
+        else
+            bwd_epilogue_kernel<float, float><<<grid, block, 0, stream>>>(
+                p, (const float*)a.u_all, (const float*)a.z_rows, (float*)a.dz_out);
+    }
+    return cudaGetLastError();
+}
+
+// --------------------------------------------------------------- finalize dz ---
+template <typename TZ>
+__global__ void __launch_bounds__(256)
+finalize_dz_kernel(const float* __restrict__ du_rows, const TZ* __restrict__ z_rows,
+                   const float* __restrict__ inv_norm, const float* __restrict__ grad_out,
+                   int64_t rows, int D, TZ* __restrict__ dz_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const float inv = inv_norm[r];
+    const float g = grad_out ? *grad_out : 1.0f;
+    float dot = 0.f;
+    for (int k = lane * 4; k < D; k += 128) {
+        const float4 d = *reinterpret_cast<const float4*>(du_rows + r * D + k);
+        const float4 zz = Elem<TZ>::ld4(z_rows + r * D + k);
+        dot += (d.x * zz.x + d.y * zz.y + d.z * zz.z + d.w * zz.w) * inv;
+    }
+    dot = warp_sum(dot);
+    const float gi = g * inv;
+    for (int k = lane * 4; k < D; k += 128) {
+        const float4 d = *reinterpret_cast<const float4*>(du_rows + r * D + k);
+        const float4 zz = Elem<TZ>::ld4(z_rows + r * D + k);
+        float4 o;
+        o.x = gi * (d.x - dot * zz.x * inv);
+        o.y = gi * (d.y - dot * zz.y * inv);
+        o.z = gi * (d.z - dot * zz.z * inv);
+        o.w = gi * (d.w - dot * zz.w * inv);
+        Elem<TZ>::st4(dz_out + r * D + k, o);
+    }
+}
+
+cudaError_t launch_finalize_dz(const float* du_rows, const void* z_rows, bool z_bf16,
+                               const float* inv_norm, const float* grad_out, int64_t rows, int64_t D,
+                               void* dz_out, cudaStream_t stream) {
+    if (rows == 0) return cudaSuccess;
+    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
+    if (z_bf16)
+        finalize_dz_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
+            du_rows, (const __nv_bfloat16*)z_rows, inv_norm, grad_out, rows, (int)D,
+            (__nv_bfloat16*)dz_out);
+    else
+        finalize_dz_kernel<float><<<grid, block, 0, stream>>>(du_rows, (const float*)z_rows, inv_norm,
+                                                            grad_out, rows, (int)D, (float*)dz_out);
+    return cudaGetLastError();
+}
+
+}  // namespace ntxent_b200

@@ -1,0 +1,320 @@
+// simt_kernels.cu -- row normalisation and the fp32-FMA tile kernels.
+//
+// These are the exact-fp32 members of the engine: the path taken for fp32 operands (the
+// north_star's 1e-5 / 1e-4 tolerance case), for embedding widths the tcgen05 tiles do not
+// cover (D not a multiple of 64, or D > 256) and when NTXENT_FLAG_FORCE_SIMT is set.  They
+// share everything around them (normalise -> tile pass -> finalize/epilogue, the split plan,
+// the workspace) with the tcgen05 kernels in tc_kernels.cu.
+//
+// They replace, for this path, the reference's materialised pipeline
+// cublasSgemm -> row_max_kernel -> softmax_kernel -> compute_loss_kernel
+// (src/ntxent_kernel.cu:162-199) and its backward (src/ntxent_kernel.cu:217-236); the
+// [2B,2B] logits/softmax tensors are never formed.
+#include "common.cuh"
+
+namespace ntxent_b200 {
+
+// ------------------------------------------------------------------ normalise ---
+// One warp per row.  u = z / max(|z|, eps), computed as (z/amax) / |z/amax| so that
+// rows scaled by 1e-5 .. 1e5 (python/test.py:64) neither underflow nor overflow.
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ z, int64_t rows,
+                                                        int D, TOut* __restrict__ u,
+                                                        float* __restrict__ inv_norm) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const TIn* zr = z + row * D;
+    float amax = 0.f;
+    for (int k = lane * 4; k < D; k += 128) {
+        float4 v = Elem<TIn>::ld4(zr + k);
+        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+    }
+    amax = warp_max(amax);
+    const float sc = (amax > 0.f && amax < INFINITY) ? 1.0f / amax : 1.0f;
+    float ss = 0.f;
+    for (int k = lane * 4; k < D; k += 128) {
+        float4 v = Elem<TIn>::ld4(zr + k);
+        v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    const float nrm = sqrtf(ss) / sc;  // |z|
+    const float inv = 1.0f / fmaxf(nrm, kNormEps);
+    if (lane == 0 && inv_norm) inv_norm[row] = inv;
+    TOut* ur = u + row * D;
+    for (int k = lane * 4; k < D; k += 128) {
+        float4 v = Elem<TIn>::ld4(zr + k);
+        v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+        Elem<TOut>::st4(ur + k, v);
+    }
+}
+
+cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
+                             bool op_bf16, float* inv_norm, cudaStream_t stream) {
+    if (rows == 0) return cudaSuccess;
+    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
+    if (z_bf16 && op_bf16)
+        normalize_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, stream>>>(
+            (const __nv_bfloat16*)z, rows, (int)D, (__nv_bfloat16*)u_out, inv_norm);
+    else if (z_bf16)
+        normalize_kernel<__nv_bfloat16, float><<<grid, block, 0, stream>>>(
+            (const __nv_bfloat16*)z, rows, (int)D, (float*)u_out, inv_norm);
+    else if (op_bf16)
+        normalize_kernel<float, __nv_bfloat16><<<grid, block, 0, stream>>>(
+            (const float*)z, rows, (int)D, (__nv_bfloat16*)u_out, inv_norm);
+    else
+        normalize_kernel<float, float><<<grid, block, 0, stream>>>((const float*)z, rows, (int)D,
+                                                                  (float*)u_out, inv_norm);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------- 64x64 S tile ---
+constexpr int kTM = 64, kTN = 64, kTK = 16, kPad = 4;
+
+// acc[a][b] = u_{a0+ty*4+a} . u_{b0+tx*4+b} (fp32), rows past M read as zero.
+template <typename T>
+__device__ __forceinline__ void simt_s_tile(const T* __restrict__ U, int64_t M, int D, int64_t a0,
+                                            int64_t b0, float (&acc)[4][4],
+                                            float (*As)[kTM + kPad], float (*Bs)[kTN + kPad]) {
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int lr = tid >> 2, lk = (tid & 3) * 4;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int k0 = 0; k0 < D; k0 += kTK) {
+        float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+        if (k0 + lk < D) {
+            if (a0 + lr < M) va = Elem<T>::ld4(U + (a0 + lr) * D + k0 + lk);
+            if (b0 + lr < M) vb = Elem<T>::ld4(U + (b0 + lr) * D + k0 + lk);
+        }
+        __syncthreads();
+        As[lk + 0][lr] = va.x; As[lk + 1][lr] = va.y; As[lk + 2][lr] = va.z; As[lk + 3][lr] = va.w;
+        Bs[lk + 0][lr] = vb.x; Bs[lk + 1][lr] = vb.y; Bs[lk + 2][lr] = vb.z; Bs[lk + 3][lr] = vb.w;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kTK; ++k) {
+            const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+            const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- forward ---
+// grid (row tiles, column splits).  Each CTA walks its column range and keeps a running
+// base-2 (max, sum) per row; partials go to part_m/part_s[split][row_count].
+template <typename T>
+__global__ void __launch_bounds__(256)
+simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
+                float scale_log2, int64_t cols_per_split, float* __restrict__ part_m,
+                float* __restrict__ part_s, unsigned* __restrict__ counter) {
+    __shared__ __align__(16) float As[kTK][kTM + kPad];
+    __shared__ __align__(16) float Bs[kTK][kTN + kPad];
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *counter = 0u;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int64_t a0 = row_begin + (int64_t)blockIdx.x * kTM;
+    const int64_t b_lo = (int64_t)blockIdx.y * cols_per_split;
+    const int64_t b_hi = min(M, b_lo + cols_per_split);
+    float m[4], s[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) { m[a] = -INFINITY; s[a] = 0.f; }
+    float acc[4][4];
+    for (int64_t b0 = b_lo; b0 < b_hi; b0 += kTN) {
+        simt_s_tile<T>(U, M, D, a0, b0, acc, As, Bs);
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int64_t row = a0 + ty * 4 + a;
+            float t[4], tmax = -INFINITY;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int64_t col = b0 + tx * 4 + b;
+                const bool ok = (col < b_hi) && (col != row);
+                t[b] = ok ? acc[a][b] * scale_log2 : -INFINITY;
+                tmax = fmaxf(tmax, t[b]);
+            }
+            const float mn = fmaxf(m[a], tmax);
+            if (mn != -INFINITY) {
+                float add = 0.f;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) add += exp2f(t[b] - mn);
+                s[a] = s[a] * exp2f(m[a] - mn) + add;
+                m[a] = mn;
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[a], o);
+            const float s2 = __shfl_xor_sync(0xffffffffu, s[a], o);
+            lse2_merge(m[a], s[a], m2, s2);
+        }
+        const int64_t r = (int64_t)blockIdx.x * kTM + ty * 4 + a;
+        if (tx == 0 && r < row_count) {
+            part_m[(int64_t)blockIdx.y * row_count + r] = m[a];
+            part_s[(int64_t)blockIdx.y * row_count + r] = s[a];
+        }
+    }
+}
+
+cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                            int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
+                            float* part_m, float* part_s, unsigned* counter, cudaStream_t stream) {
+    dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit), block(256);
+    const float scale_log2 = kLog2e / tau;
+    if (op_bf16)
+        simt_fwd_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
+            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, scale_log2,
+            plan.cols_per_split, part_m, part_s, counter);
+    else
+        simt_fwd_kernel<float><<<grid, block, 0, stream>>>((const float*)u_all, M, (int)D,
+                                                           row_begin, row_count, scale_log2,
+                                                           plan.cols_per_split, part_m, part_s,
+                                                           counter);
+    return cudaGetLastError();
+}
+
+// --------------------------------------------------------------- backward ---
+// grid (A row tiles, B column splits, D chunks of 128).  Per column tile: recompute S,
+// form the weights W (mode), stage them in shared memory and accumulate W . U_b into a
+// 64 x 128 register tile.  Output: acc[split][a_count][D] raw sums (scaled in the epilogue).
+constexpr int kDC = 128;
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256)
+simt_bwd_kernel(const T* __restrict__ U, const float* __restrict__ lse, int64_t M, int D,
+                int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
+                float scale_log2, int64_t cols_per_split, float* __restrict__ acc_out) {
+    __shared__ __align__(16) float As[kTK][kTM + kPad];
+    __shared__ __align__(16) float Bs[kTK][kTN + kPad];
+    __shared__ float Ws[kTM][kTN + 1];
+    __shared__ __align__(16) float Vs[kTK][kDC + kPad];
+    __shared__ float lcol[kTN];
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int64_t a0 = a_begin + (int64_t)blockIdx.x * kTM;
+    const int64_t a_end = a_begin + a_count;
+    const int64_t b_lo = b_begin + (int64_t)blockIdx.y * cols_per_split;
+    const int64_t b_hi = min(b_begin + b_count, b_lo + cols_per_split);
+    const int dc0 = blockIdx.z * kDC;
+    float lrow[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t row = a0 + ty * 4 + a;
+        lrow[a] = (MODE != kCol && row < a_end) ? lse[row] * kLog2e : 0.f;
+    }
+    float o[4][8];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) o[a][c] = 0.f;
+    float acc[4][4];
+    for (int64_t b0 = b_lo; b0 < b_hi; b0 += kTN) {
+        simt_s_tile<T>(U, M, D, a0, b0, acc, As, Bs);
+        if (MODE != kRow && tid < kTN) lcol[tid] = (b0 + tid < b_hi) ? lse[b0 + tid] * kLog2e : 0.f;
+        __syncthreads();
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int64_t row = a0 + ty * 4 + a;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int64_t col = b0 + tx * 4 + b;
+                const float t = acc[a][b] * scale_log2;
+                float w = 0.f;
+                if (col < b_hi && col != row && row < a_end) {
+                    if (MODE != kCol) w += exp2f(t - lrow[a]);
+                    if (MODE != kRow) w += exp2f(t - lcol[tx * 4 + b]);
+                }
+                Ws[ty * 4 + a][tx * 4 + b] = w;
+            }
+        }
+        for (int j0 = 0; j0 < kTN; j0 += kTK) {
+            // stage U[b0+j0 .. +15][dc0 .. dc0+127]
+            {
+                const int jr = tid >> 4, c = (tid & 15) * 8;
+                const int64_t brow = b0 + j0 + jr;
+                float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+                if (brow < b_hi && dc0 + c < D) {
+                    v0 = Elem<T>::ld4(U + brow * D + dc0 + c);
+                    v1 = Elem<T>::ld4(U + brow * D + dc0 + c + 4);
+                }
+                __syncthreads();  // W stores (first round) / previous Vs reads complete
+                *reinterpret_cast<float4*>(&Vs[jr][c]) = v0;
+                *reinterpret_cast<float4*>(&Vs[jr][c + 4]) = v1;
+                __syncthreads();
+            }
+#pragma unroll
+            for (int j = 0; j < kTK; ++j) {
+                const float4 v0 = *reinterpret_cast<const float4*>(&Vs[j][tx * 4]);
+                const float4 v1 = *reinterpret_cast<const float4*>(&Vs[j][64 + tx * 4]);
+                const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    const float w = Ws[ty * 4 + a][j0 + j];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) o[a][c] = fmaf(w, vv[c], o[a][c]);
+                }
+            }
+        }
+        __syncthreads();  // Ws / lcol reuse by the next column tile
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t r = (int64_t)blockIdx.x * kTM + ty * 4 + a;
+        if (r >= a_count) continue;
+        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D + dc0;
+        if (dc0 + tx * 4 < D)
+            *reinterpret_cast<float4*>(dst + tx * 4) = make_float4(o[a][0], o[a][1], o[a][2], o[a][3]);
+        if (dc0 + 64 + tx * 4 < D)
+            *reinterpret_cast<float4*>(dst + 64 + tx * 4) =
+                make_float4(o[a][4], o[a][5], o[a][6], o[a][7]);
+    }
+}
+
+template <typename T>
+static cudaError_t launch_simt_bwd_t(const T* U, const float* lse, int64_t M, int64_t D,
+                                     int64_t a_begin, int64_t a_count, int64_t b_begin,
+                                     int64_t b_count, float tau, int mode, const SplitPlan& plan,
+                                     float* acc, cudaStream_t stream) {
+    dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit, (unsigned)((D + kDC - 1) / kDC));
+    dim3 block(256);
+    const float sl2 = kLog2e / tau;
+    switch (mode) {
+        case kSym:
+            simt_bwd_kernel<T, kSym><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
+                                                                b_begin, b_count, sl2,
+                                                                plan.cols_per_split, acc);
+            break;
+        case kRow:
+            simt_bwd_kernel<T, kRow><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
+                                                                b_begin, b_count, sl2,
+                                                                plan.cols_per_split, acc);
+            break;
+        default:
+            simt_bwd_kernel<T, kCol><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
+                                                                b_begin, b_count, sl2,
+                                                                plan.cols_per_split, acc);
+            break;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
+                            int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
+                            int64_t b_count, float tau, int mode, const SplitPlan& plan, float* acc,
+                            cudaStream_t stream) {
+    if (op_bf16)
+        return launch_simt_bwd_t<__nv_bfloat16>((const __nv_bfloat16*)u_all, lse_all, M, D, a_begin,
+                                                a_count, b_begin, b_count, tau, mode, plan, acc,
+                                                stream);
+    return launch_simt_bwd_t<float>((const float*)u_all, lse_all, M, D, a_begin, a_count, b_begin,
+                                    b_count, tau, mode, plan, acc, stream);
+}
+
+}  // namespace ntxent_b200

@@ -1,0 +1,90 @@
+"""The reference's operator surface, in Python, over the C-ABI.
+
+Mirrors `forward(z, T, use_mixed_precision=False)` / `backward(z, softmax, grad_out, T,
+use_mixed_precision=False)` / `check_tensor_core_support()` of the reference's pybind module
+(src/binding.cpp:7-10, src/binding_new.cpp:4-21; C++ signatures include/ntxent_kernel.cuh:31-52).
+The C++ twin of this file is csrc/binding.cpp.
+
+Differences a caller of the reference has to know:
+  * z is the stacked [2N, D] batch (the reference duplicates z[B, D] itself,
+    src/ntxent_kernel.cu:161, which is not NT-Xent);
+  * backward's second argument is the forward's saved state: the row log-sum-exp l[M] from
+    `forward_with_state`, never an [M, M] softmax;
+  * `grad_out` is honoured (the reference ignores it, src/ntxent_kernel.cu:205-239);
+  * the second return value of backward is P_{i,pos(i)} as an [M] tensor.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import capi
+
+
+def check_tensor_core_support() -> bool:
+    """True when the current device can run the tcgen05 kernels (sm_100).
+
+    Reference: ntxent::utils::check_tensor_core_support (include/ntxent_kernel.cuh:99-110)."""
+    return bool(capi.lib().ntxent_b200_device_supported())
+
+
+def forward_with_state(z: torch.Tensor, T: float, use_mixed_precision: bool = False):
+    """-> (loss[1], lse[M]).  `lse` is what backward needs."""
+    return capi.forward(z, T, use_mixed_precision)
+
+
+def forward(z: torch.Tensor, T: float, use_mixed_precision: bool = False) -> torch.Tensor:
+    """NT-Xent forward: loss as a [1] fp32 tensor.  Differentiable when z requires grad
+    (tests/test_forward.cpp:29-38 calls loss.backward())."""
+    if z.requires_grad and torch.is_grad_enabled():
+        return _NTXentFunction.apply(z, float(T), bool(use_mixed_precision))
+    return capi.forward(z, T, use_mixed_precision)[0]
+
+
+def backward(z: torch.Tensor, softmax: torch.Tensor, grad_out: torch.Tensor, T: float,
+             use_mixed_precision: bool = False):
+    """NT-Xent backward -> (grad_z[M,D], grad_internal[M]).
+
+    `softmax` is the forward's state l[M] (see module docstring); `grad_out` may be a scalar
+    tensor or any tensor whose first element is the incoming gradient of the loss."""
+    return capi.backward(z, softmax, grad_out, T, use_mixed_precision)
+
+
+class _NTXentFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, T, use_mixed_precision):
+        loss, lse = capi.forward(z.detach(), T, use_mixed_precision)
+        ctx.save_for_backward(z.detach(), lse)
+        ctx.T, ctx.mp = T, use_mixed_precision
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        z, lse = ctx.saved_tensors
+        dz, _ = capi.backward(z, lse, grad_loss, ctx.T, ctx.mp, want_pos_prob=False)
+        return dz, None, None
+
+
+def ntxent_loss(z: torch.Tensor, temperature: float = 0.07,
+                use_mixed_precision: bool = False) -> torch.Tensor:
+    """Scalar (0-dim) differentiable NT-Xent loss of the stacked batch z[2N, D]."""
+    return forward(z, temperature, use_mixed_precision).squeeze(0)
+
+
+class NTXentLoss(torch.nn.Module):
+    """nn.Module face of the op.  With `process_group` set, the batch is
+    row-partitioned across the group (see distributed.py)."""
+
+    def __init__(self, temperature: float = 0.07, use_mixed_precision: bool = False,
+                 process_group=None, backward_mode: str = "symmetric"):
+        super().__init__()
+        self.temperature = float(temperature)
+        self.use_mixed_precision = bool(use_mixed_precision)
+        self.process_group = process_group
+        self.backward_mode = backward_mode
+
+    def forward(self, z: torch.Tensor) -> torch.Tensor:
+        if self.process_group is not None:
+            from .distributed import distributed_ntxent_loss
+            return distributed_ntxent_loss(z, self.temperature, self.use_mixed_precision,
+                                           group=self.process_group, backward_mode=self.backward_mode)
+        return ntxent_loss(z, self.temperature, self.use_mixed_precision)

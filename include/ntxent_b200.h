@@ -1,0 +1,158 @@
+/*
+ * ntxent_b200.h -- C-ABI of the B200-native NT-Xent loss engine.
+ *
+ * This is the drop-in boundary for the reference's NT-Xent hot path
+ * (sanowl/CUDA-NT-Xent-MPI-NCCL-SimCLR).  Plain pointers and sizes only: no
+ * torch types, no C++ types, nothing allocated inside.  Every pointer marked
+ * "device" is CUDA device memory on the CURRENT device; every call is
+ * asynchronous on `stream` and never synchronises the host.
+ *
+ * Conventions
+ *   z        [M, D] row-major, M = 2N stacked views: rows 0..N-1 are view 1,
+ *            rows N..2N-1 view 2; the positive of row i is (i + N) mod M.
+ *            (The reference takes z[B, D] and duplicates it itself,
+ *            src/ntxent_kernel.cu:146-148,161; here the caller stacks.)
+ *   dtype    storage type of z and dz: NTXENT_F32 or NTXENT_BF16.
+ *   operands the similarity contraction runs on bf16 operands with fp32
+ *            accumulation when dtype is BF16 or NTXENT_FLAG_MIXED_PRECISION is
+ *            set (the reference's `use_mixed_precision`, include/ntxent_kernel.cuh:34,51,
+ *            which it never reads); otherwise on fp32 operands.
+ *   return   0 on success; negative NTXENT_ERR_* for argument errors; positive
+ *            values are cudaError_t codes.  Nothing throws.
+ */
+#ifndef NTXENT_B200_H
+#define NTXENT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Same type as cudaStream_t, spelled so that this header needs no CUDA include. */
+typedef struct CUstream_st* ntxent_stream_t;
+
+enum { NTXENT_F32 = 0, NTXENT_BF16 = 1 };
+
+#define NTXENT_FLAG_MIXED_PRECISION 1u /* bf16 operands even for fp32 z                         */
+#define NTXENT_FLAG_FORCE_SIMT      2u /* run the fp32-FMA tile kernels instead of tcgen05      */
+#define NTXENT_FLAG_ONLINE_MAX      4u /* force the running-max logsumexp (default: automatic)  */
+
+#define NTXENT_OK                    0
+#define NTXENT_ERR_INVALID_ARGUMENT (-1)
+#define NTXENT_ERR_UNSUPPORTED_DEVICE (-2)
+#define NTXENT_ERR_WORKSPACE_TOO_SMALL (-3)
+#define NTXENT_ERR_UNSUPPORTED_SHAPE (-4)
+
+/* Backward formulations of the row-partitioned path. */
+enum {
+    NTXENT_BWD_SYMMETRIC = 0, /* dU_I = (G + G^T)_{I,:} U / tau; needs l for ALL rows        */
+    NTXENT_BWD_CONTRACT  = 1  /* row term G_{I,:} U and column term G_{I,:}^T U_I, the latter
+                                 to be reduce-scattered; needs l for rows I only             */
+};
+
+/* Replaces ntxent::utils::check_tensor_core_support (include/ntxent_kernel.cuh:99-110,
+ * exported to Python at src/binding_new.cpp:19).  1 if the current device is sm_100. */
+int ntxent_b200_device_supported(void);
+
+/* Message for a return code of this library (static storage). */
+const char* ntxent_b200_strerror(int code);
+
+/* Library version string, e.g. "ntxent_b200 0.1 (sm_100a)". */
+const char* ntxent_b200_version(void);
+
+/* Bytes of device scratch the single-device entry points below need for an
+ * [M, D] problem.  The reference allocates its temporaries per call through
+ * ATen (src/ntxent_kernel.cu:154-158,217-218); here the caller owns them. */
+size_t ntxent_b200_workspace_bytes(int64_t M, int64_t D, int dtype, unsigned flags);
+
+/* Forward: replaces ntxent::ntxent_forward_cuda (include/ntxent_kernel.cuh:31-35,
+ * src/ntxent_kernel.cu:138-203).  loss_out: device float[1] (mean over the M
+ * rows).  lse_out: device float[M], the row log-sum-exp l_i that backward
+ * consumes in place of the reference's [2B,2B] softmax tensor. */
+int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,
+                        void* workspace, size_t workspace_bytes,
+                        float* loss_out, float* lse_out, ntxent_stream_t stream);
+
+/* Backward: replaces ntxent::ntxent_backward_cuda (include/ntxent_kernel.cuh:46-52,
+ * src/ntxent_kernel.cu:205-239).  lse: device float[M] from forward.
+ * grad_out: device float[1] (NULL means 1).  dz_out: device [M, D] in `dtype`.
+ * pos_prob_out: device float[M] or NULL; receives P_{i,pos(i)}, the small
+ * stand-in for the reference's second return value ("grad_internal",
+ * include/ntxent_kernel.cuh:43). */
+int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
+                         int64_t M, int64_t D, float tau, int dtype, unsigned flags,
+                         void* workspace, size_t workspace_bytes,
+                         void* dz_out, float* pos_prob_out, ntxent_stream_t stream);
+
+/* Forward and backward in one call (one normalisation pass); the benchmark's
+ * timed unit (src/benchmark.cpp:30-39 times the forward only). */
+int ntxent_b200_forward_backward(const void* z, const float* grad_out,
+                                 int64_t M, int64_t D, float tau, int dtype, unsigned flags,
+                                 void* workspace, size_t workspace_bytes,
+                                 float* loss_out, float* lse_out, void* dz_out,
+                                 float* pos_prob_out, ntxent_stream_t stream);
+
+/* ---- Row-partitioned (multi-GPU) building blocks ---------------------------
+ * The reference names NCCL/MPI only as link options (CMakeLists.txt:13-14,
+ * 41-47,115-121) and has no call sites; these are the pieces a data-parallel
+ * caller composes around its collectives (all-gather of U, reduce-scatter of
+ * the column term or all-gather of l).  Rank r owns rows
+ * [row_begin, row_begin + row_count) of the global M.
+ */
+
+/* Size in bytes of one operand element for (dtype, flags): 2 (bf16) or 4 (fp32). */
+int ntxent_b200_operand_size(int dtype, unsigned flags);
+
+/* L2-normalise `rows` rows of z: u_out [rows, D] in the operand type,
+ * inv_norm_out float[rows] = 1 / max(|z_i|, 1e-12). */
+int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
+                          void* u_out, float* inv_norm_out, ntxent_stream_t stream);
+
+/* Scratch bytes for the two calls below. */
+size_t ntxent_b200_rows_workspace_bytes(int64_t M, int64_t D, int64_t row_count,
+                                        int dtype, unsigned flags);
+
+/* Forward for a row block against all M columns of the gathered u_all [M, D]
+ * (operand type).  lse_rows_out float[row_count]; loss_partial_out float[1] =
+ * sum over the block of (l_i - S_{i,pos(i)}) (NOT divided by M). */
+int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D,
+                             int64_t row_begin, int64_t row_count, float tau,
+                             int dtype, unsigned flags, void* workspace, size_t workspace_bytes,
+                             float* lse_rows_out, float* loss_partial_out, ntxent_stream_t stream);
+
+/* Backward for a row block.  lse_all float[M] (CONTRACT mode reads only the
+ * block's entries).  du_rows_out float[row_count, D]: SYMMETRIC -> the complete
+ * dU of the block; CONTRACT -> its row term.  du_cols_out float[M, D]: CONTRACT
+ * only, the block's column term for every global row (sum over ranks, e.g. by
+ * reduce-scatter, then add to the row term); NULL in SYMMETRIC mode. */
+int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                              int64_t row_begin, int64_t row_count, float tau, int mode,
+                              int dtype, unsigned flags, void* workspace, size_t workspace_bytes,
+                              float* du_rows_out, float* du_cols_out, ntxent_stream_t stream);
+
+/* Normalisation Jacobian: dz_i = g (dU_i - (dU_i . u_i) u_i) * inv_norm_i with
+ * u_i = z_i * inv_norm_i.  z_rows, dz_out in `dtype`; g = *grad_out (NULL: 1). */
+int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,
+                            const float* grad_out, int64_t rows, int64_t D, int dtype,
+                            void* dz_out, ntxent_stream_t stream);
+
+/* ---- Measurement aids (the reference times with host clocks around the op,
+ * src/benchmark.cpp:30-39; these give the benchmark per-kernel device times) ----
+ * Between _begin and _end every launch of the two tile kernels (forward pass,
+ * backward pass) is bracketed by CUDA events on its stream.  _end synchronises
+ * on them and returns the summed milliseconds and launch counts.  Not
+ * thread-safe; meant for bench.py only. */
+int ntxent_b200_profile_begin(void);
+int ntxent_b200_profile_end(float* fwd_ms, int* fwd_launches, float* bwd_ms, int* bwd_launches);
+
+/* Which kernel family and how many column splits a call with these arguments
+ * will use (reported by the benchmark next to its numbers). */
+int ntxent_b200_plan_info(int64_t M, int64_t D, int64_t row_count, int dtype, unsigned flags,
+                          int* uses_tcgen05, int* fwd_splits, int* bwd_splits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NTXENT_B200_H */

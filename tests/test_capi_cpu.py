@@ -1,0 +1,90 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/*.h declares,
+sizes workspaces and rejects bad arguments -- no compute (there is no GPU here), and no
+fallback: a CPU tensor must raise."""
+import ctypes
+import glob
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import ROOT
+
+import ntxent_b200
+from ntxent_b200 import capi
+
+
+def _declared_symbols():
+    names = set()
+    for h in glob.glob(os.path.join(ROOT, "include", "*.h")):
+        text = open(h).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names |= set(re.findall(r"\b(ntxent_b200_[a-z_0-9]+)\s*\(", text))
+    return names
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = capi.lib()
+    declared = _declared_symbols()
+    assert len(declared) >= 16
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/ but not exported"
+    assert set(capi.EXPORTS) == declared
+    assert b"sm_100a" in L.ntxent_b200_version()
+
+
+def test_strerror_and_codes():
+    L = capi.lib()
+    assert L.ntxent_b200_strerror(0) == b"ok"
+    for code in (-1, -2, -3, -4):
+        assert len(L.ntxent_b200_strerror(code)) > 5
+    assert b"unknown" in L.ntxent_b200_strerror(-99)
+
+
+def test_workspace_sizing():
+    L = capi.lib()
+    # O(M*D) memory, never O(M^2): the reference's three [M,M] fp32 temporaries would be 12.9 GB here
+    n = L.ntxent_b200_workspace_bytes(32768, 128, capi.BF16, 0)
+    assert 0 < n < 512 * 2**20
+    assert L.ntxent_b200_workspace_bytes(131072, 256, capi.BF16, 0) < 4 * 2**30
+    assert L.ntxent_b200_workspace_bytes(31, 128, capi.F32, 0) == 0      # odd M
+    assert L.ntxent_b200_workspace_bytes(32, 12, capi.F32, 0) == 0       # D % 8 != 0
+    assert L.ntxent_b200_workspace_bytes(32, 128, 7, 0) == 0             # unknown dtype
+    assert L.ntxent_b200_rows_workspace_bytes(4096, 128, 1024, capi.BF16, 0) > 0
+    assert L.ntxent_b200_rows_workspace_bytes(4096, 128, 8192, capi.BF16, 0) == 0
+    assert L.ntxent_b200_operand_size(capi.F32, 0) == 4
+    assert L.ntxent_b200_operand_size(capi.F32, capi.FLAG_MIXED_PRECISION) == 2
+    assert L.ntxent_b200_operand_size(capi.BF16, 0) == 2
+
+
+def test_argument_errors_return_codes_without_touching_the_device():
+    L = capi.lib()
+    null = ctypes.c_void_p(None)
+    one = ctypes.c_void_p(256)  # never dereferenced: argument checks come first
+    assert L.ntxent_b200_forward(null, 64, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
+    assert L.ntxent_b200_forward(one, 63, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
+    assert L.ntxent_b200_forward(one, 64, 128, -1.0, 0, 0, one, 1 << 30, one, one, null) == -1
+    assert L.ntxent_b200_forward(one, 64, 100, 0.5, 0, 0, one, 1 << 30, one, one, null) == -4
+    assert L.ntxent_b200_forward(one, 64, 128, 0.5, 0, 0, one, 16, one, one, null) == -3
+    assert L.ntxent_b200_backward(one, null, null, 64, 128, 0.5, 0, 0, one, 1 << 30, one, null, null) == -1
+    assert L.ntxent_b200_backward_rows(one, one, 64, 128, 0, 32, 0.5, 5, 0, 0, one, 1 << 30, one, null,
+                                       null) == -1  # unknown mode
+    assert L.ntxent_b200_backward_rows(one, one, 64, 128, 0, 32, 0.5, capi.BWD_CONTRACT, 0, 0, one,
+                                       1 << 30, one, null, null) == -1  # contract needs du_cols
+    assert L.ntxent_b200_forward_rows(one, 64, 128, 48, 32, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
+
+
+def test_no_cpu_fallback():
+    z = torch.randn(8, 16)
+    with pytest.raises(capi.NTXentError, match="CUDA"):
+        ntxent_b200.forward(z, 0.5)
+    with pytest.raises(capi.NTXentError, match="CUDA"):
+        ntxent_b200.backward(z, torch.zeros(8), torch.ones(1), 0.5)
+
+
+def test_device_supported_is_false_without_a_gpu():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    assert capi.lib().ntxent_b200_device_supported() == 0
+    assert ntxent_b200.check_tensor_core_support() is False

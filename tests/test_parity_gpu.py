@@ -1,0 +1,259 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI (ntxent_b200.capi -> ctypes ->
+libntxent_b200.so), against the fp64 oracle on the same seeded inputs.
+
+Tolerances are BASELINE.json's north_star: fp32 operands -- loss 1e-5 relative, dz 1e-4
+(max-abs error over the max-abs entry of the oracle's dz); bf16 operands with fp32
+accumulation -- loss 2e-3 relative (dz is not given a bound there; 3e-2 in the same norm is
+used and stated).  Every property the reference's own tests assert is checked as well.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import seeded_z
+
+import ntxent_b200
+from ntxent_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL_F32, DZ_TOL_F32 = 1e-5, 1e-4
+LOSS_RTOL_BF16, DZ_TOL_BF16 = 2e-3, 3e-2
+
+PATHS = {"auto": 0, "simt": capi.FLAG_FORCE_SIMT}
+
+
+def dev(a, dtype=torch.float32):
+    return torch.from_numpy(np.ascontiguousarray(a)).to("cuda").to(dtype)
+
+
+def run_gpu(z_t, tau, flags=0, mp=False, grad_out=None):
+    loss, lse = capi.forward(z_t, tau, mp, flags)
+    g = None if grad_out is None else torch.tensor([grad_out], device="cuda", dtype=torch.float32)
+    dz, pp = capi.backward(z_t, lse, g, tau, mp, flags)
+    torch.cuda.synchronize()
+    return float(loss.item()), lse.double().cpu().numpy(), dz.double().cpu().numpy(), pp.double().cpu().numpy()
+
+
+def dz_err(dz, ref):
+    return np.abs(dz - ref).max() / max(np.abs(ref).max(), 1e-300)
+
+
+# ---------------------------------------------------------------- golden fixtures
+@pytest.mark.parametrize("path", list(PATHS))
+def test_golden_fixtures_fp32(golden, path):
+    for name, c in golden.items():
+        M, D = c["z"].shape
+        if D % 8:
+            continue
+        tau = float(c["tau"])
+        loss, lse, dz, _ = run_gpu(dev(c["z"]), tau, PATHS[path])
+        # the device sees fp32-rounded inputs; compare against the fixture computed from fp64 z
+        assert loss == pytest.approx(float(c["loss"]), rel=LOSS_RTOL_F32, abs=1e-6), name
+        assert dz_err(dz, c["dz"]) <= DZ_TOL_F32, name
+
+
+# ------------------------------------------------------- BASELINE.json configurations
+@pytest.mark.parametrize("path", list(PATHS))
+def test_config_c1_fp32(oracle, path):
+    """configs[0]: N=256 pairs, D=128, tau=0.5, fp32."""
+    z = seeded_z(512, 128)
+    loss, lse, dz, pp = run_gpu(dev(z), 0.5, PATHS[path])
+    rl, rlse, rdz = oracle.forward_backward(z.astype(np.float64), 0.5)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_F32)
+    np.testing.assert_allclose(lse, rlse, rtol=1e-5, atol=1e-5)
+    assert dz_err(dz, rdz) <= DZ_TOL_F32
+    _, rpp = oracle.backward(z.astype(np.float64), rlse, 0.5)
+    np.testing.assert_allclose(pp, rpp, rtol=2e-4)
+
+
+def test_config_c2_bf16(oracle):
+    """configs[1]: 2N=4096, D=128, tau=0.1, bf16 embeddings."""
+    z_t = dev(seeded_z(4096, 128), torch.bfloat16)
+    z64 = z_t.double().cpu().numpy()  # the oracle sees exactly the bf16 values the device has
+    loss, lse, dz, _ = run_gpu(z_t, 0.1)
+    rl, rlse, rdz = oracle.forward_backward(z64, 0.1)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_BF16)
+    assert dz_err(dz, rdz) <= DZ_TOL_BF16
+    # fp32 z with use_mixed_precision=True takes the same bf16-operand path
+    loss2, _, dz2, _ = run_gpu(z_t.float(), 0.1, mp=True)
+    assert loss2 == pytest.approx(rl, rel=LOSS_RTOL_BF16)
+    assert dz_err(dz2, rdz) <= DZ_TOL_BF16
+
+
+def test_config_c3_fp32(oracle):
+    """configs[2]: 2N=8192, D=128, tau=0.5, fp32 tolerance path."""
+    z = seeded_z(8192, 128)
+    loss, lse, dz, _ = run_gpu(dev(z), 0.5)
+    rl, rlse, rdz = oracle.forward_backward(z.astype(np.float64), 0.5)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_F32)
+    assert dz_err(dz, rdz) <= DZ_TOL_F32
+
+
+def test_config_c4_full_size_properties(oracle):
+    """configs[3] at full size (2N=32768, D=128, bf16): properties that need no O(M^2) oracle,
+    plus an oracle check of a row sample (the fp32 row-block form, 256 rows)."""
+    M, D, tau = 32768, 128, 0.1
+    z = seeded_z(M, D)
+    z_t = dev(z, torch.bfloat16)
+    loss, lse, dz, pp = run_gpu(z_t, tau)
+    assert math.isfinite(loss) and 0 < loss < math.log(M)
+    zq = z_t.double().cpu().numpy()
+    # 1. the gradient is orthogonal to every row (normalisation Jacobian)
+    assert np.abs((zq * dz).sum(1)).max() <= 1e-2 * np.abs(dz).max() * np.abs(zq).max()
+    # 2. scale invariance: loss(2z) = loss(z), dz(2z) = dz(z)/2 (power of two: exact in bf16)
+    loss2, _, dz2, _ = run_gpu(z_t * 2, tau)
+    assert loss2 == pytest.approx(loss, rel=1e-6)
+    assert dz_err(dz2 * 2, dz) <= 1e-2
+    # 3. swapping the two views leaves the loss unchanged and permutes the gradient
+    zs = torch.cat([z_t[M // 2:], z_t[:M // 2]])
+    loss3, _, dz3, _ = run_gpu(zs, tau)
+    assert loss3 == pytest.approx(loss, rel=1e-6)
+    assert dz_err(np.concatenate([dz3[M // 2:], dz3[:M // 2]]), dz) <= 1e-2
+    # 4. a row sample against the oracle's fp32 row-block form
+    R = 256
+    rlse, _, _, _ = oracle.rowblock_f32(zq.astype(np.float32), tau, 0, R)
+    np.testing.assert_allclose(lse[:R], rlse, rtol=0, atol=5e-3)
+    # 5. probabilities of the positives are probabilities
+    assert (pp > 0).all() and (pp < 1).all()
+
+
+# ------------------------------------------------------------------------ edge cases
+@pytest.mark.parametrize("path", list(PATHS))
+@pytest.mark.parametrize("M,D,tau", [
+    (2, 8, 0.5), (4, 16, 1.0), (16, 128, 0.07), (34, 64, 0.2), (130, 72, 0.3), (254, 256, 0.07),
+    (256, 512, 0.07), (1000, 64, 0.05), (128, 1024, 0.5),
+])
+def test_small_and_ragged_shapes_fp32(oracle, path, M, D, tau):
+    z = seeded_z(M, D, seed=M * 7 + D)
+    loss, lse, dz, _ = run_gpu(dev(z), tau, PATHS[path], grad_out=-1.75)
+    rl, rlse, rdz = oracle.forward_backward(z.astype(np.float64), tau, grad_out=-1.75)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_F32, abs=1e-6)
+    assert dz_err(dz, rdz) <= DZ_TOL_F32
+
+
+@pytest.mark.parametrize("M,D,tau", [(16, 64, 0.07), (130, 128, 0.1), (1000, 64, 0.2),
+                                      (384, 256, 0.07), (2048, 128, 0.5)])
+def test_small_and_ragged_shapes_bf16(oracle, M, D, tau):
+    z_t = dev(seeded_z(M, D, seed=M + D), torch.bfloat16)
+    loss, lse, dz, _ = run_gpu(z_t, tau)
+    rl, rlse, rdz = oracle.forward_backward(z_t.double().cpu().numpy(), tau)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_BF16, abs=1e-4)
+    assert dz_err(dz, rdz) <= DZ_TOL_BF16
+
+
+@pytest.mark.parametrize("path", list(PATHS))
+def test_numerical_stability_sweep(oracle, path):
+    """python/test.py:57-79: B=128, D=256, normalised z times {1e-5,1,1e5}, T in {0.01,0.07,1}."""
+    z = seeded_z(128, 256, seed=99)
+    z /= np.linalg.norm(z, axis=1, keepdims=True)
+    for scale in (1e-5, 1.0, 1e5):
+        for tau in (0.01, 0.07, 1.0):
+            zz = (z * scale).astype(np.float32)
+            loss, _, dz, _ = run_gpu(dev(zz), tau, PATHS[path])
+            rl, _, rdz = oracle.forward_backward(zz.astype(np.float64), tau)
+            assert math.isfinite(loss) and np.isfinite(dz).all()
+            assert loss == pytest.approx(rl, rel=1e-4, abs=1e-6), (scale, tau)
+            assert dz_err(dz, rdz) <= 5e-4, (scale, tau)
+            # bf16 operands at the same extremes: finite, and close where tau allows
+            lb, _, dzb, _ = run_gpu(dev(zz), tau, PATHS[path], mp=True)
+            assert math.isfinite(lb) and np.isfinite(dzb).all()
+
+
+def test_degenerate_rows():
+    """KAT-3 (all rows identical -> ln(M-1), zero gradient) and all-zero rows (eps guard)."""
+    z = torch.ones(64, 32, device="cuda") * torch.linspace(0.5, 2.0, 32, device="cuda")
+    loss, _, dz, _ = run_gpu(z, 0.3)
+    assert loss == pytest.approx(math.log(63), rel=1e-5)
+    assert np.abs(dz).max() < 1e-6
+    z0 = torch.zeros(16, 32, device="cuda")
+    loss0, _, dz0, _ = run_gpu(z0, 0.5)
+    assert loss0 == pytest.approx(math.log(15), rel=1e-5) and np.isfinite(dz0).all()
+
+
+def test_reference_property_tests():
+    """tests/test_forward.cpp:19-52 and tests/test_backward.cpp:19-49 through the operator surface."""
+    g = torch.Generator(device="cuda").manual_seed(0)
+    for B in (16, 32, 64, 128):
+        z = torch.nn.functional.normalize(torch.randn(B, 128, device="cuda", generator=g))
+        loss = ntxent_b200.forward(z, 0.07)
+        assert loss.shape == (1,) and loss.item() > 0 and not torch.isnan(loss).item()
+    z = torch.nn.functional.normalize(torch.randn(32, 128, device="cuda", generator=g))
+    loss, state = ntxent_b200.forward_with_state(z, 0.07)
+    grad_z, grad_internal = ntxent_b200.backward(z, state, torch.ones_like(state), 0.07)
+    assert not torch.isnan(grad_z).any() and not torch.isnan(grad_internal).any()
+    assert 0.0 < torch.norm(grad_z).item() < 100.0
+    # GradientCheck: autograd through the op
+    zr = torch.randn(32, 128, device="cuda", generator=g).requires_grad_(True)
+    loss = ntxent_b200.forward(torch.nn.functional.normalize(zr), 0.07)
+    loss.backward()
+    assert zr.grad is not None and not torch.isnan(zr.grad).any() and zr.grad.abs().max() > 0
+    assert ntxent_b200.check_tensor_core_support() is True
+    with pytest.raises(capi.NTXentError, match="never formed"):
+        ntxent_b200.backward(z, torch.zeros(32, 32, device="cuda"), torch.ones(1, device="cuda"), 0.07)
+
+
+def test_autograd_matches_torch_reference():
+    """The op under autograd against the same expression in plain PyTorch (fp32)."""
+    torch.manual_seed(3)
+    z = torch.randn(256, 64, device="cuda")
+    za = z.clone().requires_grad_(True)
+    (ntxent_b200.ntxent_loss(za, 0.2) * 3.0).backward()
+    zb = z.clone().requires_grad_(True)
+    u = torch.nn.functional.normalize(zb)
+    s = (u @ u.t() / 0.2).masked_fill(torch.eye(256, dtype=torch.bool, device="cuda"), float("-inf"))
+    tgt = (torch.arange(256, device="cuda") + 128) % 256
+    (torch.nn.functional.cross_entropy(s, tgt) * 3.0).backward()
+    assert (za.grad - zb.grad).abs().max() <= 1e-4 * zb.grad.abs().max()
+
+
+def test_fused_equals_separate_and_is_deterministic():
+    z_t = dev(seeded_z(1024, 128, seed=5), torch.bfloat16)
+    loss, lse = capi.forward(z_t, 0.1)
+    dz, _ = capi.backward(z_t, lse, None, 0.1)
+    for _ in range(2):
+        l2, lse2, dz2 = capi.forward_backward(z_t, 0.1)
+        assert torch.equal(l2, loss) and torch.equal(lse2, lse) and torch.equal(dz2, dz)
+
+
+# ------------------------------------------------- row-partitioned path, emulated ranks
+@pytest.mark.parametrize("op_dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("R", [2, 4, 8])
+def test_row_partition_emulation(oracle, R, op_dtype):
+    """R ranks emulated on one GPU with explicit gather / reduce-scatter
+    buffers; both backward formulations must reproduce the single-device result and the oracle."""
+    M, D, tau = 1024, 128, 0.1
+    z_t = dev(seeded_z(M, D, seed=17), op_dtype)
+    rows = M // R
+    loss1, lse1, dz1 = capi.forward_backward(z_t, tau)
+    # forward: normalise shards, "all-gather", per-rank row blocks
+    shards = [capi.normalize(z_t[r * rows:(r + 1) * rows]) for r in range(R)]
+    u_all = torch.cat([s[0] for s in shards])
+    fw = [capi.forward_rows(u_all, r * rows, rows, tau) for r in range(R)]
+    lse_all = torch.cat([f[0] for f in fw])
+    loss = sum(f[1] for f in fw) / M
+    assert torch.allclose(lse_all, lse1, rtol=0, atol=1e-5)
+    assert loss.item() == pytest.approx(loss1.item(), rel=1e-6)
+    g = torch.tensor([0.5], device="cuda")
+    ref = oracle.forward_backward(z_t.double().cpu().numpy(), tau, grad_out=0.5)[2]
+    tol = DZ_TOL_F32 if op_dtype == torch.float32 else DZ_TOL_BF16
+    # symmetric form: all-gather of l only
+    dz_sym = torch.cat([
+        capi.finalize_dz(capi.backward_rows(u_all, lse_all, r * rows, rows, tau, capi.BWD_SYMMETRIC)[0],
+                         z_t[r * rows:(r + 1) * rows], shards[r][1], g) for r in range(R)])
+    assert dz_err(dz_sym.double().cpu().numpy(), ref) <= tol
+    assert dz_err(dz_sym.double().cpu().numpy(), 0.5 * dz1.double().cpu().numpy()) <= 1e-5 + (0 if op_dtype == torch.float32 else 1e-2)
+    # contract form: row term local, column term reduce-scattered
+    parts = []
+    for r in range(R):
+        lse_local = torch.full_like(lse_all, float("nan"))  # a rank knows only its own l
+        lse_local[r * rows:(r + 1) * rows] = lse_all[r * rows:(r + 1) * rows]
+        parts.append(capi.backward_rows(u_all, lse_local, r * rows, rows, tau, capi.BWD_CONTRACT))
+    col_sum = sum(p[1] for p in parts)  # what the reduce-scatter delivers, before the scatter
+    dz_con = torch.cat([
+        capi.finalize_dz(parts[r][0] + col_sum[r * rows:(r + 1) * rows], z_t[r * rows:(r + 1) * rows],
+                         shards[r][1], g) for r in range(R)])
+    assert torch.isfinite(dz_con).all()
+    assert dz_err(dz_con.double().cpu().numpy(), ref) <= tol
