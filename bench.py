@@ -154,10 +154,14 @@ def cpu_rowblock_tflops(z, tau, seconds, rows_hint=0):
     rows = rows_hint
     if not rows:
         probe = max(16, min(M, 64))
-        t0 = time.perf_counter()
-        O.rowblock_f32(z, tau, 0, probe)
-        dt = max(time.perf_counter() - t0, 1e-6)
-        rows = int(min(M, max(probe, probe * seconds / dt)))
+        for _ in range(3):  # calibrate in growing steps (the first call also spins up the threads)
+            t0 = time.perf_counter()
+            O.rowblock_f32(z, tau, 0, probe)
+            dt = max(time.perf_counter() - t0, 1e-6)
+            if dt > 0.5 or probe >= M:
+                break
+            probe = int(min(M, max(probe * 2, probe * 1.0 / dt)))
+        rows = int(min(M, max(16, probe * seconds / dt)))
         rows = max(16, rows // 16 * 16)
     t0 = time.perf_counter()
     O.rowblock_f32(z, tau, 0, rows)

@@ -99,7 +99,7 @@ def test_config_c4_full_size_properties(oracle):
     z = seeded_z(M, D)
     z_t = dev(z, torch.bfloat16)
     loss, lse, dz, pp = run_gpu(z_t, tau)
-    assert math.isfinite(loss) and 0 < loss < math.log(M)
+    assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0  # i.i.d. rows: loss ~ ln(M) + O(1/tau^2 D)
     zq = z_t.double().cpu().numpy()
     # 1. the gradient is orthogonal to every row (normalisation Jacobian)
     assert np.abs((zq * dz).sum(1)).max() <= 1e-2 * np.abs(dz).max() * np.abs(zq).max()
