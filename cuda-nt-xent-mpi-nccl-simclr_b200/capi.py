@@ -25,7 +25,7 @@ EXPORTS = [
     "ntxent_b200_forward_backward", "ntxent_b200_operand_size", "ntxent_b200_normalize",
     "ntxent_b200_rows_workspace_bytes", "ntxent_b200_forward_rows", "ntxent_b200_backward_rows",
     "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
-    "ntxent_b200_plan_info",
+    "ntxent_b200_plan_info", "ntxent_b200_forward_static",
 ]
 
 _lib = None
@@ -78,6 +78,8 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_profile_end.argtypes = [fp, ip, fp, ip]
     L.ntxent_b200_plan_info.restype = ci
     L.ntxent_b200_plan_info.argtypes = [i64, i64, i64, ci, u32, ip, ip, ip]
+    L.ntxent_b200_forward_static.restype = ci
+    L.ntxent_b200_forward_static.argtypes = [vp, i64, i64, f32, ci, u32, vp, vp, vp]
     _lib = L
     return L
 
@@ -279,3 +281,22 @@ def finalize_dz(du_rows: torch.Tensor, z_rows: torch.Tensor, inv_norm: torch.Ten
                                             _ptr(grad_out), rows, D, _dtype_code(z_rows), _ptr(dz),
                                             _stream()))
     return dz
+
+
+STATIC_SCRATCH_BYTES = 8 << 20
+
+
+def forward_static(z: torch.Tensor, tau: float, use_mixed_precision: bool = False, flags: int = 0):
+    """Forward through ntxent_b200_forward_static: no workspace is passed, the library's built-in
+    scratch array (STATIC_SCRATCH_BYTES per GPU) is used instead.  For callers that cannot
+    allocate; larger problems raise.  -> (loss[1], lse[M])."""
+    _require_cuda(z)
+    z = z.contiguous()
+    M, D = z.shape
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        loss = torch.empty(1, dtype=torch.float32, device=z.device)
+        lse = torch.empty(M, dtype=torch.float32, device=z.device)
+        check(lib().ntxent_b200_forward_static(_ptr(z), M, D, float(tau), _dtype_code(z), fl,
+                                               _ptr(loss), _ptr(lse), _stream()))
+    return loss, lse

@@ -3,6 +3,7 @@
 #include "../../include/ntxent_b200.h"
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -240,6 +241,9 @@ const char* ntxent_b200_strerror(int code) {
             return "workspace smaller than ntxent_b200_*workspace_bytes()";
         case NTXENT_ERR_UNSUPPORTED_SHAPE:
             return "unsupported shape (need 8 <= D <= 1024, D % 8 == 0, M <= 2^24)";
+        case NTXENT_ERR_STATIC_SCRATCH_EXCEEDED:
+            return "problem needs more scratch than the built-in NTXENT_STATIC_SCRATCH_BYTES array "
+                   "of ntxent_b200_forward_static; use ntxent_b200_forward with a caller workspace";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
@@ -433,3 +437,69 @@ int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const floa
 }
 
 }  // extern "C"
+
+// ---- forward for callers that cannot allocate --------------------------------------
+// Everything below is an addition beside the entry points above; it shares their kernels and
+// changes none of their code paths.
+namespace {
+
+// The scratch of the forward pass (normalised operands, 1/|z|, split partials, the loss
+// reduction's counter and per-CTA partials) for ntxent_b200_forward_static.  It is part of
+// the library image: every GPU whose context loads this library holds these bytes until the
+// process exits, whether or not the entry point is ever called.
+static __device__ __align__(256) unsigned char g_static_scratch[NTXENT_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxStaticDevices] = {};
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel
+// can use, so the device address is looked up once per device, with that device current.
+int static_scratch_base(char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxStaticDevices) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+        g_static_ptr[dev] = ptr;
+    }
+    *out = (char*)g_static_ptr[dev];
+    return NTXENT_OK;
+}
+
+// Bytes of the workspace layout that the forward pass touches: everything in front of the
+// backward accumulators.
+size_t forward_scratch_bytes(int64_t M, int64_t D, bool op_bf16, const Plans& p) {
+    char* const probe = reinterpret_cast<char*>(kAlign);  // offsets only, never dereferenced
+    const DeviceWs w = carve_device(probe, M, D, op_bf16, p);
+    return (size_t)(reinterpret_cast<char*>(w.rows.acc_rows) - probe);
+}
+
+}  // namespace
+
+extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, float tau, int dtype,
+                                          unsigned flags, float* loss_out, float* lse_out,
+                                          ntxent_stream_t stream) {
+    if (!z || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags);
+    if (forward_scratch_bytes(M, D, opb, p) > (size_t)NTXENT_STATIC_SCRATCH_BYTES)
+        return NTXENT_ERR_STATIC_SCRATCH_EXCEEDED;
+    char* base = nullptr;
+    rc = static_scratch_base(&base);
+    if (rc != NTXENT_OK) return rc;
+    const DeviceWs w = carve_device(base, M, D, opb, p);
+    // Nothing in the array has to start at zero except the reduction counter, and the tile
+    // kernel launched first resets that itself; every other region is written before it is read,
+    // so whatever the previous call left behind is harmless.
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
+                            1.0f / (float)M, stream);
+}

@@ -44,6 +44,7 @@ enum { NTXENT_F32 = 0, NTXENT_BF16 = 1 };
 #define NTXENT_ERR_UNSUPPORTED_DEVICE (-2)
 #define NTXENT_ERR_WORKSPACE_TOO_SMALL (-3)
 #define NTXENT_ERR_UNSUPPORTED_SHAPE (-4)
+#define NTXENT_ERR_STATIC_SCRATCH_EXCEEDED (-5)
 
 /* Backward formulations of the row-partitioned path. */
 enum {
@@ -137,6 +138,37 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
 int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,
                             const float* grad_out, int64_t rows, int64_t D, int dtype,
                             void* dz_out, ntxent_stream_t stream);
+
+/* Forward pass for callers that are not allowed to allocate device memory.
+ *
+ * This entry point has no counterpart in the reference, which allocates its
+ * temporaries through ATen on every call.  It exists for hosts that hand this
+ * library a stream and buffers but own no allocator of their own and may not
+ * call cudaMalloc: a plugin running inside another framework's memory pool, a
+ * step that is being replayed from a fixed launch list, an embedded or
+ * real-time loop in which allocation is forbidden after start-up.  Such a
+ * caller cannot provide the `workspace` that ntxent_b200_forward asks for.
+ *
+ * Same results as ntxent_b200_forward (same kernels, same order), but the
+ * scratch lives in an array of NTXENT_STATIC_SCRATCH_BYTES that is built into
+ * the library.  The caller still passes z, loss_out and lse_out.
+ *
+ *   - Limit: problems whose forward scratch exceeds NTXENT_STATIC_SCRATCH_BYTES
+ *     (8 MiB: about 2N = 8192 at D = 128 with fp32 operands, twice that with
+ *     bf16) are refused with NTXENT_ERR_STATIC_SCRATCH_EXCEEDED and nothing is
+ *     launched.  Every GPU that loads the library keeps the 8 MiB until exit.
+ *   - The first call on each device looks up the array's device address (one
+ *     cudaGetSymbolAddress with that device current); make that first call
+ *     before starting any stream capture.  No call allocates or frees.
+ *   - All calls on a device share the one array, and it keeps whatever the last
+ *     call wrote.  The pass re-initialises the little it needs zeroed, so
+ *     back-to-back calls on one stream are fine; calls that can run on the GPU
+ *     at the same time (different streams, different host threads) race on it
+ *     and must be serialised by the caller. */
+#define NTXENT_STATIC_SCRATCH_BYTES (8u << 20)
+int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, float tau, int dtype,
+                               unsigned flags, float* loss_out, float* lse_out,
+                               ntxent_stream_t stream);
 
 /* ---- Measurement aids (the reference times with host clocks around the op,
  * src/benchmark.cpp:30-39; these give the benchmark per-kernel device times) ----
