@@ -145,7 +145,7 @@ int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const floa
  * temporaries through ATen on every call.  It exists for hosts that hand this
  * library a stream and buffers but own no allocator of their own and may not
  * call cudaMalloc: a plugin running inside another framework's memory pool, a
- * step that is being replayed from a fixed launch list, an embedded or
+ * service whose device memory was carved up at start-up, an embedded or
  * real-time loop in which allocation is forbidden after start-up.  Such a
  * caller cannot provide the `workspace` that ntxent_b200_forward asks for.
  *

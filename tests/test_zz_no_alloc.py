@@ -1,7 +1,7 @@
 """GPU test of ntxent_b200_forward_static, the forward entry point that allocates nothing.
 
 Some hosts of this library cannot give it a workspace: they run inside someone else's memory
-pool or replay a fixed list of launches, and are not allowed to call cudaMalloc.  For them the
+pool or had all device memory handed out at start-up, and are not allowed to call cudaMalloc.  For them the
 library carries its forward scratch inside itself (8 MiB per GPU).  This file checks, through
 the C-ABI, that the entry point returns what ntxent_b200_forward returns -- on two calls in a
 row with different inputs and shapes, because the built-in array is shared and keeps the
