@@ -103,6 +103,6 @@ def build_binding(force: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    build_library(force="--force" in sys.argv, verbose=True)
+    build_library(force="--force" in sys.argv, verbose="-v" in sys.argv)
     if "--binding" in sys.argv:
         build_binding(force="--force" in sys.argv)

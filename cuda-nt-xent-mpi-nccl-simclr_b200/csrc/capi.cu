@@ -82,11 +82,13 @@ inline bool want_tc(int64_t D, bool op_bf16, unsigned flags) {
 struct Plans {
     SplitPlan fwd, bwd_rows, bwd_cols;
     bool tc;
+    unsigned flags;
 };
 
 // All split decisions in one place so that sizing and launching can never disagree.
 Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned flags) {
     Plans p;
+    p.flags = flags;
     p.tc = want_tc(D, op_bf16, flags);
     const int sms = device_sm_count();
     if (p.tc) {
@@ -168,8 +170,8 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
                      float* loss_out, float loss_scale, cudaStream_t st) {
     g_timer.start(0, st);
     if (p.tc)
-        NTX_TRY(tc_launch_fwd(u_all, M, D, row_begin, row_count, tau, p.fwd, w.part_m, w.part_s,
-                              w.counter, st));
+        NTX_TRY(tc_launch_fwd(u_all, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
+                              w.part_s, w.counter, st));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, w.counter, st));
@@ -182,11 +184,11 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
 
 int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                   int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float tau,
-                  int mode, bool tc, const SplitPlan& plan, float* acc, cudaStream_t st) {
+                  int mode, const Plans& p, const SplitPlan& plan, float* acc, cudaStream_t st) {
     g_timer.start(1, st);
-    if (tc)
+    if (p.tc)
         NTX_TRY(tc_launch_bwd(u_all, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau, mode,
-                              plan, acc, st));
+                              p.flags, plan, acc, st));
     else
         NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
                                 tau, mode, plan, acc, st));
@@ -197,7 +199,7 @@ int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t
 int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_bf16, const float* lse,
                         const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
                         void* dz_out, float* pos_prob_out, cudaStream_t st) {
-    int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p.tc, p.bwd_rows,
+    int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows,
                            w.rows.acc_rows, st);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
@@ -400,7 +402,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     const bool sym = (mode == NTXENT_BWD_SYMMETRIC);
     rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau,
-                       sym ? kSym : kRow, p.tc, p.bwd_rows, w.acc_rows, stream);
+                       sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, stream);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
     e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = u_all; e.op_bf16 = opb;
@@ -410,7 +412,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     e.du_out = du_rows_out;
     NTX_TRY(launch_bwd_epilogue(e, stream));
     if (!sym) {
-        rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p.tc,
+        rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p,
                            p.bwd_cols, w.acc_cols, stream);
         if (rc != NTXENT_OK) return rc;
         BwdEpilogueArgs c{};

@@ -1,13 +1,540 @@
-// tc_kernels.cu -- placeholder until the tcgen05 kernels land (phase B).
+// tc_kernels.cu -- the tcgen05 / TMEM / TMA tile kernels (bf16 operands, fp32 accumulation).
+//
+// Forward  (K1): per CTA one 128-row tile of U against a range of 128-column tiles.
+//   TMA (128B swizzle) stages U tiles in shared memory; one thread issues tcgen05.mma
+//   S = U_a U_b^T into a double-buffered TMEM accumulator; four warps pull S rows out with
+//   tcgen05.ld (one row per thread) and fold them into a base-2 running (max, sum).
+// Backward (K2): same S recompute; the four warps turn S into the weights W (bf16), write
+//   them back over the S columns with tcgen05.st, and a second tcgen05.mma (A = W from TMEM,
+//   B = the same U_b tile read MN-major) accumulates  acc_a += W_ab u_b  in TMEM.
+//
+// These replace the reference's cublasSgemm + row_max/softmax/compute_loss kernels
+// (src/ntxent_kernel.cu:8-134,162-199) and its backward SGEMM (src/ntxent_kernel.cu:217-236).
 #include "tc_kernels.cuh"
+
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+#include "tc_ptx.cuh"
+
 namespace ntxent_b200 {
-bool tc_supported(int64_t, bool) { return false; }
-SplitPlan tc_plan_fwd(int64_t, int64_t, int64_t, int) { return SplitPlan{}; }
-SplitPlan tc_plan_bwd(int64_t, int64_t, int64_t, int64_t, int) { return SplitPlan{}; }
-cudaError_t tc_launch_fwd(const void*, int64_t, int64_t, int64_t, int64_t, float, const SplitPlan&,
-                          float*, float*, unsigned*, cudaStream_t) { return cudaErrorNotSupported; }
-cudaError_t tc_launch_bwd(const void*, const float*, int64_t, int64_t, int64_t, int64_t, int64_t,
-                          int64_t, float, int, const SplitPlan&, float*, cudaStream_t) {
-    return cudaErrorNotSupported;
+using namespace ptx;
+
+namespace {
+
+constexpr int kTile = 128;                  // rows per row tile = columns per column tile
+constexpr int kAtomBytes = kTile * 128;     // one 128B-swizzle atom: [128 rows x 64 bf16]
+constexpr int kThreads = 192;               // warp 0 TMA, warp 1 MMA, warps 2..5 softmax
+constexpr int kSoftmaxThreads = 128;
+constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
+
+template <int D>
+struct Cfg {
+    static_assert(D % 64 == 0 && D >= 64 && D <= 256, "tcgen05 tiles cover D in {64,128,192,256}");
+    static constexpr int kAtoms = D / 64;
+    static constexpr int kTileBytes = kAtoms * kAtomBytes;
+    static constexpr int kKSteps = D / 16;  // MMAs per S tile (K = 16 bf16 each)
+    // forward: two CTAs per SM when the tiles allow it
+    static constexpr int kFwdStages = (D <= 64) ? 3 : 2;
+    static constexpr int kFwdSmem = (1 + kFwdStages) * kTileBytes + 2048;
+    static constexpr int kFwdCtasPerSm = (kFwdSmem <= 112 * 1024) ? 2 : 1;
+    // backward: one CTA per SM (512 TMEM columns)
+    static constexpr int kBwdStages = (D <= 128) ? 4 : 2;
+    static constexpr int kBwdSmem = (1 + kBwdStages) * kTileBytes + 2048 + 2 * kTile * 4;
+};
+
+// K-major operand (rows = M or N index, 64 bf16 = 128 B per row, 8-row groups 1024 B apart).
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
+    // kstep counts 16-element K slices: 4 per swizzle atom, 32 B each inside the 128 B row
+    const uint32_t addr = tile_addr + (kstep >> 2) * kAtomBytes + (kstep & 3) * 32;
+    return smem_desc_sw128(addr, 16, 1024);
 }
+// MN-major view of the same tile (K index = tile row): 16 K rows per MMA = 2048 B; the next
+// 64 N elements live one atom (16 KB) further: LBO = atom stride, SBO = 8-row group stride.
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
+    return smem_desc_sw128(tile_addr + kstep * 2048, kAtomBytes, 1024);
+}
+
+__device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
+    return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
+}
+
+// ------------------------------------------------------------------ forward ---
+template <int D, bool kOnline>
+__global__ void __launch_bounds__(kThreads, Cfg<D>::kFwdCtasPerSm)
+tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
+              int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
+              float* __restrict__ part_m, float* __restrict__ part_s, unsigned* __restrict__ counter) {
+    using C = Cfg<D>;
+    constexpr int NS = C::kFwdStages;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* q_tile = smem;
+    uint8_t* k_tiles = smem + C::kTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (1 + NS) * C::kTileBytes);
+    uint64_t* q_full = bars;
+    uint64_t* k_full = bars + 1;
+    uint64_t* k_empty = k_full + NS;
+    uint64_t* s_full = k_empty + NS;
+    uint64_t* s_empty = s_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *counter = 0u;
+
+    const int64_t a0 = row_begin + (int64_t)blockIdx.x * kTile;
+    const int jt0 = blockIdx.y * tiles_per_split;
+    const int n_tiles = min(tiles_per_split, col_tiles - jt0);
+
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmap);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<256>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, C::kTileBytes);
+            for (int a = 0; a < C::kAtoms; ++a)
+                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * 64, (int32_t)a0);
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it % NS;
+                const uint32_t ph = (it / NS) & 1;
+                mbar_wait(&k_empty[st], ph ^ 1);
+                mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
+                for (int a = 0; a < C::kAtoms; ++a)
+                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st], a * 64,
+                                (jt0 + it) * kTile);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16(kTile, kTile, false);
+            const uint32_t q_addr = smem_u32(q_tile);
+            mbar_wait(q_full, 0);
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it % NS, buf = it & 1;
+                mbar_wait(&k_full[st], (it / NS) & 1);
+                mbar_wait(&s_empty[buf], ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+#pragma unroll
+                for (int kk = 0; kk < C::kKSteps; ++kk)
+                    mma_ss_f16(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
+                               idesc, kk > 0);
+                tc_commit(&k_empty[st]);
+                tc_commit(&s_full[buf]);
+            }
+        }
+        __syncwarp();
+    } else {
+        const int quad = warp & 3;  // TMEM lanes 32*quad .. 32*quad+31 belong to this warp
+        const int row_in_tile = quad * 32 + lane;
+        const int64_t row = a0 + row_in_tile;
+        float m_run = kOnline ? -INFINITY : k_scale;
+        float s_run = 0.f;
+        for (int it = 0; it < n_tiles; ++it) {
+            const int buf = it & 1;
+            const int64_t j0 = (int64_t)(jt0 + it) * kTile;
+            const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > M);
+            mbar_wait(&s_full[buf], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * kTile;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c * 32, v);
+                tmem_ld_wait();
+                if (c == 3) {  // the whole S row is in registers: hand the buffer back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_empty[buf]);
+                }
+                if (!kOnline) {
+                    float part = 0.f;
+                    if (!special) {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e)
+                            part += ex2(fmaf(__uint_as_float(v[e]), k_scale, -k_scale));
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            const int64_t col = j0 + c * 32 + e;
+                            const float t = fmaf(__uint_as_float(v[e]), k_scale, -k_scale);
+                            part += (col < M && col != row) ? ex2(t) : 0.f;
+                        }
+                    }
+                    s_run += part;
+                } else {
+                    float t[32], cmax = -INFINITY;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        const int64_t col = j0 + c * 32 + e;
+                        const bool ok = !special || (col < M && col != row);
+                        t[e] = ok ? __uint_as_float(v[e]) * k_scale : -INFINITY;
+                        cmax = fmaxf(cmax, t[e]);
+                    }
+                    const float mn = fmaxf(m_run, cmax);
+                    if (mn != -INFINITY) {
+                        float part = 0.f;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) part += ex2(t[e] - mn);
+                        s_run = s_run * ex2(m_run - mn) + part;
+                        m_run = mn;
+                    }
+                }
+            }
+        }
+        const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
+        if (r < row_count) {
+            part_m[(int64_t)blockIdx.y * row_count + r] = m_run;
+            part_s[(int64_t)blockIdx.y * row_count + r] = s_run;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+// ----------------------------------------------------------------- backward ---
+// MODE: kSym / kRow / kCol (common.cuh).  kTwoExp (kSym only): W = 2^(t-l_a) + 2^(t-l_b) instead
+// of the one-exponential form E (e_a + e_b), E = 2^(t-k), used when 1/tau is too large for it.
+template <int D, int MODE, bool kTwoExp>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ lse, int64_t M,
+              int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale,
+              int tiles_per_split, int col_tiles, float* __restrict__ acc_out) {
+    using C = Cfg<D>;
+    constexpr int NS = C::kBwdStages;
+    constexpr uint32_t kAccCol = 256;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* q_tile = smem;
+    uint8_t* k_tiles = smem + C::kTileBytes;
+    float* colc = reinterpret_cast<float*>(smem + (1 + NS) * C::kTileBytes);  // [2][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(colc + 2 * kTile);
+    uint64_t* q_full = bars;
+    uint64_t* k_full = bars + 1;
+    uint64_t* k_empty = k_full + NS;
+    uint64_t* s_full = k_empty + NS;
+    uint64_t* p_full = s_full + 2;
+    uint64_t* s_free = p_full + 2;
+    uint64_t* acc_full = s_free + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t a0 = a_begin + (int64_t)blockIdx.x * kTile;
+    const int64_t a_end = a_begin + a_count, b_end = b_begin + b_count;
+    const int jt0 = blockIdx.y * tiles_per_split;
+    const int n_tiles = min(tiles_per_split, col_tiles - jt0);
+
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmap);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&s_full[b], 1);
+            mbar_init(&p_full[b], 4);
+            mbar_init(&s_free[b], 1);
+        }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, C::kTileBytes);
+            for (int a = 0; a < C::kAtoms; ++a)
+                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * 64, (int32_t)a0);
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it % NS;
+                mbar_wait(&k_empty[st], ((it / NS) & 1) ^ 1);
+                mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
+                for (int a = 0; a < C::kAtoms; ++a)
+                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st], a * 64,
+                                (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile));
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
+            constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
+            const uint32_t q_addr = smem_u32(q_tile);
+            mbar_wait(q_full, 0);
+            auto issue_s = [&](int it) {
+                const int st = it % NS, buf = it & 1;
+                mbar_wait(&k_full[st], (it / NS) & 1);
+                mbar_wait(&s_free[buf], ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+#pragma unroll
+                for (int kk = 0; kk < C::kKSteps; ++kk)
+                    mma_ss_f16(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
+                               idesc_s, kk > 0);
+                tc_commit(&s_full[buf]);
+            };
+            issue_s(0);
+            for (int it = 0; it < n_tiles; ++it) {
+                if (it + 1 < n_tiles) issue_s(it + 1);
+                const int st = it % NS, buf = it & 1;
+                mbar_wait(&p_full[buf], (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+#pragma unroll
+                for (int kk = 0; kk < kTile / 16; ++kk)
+                    mma_ts_f16(tmem_base + kAccCol, tmem_base + buf * kTile + kk * 8,
+                               desc_mnmajor(k_addr, kk), idesc_pv, (it > 0) || (kk > 0));
+                tc_commit(&k_empty[st]);
+                tc_commit(&s_free[buf]);
+            }
+            tc_commit(acc_full);
+        }
+        __syncwarp();
+    } else {
+        const int quad = warp & 3;
+        const int row_in_tile = quad * 32 + lane;
+        const int st_tid = threadIdx.x - 64;  // 0..127 among the softmax threads
+        const int64_t row = a0 + row_in_tile;
+        const bool row_ok = row < a_end;
+        // per-row constant: l_a in base-2 units, or e_a = 2^(k - l_a) for the one-exponential form
+        float row_c = 0.f;
+        if (MODE != kCol && row_ok) {
+            const float l2 = lse[row] * kLog2e;
+            row_c = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+        } else if (MODE != kCol) {
+            row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range get W = 0
+        }
+        auto col_const = [&](int it) -> float {
+            if (MODE == kRow) return 0.f;
+            const int64_t col = b_begin + (int64_t)(jt0 + it) * kTile + st_tid;
+            if (it >= n_tiles || col >= b_end) return (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
+            const float l2 = lse[col] * kLog2e;
+            return (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+        };
+        float next_colc = col_const(0);
+        for (int it = 0; it < n_tiles; ++it) {
+            const int buf = it & 1;
+            const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
+            const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
+            if (MODE != kRow) {
+                colc[buf * kTile + st_tid] = next_colc;
+                next_colc = col_const(it + 1);  // in flight while this tile is processed
+                named_bar_sync(1, kSoftmaxThreads);
+            }
+            mbar_wait(&s_full[buf], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * kTile;
+            const float* cc = colc + buf * kTile;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c * 32, v);
+                tmem_ld_wait();
+                uint32_t packed[16];
+#pragma unroll
+                for (int e = 0; e < 32; e += 2) {
+                    float w[2];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const float s = __uint_as_float(v[e + h]);
+                        const int ci = c * 32 + e + h;
+                        float x;
+                        if (MODE == kRow) {
+                            x = ex2(fmaf(s, k_scale, -row_c));
+                        } else if (MODE == kCol) {
+                            x = ex2(fmaf(s, k_scale, -cc[ci]));
+                        } else if (kTwoExp) {
+                            x = ex2(fmaf(s, k_scale, -row_c)) + ex2(fmaf(s, k_scale, -cc[ci]));
+                        } else {
+                            x = ex2(fmaf(s, k_scale, -k_scale)) * (row_c + cc[ci]);
+                        }
+                        if (special) {
+                            const int64_t col = j0 + ci;
+                            if (col >= b_end || col == row) x = 0.f;
+                        }
+                        w[h] = x;
+                    }
+                    packed[e >> 1] = pack_bf16(w[0], w[1]);
+                }
+                // W overwrites the S columns already consumed (bf16 pairs: 16 columns per 32 values)
+                tmem_st16(taddr + c * 16, packed);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[buf]);
+        }
+        // epilogue: raw accumulator rows -> acc_out[split][row][D]
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
+        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCol;
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c * 32, v);
+            tmem_ld_wait();
+            if (r < a_count) {
+#pragma unroll
+                for (int e = 0; e < 32; e += 4)
+                    *reinterpret_cast<float4*>(dst + c * 32 + e) =
+                        make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
+                                    __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// --------------------------------------------------------------------- host ---
+PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &p, 12000, cudaEnableDefault, &q) ==
+                cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    });
+    return fn;
+}
+
+// [M, D] bf16 row-major, box = [128 rows x 64 columns], 128-byte swizzle, zero fill past the edge.
+cudaError_t make_tmap(const void* u_all, int64_t M, int64_t D, CUtensorMap* out) {
+    auto fn = encode_fn();
+    if (!fn) return cudaErrorNotSupported;
+    cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)M};
+    cuuint64_t strides[1] = {(cuuint64_t)D * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)kTile};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(u_all), dims, strides, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+template <int D, bool kOnline>
+cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
+                         float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
+                         float* part_s, unsigned* counter, cudaStream_t stream) {
+    using C = Cfg<D>;
+    // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
+    const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
+    auto kern = tc_fwd_kernel<D, kOnline>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
+    kern<<<grid, kThreads, smem, stream>>>(tmap, M, row_begin, row_count, k_scale,
+                                          (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s,
+                                          counter);
+    return cudaGetLastError();
+}
+
+template <int D, int MODE, bool kTwoExp>
+cudaError_t launch_bwd_t(const CUtensorMap& tmap, const float* lse, int64_t M, int64_t a_begin,
+                         int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale,
+                         const SplitPlan& plan, int col_tiles, float* acc, cudaStream_t stream) {
+    using C = Cfg<D>;
+    const int smem = max(C::kBwdSmem, 120 * 1024);
+    auto kern = tc_bwd_kernel<D, MODE, kTwoExp>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
+    kern<<<grid, kThreads, smem, stream>>>(tmap, lse, M, a_begin, a_count, b_begin, b_count, k_scale,
+                                          (int)(plan.cols_per_split / kTile), col_tiles, acc);
+    return cudaGetLastError();
+}
+
+template <int D>
+cudaError_t launch_bwd_d(const CUtensorMap& tmap, const float* lse, int64_t M, int64_t a_begin,
+                         int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale, int mode,
+                         bool two_exp, const SplitPlan& plan, int col_tiles, float* acc,
+                         cudaStream_t stream) {
+#define NTX_BWD(MODE, TWO) \
+    launch_bwd_t<D, MODE, TWO>(tmap, lse, M, a_begin, a_count, b_begin, b_count, k_scale, plan, col_tiles, acc, stream)
+    if (mode == kRow) return NTX_BWD(kRow, false);
+    if (mode == kCol) return NTX_BWD(kCol, false);
+    return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
+#undef NTX_BWD
+}
+
+}  // namespace
+
+bool tc_supported(int64_t D, bool op_bf16) {
+    return op_bf16 && (D == 64 || D == 128 || D == 192 || D == 256);
+}
+
+SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, int num_sms) {
+    const int per_sm = (D <= 128) ? 2 : 1;
+    return plan_splits(row_count, M, kTile, kTile, num_sms * per_sm, 32);
+}
+
+SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, int num_sms) {
+    (void)M; (void)D;
+    return plan_splits(a_count, b_count, kTile, kTile, num_sms, 32);
+}
+
+cudaError_t tc_launch_fwd(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+                          int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
+                          float* part_m, float* part_s, unsigned* counter, cudaStream_t stream) {
+    CUtensorMap tmap;
+    cudaError_t e = make_tmap(u_all, M, D, &tmap);
+    if (e != cudaSuccess) return e;
+    const float k_scale = kLog2e / tau;
+    const bool online = (flags & 4u) || k_scale > kFixedMaxLimit;
+    const int col_tiles = (int)((M + kTile - 1) / kTile);
+#define NTX_FWD(DD)                                                                                   \
+    (online ? launch_fwd_t<DD, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
+                                     part_s, counter, stream)                                         \
+            : launch_fwd_t<DD, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
+                                      part_s, counter, stream))
+    switch (D) {
+        case 64: return NTX_FWD(64);
+        case 128: return NTX_FWD(128);
+        case 192: return NTX_FWD(192);
+        case 256: return NTX_FWD(256);
+        default: return cudaErrorNotSupported;
+    }
+#undef NTX_FWD
+}
+
+cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
+                          float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
+                          cudaStream_t stream) {
+    CUtensorMap tmap;
+    cudaError_t e = make_tmap(u_all, M, D, &tmap);
+    if (e != cudaSuccess) return e;
+    const float k_scale = kLog2e / tau;
+    const bool two_exp = (flags & 4u) || k_scale > kFixedMaxLimit;
+    const int col_tiles = (int)((b_count + kTile - 1) / kTile);
+    switch (D) {
+        case 64: return launch_bwd_d<64>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 128: return launch_bwd_d<128>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 192: return launch_bwd_d<192>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 256: return launch_bwd_d<256>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        default: return cudaErrorNotSupported;
+    }
+}
+
 }  // namespace ntxent_b200

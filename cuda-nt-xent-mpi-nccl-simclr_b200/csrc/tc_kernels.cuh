@@ -11,12 +11,12 @@ SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, int num_sms);
 SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, int num_sms);
 
 cudaError_t tc_launch_fwd(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
-                          int64_t row_count, float tau, const SplitPlan& plan, float* part_m,
-                          float* part_s, unsigned* counter, cudaStream_t stream);
+                          int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
+                          float* part_m, float* part_s, unsigned* counter, cudaStream_t stream);
 
 cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
-                          float tau, int mode, const SplitPlan& plan, float* acc,
+                          float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
                           cudaStream_t stream);
 
 }  // namespace ntxent_b200
