@@ -39,9 +39,6 @@ struct Cfg {
     static constexpr int kFwdStages = (D <= 64) ? 3 : 2;
     static constexpr int kFwdSmem = (1 + kFwdStages) * kTileBytes + 2048;
     static constexpr int kFwdCtasPerSm = (kFwdSmem <= 112 * 1024) ? 2 : 1;
-    // backward: one CTA per SM (512 TMEM columns)
-    static constexpr int kBwdStages = (D <= 128) ? 4 : 2;
-    static constexpr int kBwdSmem = (1 + kBwdStages) * kTileBytes + 2048 + 2 * kTile * 4;
 };
 
 // K-major operand (rows = M or N index, 64 bf16 = 128 B per row, 8-row groups 1024 B apart).
@@ -208,19 +205,71 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 // ----------------------------------------------------------------- backward ---
 // MODE: kSym / kRow / kCol (common.cuh).  kTwoExp (kSym only): W = 2^(t-l_a) + 2^(t-l_b) instead
 // of the one-exponential form E (e_a + e_b), E = 2^(t-k), used when 1/tau is too large for it.
+//
+// 320 threads: warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 weight stage.  The weight
+// warps come in two groups of four: warp w works on TMEM lanes 32*(w%4).. (its row) and on
+// columns [64*half, 64*half+64) of every S tile, half = (w-2)/4, so each scheduler always has
+// two of them to interleave.  The row tile U_a never touches shared memory: each thread
+// loads its own row from global memory once and parks it in TMEM as the A operand of
+// S = U_a U_b^T (both MMAs read A from TMEM, B from the one shared-memory copy of U_b).
+//
+// TMEM columns: S/W buffers (kSBufs x 128) | acc (D) | U_a (D/2, bf16 pairs).
+template <int D>
+struct BwdCfg {
+    static constexpr int kSBufs = (D <= 128) ? 2 : 1;
+    static constexpr uint32_t kAccCol = kSBufs * 128;
+    static constexpr uint32_t kQCol = kAccCol + D;
+    static_assert(kQCol + D / 2 <= 512, "TMEM budget");
+    static constexpr int kStages = (D <= 128) ? 4 : 3;
+    static constexpr int kSmem = kStages * Cfg<D>::kTileBytes + 2048 + 2 * kTile * 4;
+    static constexpr int kThreads = 320;
+    static constexpr int kWeightThreads = 256;
+};
+
+template <int MODE, bool kTwoExp, bool kSpecial>
+__device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (&packed)[16],
+                                             const float* __restrict__ cc, float k_scale, float row_c,
+                                             int64_t col0, int64_t row, int64_t b_end) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+        float w[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float s = __uint_as_float(v[e + h]);
+            float x;
+            if (MODE == kRow) {
+                x = ex2(fmaf(s, k_scale, -row_c));
+            } else if (MODE == kCol) {
+                x = ex2(fmaf(s, k_scale, -cc[e + h]));
+            } else if (kTwoExp) {
+                x = ex2(fmaf(s, k_scale, -row_c)) + ex2(fmaf(s, k_scale, -cc[e + h]));
+            } else {
+                x = ex2(fmaf(s, k_scale, -k_scale)) * (row_c + cc[e + h]);
+            }
+            if (kSpecial) {
+                const int64_t col = col0 + e + h;
+                if (col >= b_end || col == row) x = 0.f;
+            }
+            w[h] = x;
+        }
+        packed[e >> 1] = pack_bf16(w[0], w[1]);
+    }
+}
+
 template <int D, int MODE, bool kTwoExp>
-__global__ void __launch_bounds__(kThreads, 1)
-tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ lse, int64_t M,
-              int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale,
-              int tiles_per_split, int col_tiles, float* __restrict__ acc_out) {
+__global__ void __launch_bounds__(BwdCfg<D>::kThreads, 1)
+tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __restrict__ U,
+              const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
+              int64_t b_begin, int64_t b_count, float k_scale, int tiles_per_split, int col_tiles,
+              float* __restrict__ acc_out) {
     using C = Cfg<D>;
-    constexpr int NS = C::kBwdStages;
-    constexpr uint32_t kAccCol = 256;
+    using B = BwdCfg<D>;
+    constexpr int NS = B::kStages;
+    constexpr int NB = B::kSBufs;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
-    uint8_t* q_tile = smem;
-    uint8_t* k_tiles = smem + C::kTileBytes;
-    float* colc = reinterpret_cast<float*>(smem + (1 + NS) * C::kTileBytes);  // [2][128]
+    uint8_t* k_tiles = smem;
+    float* colc = reinterpret_cast<float*>(smem + NS * C::kTileBytes);  // [2][128]
     uint64_t* bars = reinterpret_cast<uint64_t*>(colc + 2 * kTile);
     uint64_t* q_full = bars;
     uint64_t* k_full = bars + 1;
@@ -239,11 +288,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict_
 
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmap);
-        mbar_init(q_full, 1);
+        mbar_init(q_full, 8);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&s_full[b], 1);
-            mbar_init(&p_full[b], 4);
+            mbar_init(&p_full[b], 8);
             mbar_init(&s_free[b], 1);
         }
         mbar_init(acc_full, 1);
@@ -257,9 +306,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict_
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_arrive_expect_tx(q_full, C::kTileBytes);
-            for (int a = 0; a < C::kAtoms; ++a)
-                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * 64, (int32_t)a0);
             for (int it = 0; it < n_tiles; ++it) {
                 const int st = it % NS;
                 mbar_wait(&k_empty[st], ((it / NS) & 1) ^ 1);
@@ -274,30 +320,36 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict_
         if (lane == 0) {
             constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
             constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
-            const uint32_t q_addr = smem_u32(q_tile);
             mbar_wait(q_full, 0);
+            tc_fence_after();
             auto issue_s = [&](int it) {
-                const int st = it % NS, buf = it & 1;
+                const int st = it % NS, buf = it % NB;
                 mbar_wait(&k_full[st], (it / NS) & 1);
-                mbar_wait(&s_free[buf], ((it >> 1) & 1) ^ 1);
+                mbar_wait(&s_free[buf], ((it / NB) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
-                    mma_ss_f16(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
-                               idesc_s, kk > 0);
+                    mma_ts_f16(tmem_base + buf * kTile, tmem_base + B::kQCol + kk * 8,
+                               desc_kmajor(k_addr, kk), idesc_s, kk > 0);
                 tc_commit(&s_full[buf]);
             };
-            issue_s(0);
+            if (NB == 2) issue_s(0);
             for (int it = 0; it < n_tiles; ++it) {
-                if (it + 1 < n_tiles) issue_s(it + 1);
-                const int st = it % NS, buf = it & 1;
-                mbar_wait(&p_full[buf], (it >> 1) & 1);
+                if (NB == 2) {
+                    if (it + 1 < n_tiles) issue_s(it + 1);
+                } else {
+                    issue_s(it);
+                }
+                const int st = it % NS, buf = it % NB;
+                mbar_wait(&p_full[buf], (it / NB) & 1);
                 tc_fence_after();
                 const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
 #pragma unroll
                 for (int kk = 0; kk < kTile / 16; ++kk)
-                    mma_ts_f16(tmem_base + kAccCol, tmem_base + buf * kTile + kk * 8,
+                    // W for K rows [64h, 64h+64) sits at columns [64h, 64h+32) of the buffer
+                    mma_ts_f16(tmem_base + B::kAccCol,
+                               tmem_base + buf * kTile + (kk >> 2) * 64 + (kk & 3) * 8,
                                desc_mnmajor(k_addr, kk), idesc_pv, (it > 0) || (kk > 0));
                 tc_commit(&k_empty[st]);
                 tc_commit(&s_free[buf]);
@@ -307,88 +359,96 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict_
         __syncwarp();
     } else {
         const int quad = warp & 3;
+        const int half = (warp - 2) >> 2;
         const int row_in_tile = quad * 32 + lane;
-        const int st_tid = threadIdx.x - 64;  // 0..127 among the softmax threads
+        const int wt = threadIdx.x - 64;  // 0..255 among the weight threads
         const int64_t row = a0 + row_in_tile;
         const bool row_ok = row < a_end;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+
+        // park this thread's half of its U_a row in TMEM (bf16 pairs, D/4 columns per half)
+        {
+            const uint4* src = reinterpret_cast<const uint4*>(U + row * D + half * (D / 2));
+#pragma unroll
+            for (int g = 0; g < D / 64; ++g) {  // 16 packed columns = 32 bf16 = 4 x uint4 per step
+                uint32_t p[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint4 t = make_uint4(0u, 0u, 0u, 0u);
+                    if (row < M) t = __ldg(src + g * 4 + q);
+                    p[q * 4 + 0] = t.x; p[q * 4 + 1] = t.y; p[q * 4 + 2] = t.z; p[q * 4 + 3] = t.w;
+                }
+                tmem_st16(lane_addr + B::kQCol + half * (D / 4) + g * 16, p);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_full);
+        }
+
         // per-row constant: l_a in base-2 units, or e_a = 2^(k - l_a) for the one-exponential form
         float row_c = 0.f;
-        if (MODE != kCol && row_ok) {
-            const float l2 = lse[row] * kLog2e;
-            row_c = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
-        } else if (MODE != kCol) {
-            row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range get W = 0
+        if (MODE != kCol) {
+            if (row_ok) {
+                const float l2 = lse[row] * kLog2e;
+                row_c = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+            } else {
+                row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
+            }
         }
         auto col_const = [&](int it) -> float {
-            if (MODE == kRow) return 0.f;
-            const int64_t col = b_begin + (int64_t)(jt0 + it) * kTile + st_tid;
+            if (MODE == kRow || wt >= kTile) return 0.f;
+            const int64_t col = b_begin + (int64_t)(jt0 + it) * kTile + wt;
             if (it >= n_tiles || col >= b_end) return (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
             const float l2 = lse[col] * kLog2e;
             return (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
         };
         float next_colc = col_const(0);
         for (int it = 0; it < n_tiles; ++it) {
-            const int buf = it & 1;
+            const int buf = it % NB;
             const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
             const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
             if (MODE != kRow) {
-                colc[buf * kTile + st_tid] = next_colc;
+                if (wt < kTile) colc[(it & 1) * kTile + wt] = next_colc;
                 next_colc = col_const(it + 1);  // in flight while this tile is processed
-                named_bar_sync(1, kSoftmaxThreads);
+                named_bar_sync(1, B::kWeightThreads);
             }
-            mbar_wait(&s_full[buf], (it >> 1) & 1);
+            const float* cc = colc + (it & 1) * kTile + half * 64;
+            mbar_wait(&s_full[buf], (it / NB) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * kTile;
-            const float* cc = colc + buf * kTile;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t v[32];
-                tmem_ld32(taddr + c * 32, v);
-                tmem_ld_wait();
-                uint32_t packed[16];
-#pragma unroll
-                for (int e = 0; e < 32; e += 2) {
-                    float w[2];
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const float s = __uint_as_float(v[e + h]);
-                        const int ci = c * 32 + e + h;
-                        float x;
-                        if (MODE == kRow) {
-                            x = ex2(fmaf(s, k_scale, -row_c));
-                        } else if (MODE == kCol) {
-                            x = ex2(fmaf(s, k_scale, -cc[ci]));
-                        } else if (kTwoExp) {
-                            x = ex2(fmaf(s, k_scale, -row_c)) + ex2(fmaf(s, k_scale, -cc[ci]));
-                        } else {
-                            x = ex2(fmaf(s, k_scale, -k_scale)) * (row_c + cc[ci]);
-                        }
-                        if (special) {
-                            const int64_t col = j0 + ci;
-                            if (col >= b_end || col == row) x = 0.f;
-                        }
-                        w[h] = x;
-                    }
-                    packed[e >> 1] = pack_bf16(w[0], w[1]);
-                }
-                // W overwrites the S columns already consumed (bf16 pairs: 16 columns per 32 values)
-                tmem_st16(taddr + c * 16, packed);
+            const uint32_t taddr = lane_addr + buf * kTile + half * 64;
+            uint32_t v0[32], v1[32];
+            tmem_ld32(taddr, v0);
+            tmem_ld32(taddr + 32, v1);
+            tmem_ld_wait();
+            uint32_t packed[16];
+            if (!special) {
+                weight_chunk<MODE, kTwoExp, false>(v0, packed, cc, k_scale, row_c, 0, 0, 0);
+                tmem_st16(taddr, packed);
+                weight_chunk<MODE, kTwoExp, false>(v1, packed, cc + 32, k_scale, row_c, 0, 0, 0);
+                tmem_st16(taddr + 16, packed);
+            } else {
+                weight_chunk<MODE, kTwoExp, true>(v0, packed, cc, k_scale, row_c, j0 + half * 64, row, b_end);
+                tmem_st16(taddr, packed);
+                weight_chunk<MODE, kTwoExp, true>(v1, packed, cc + 32, k_scale, row_c, j0 + half * 64 + 32,
+                                                  row, b_end);
+                tmem_st16(taddr + 16, packed);
             }
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[buf]);
         }
-        // epilogue: raw accumulator rows -> acc_out[split][row][D]
+        // epilogue: raw accumulator rows -> acc_out[split][row][D]; each half stores D/2 columns
         mbar_wait(acc_full, 0);
         tc_fence_after();
         const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
-        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCol;
-#pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
+        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D + half * (D / 2);
+        const uint32_t aaddr = lane_addr + B::kAccCol + half * (D / 2);
+#pragma unroll 1
+        for (int c = 0; c < D / 64; ++c) {
             uint32_t v[32];
-            tmem_ld32(taddr + c * 32, v);
+            tmem_ld32(aaddr + c * 32, v);
             tmem_ld_wait();
             if (r < a_count) {
 #pragma unroll
@@ -451,27 +511,28 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
 }
 
 template <int D, int MODE, bool kTwoExp>
-cudaError_t launch_bwd_t(const CUtensorMap& tmap, const float* lse, int64_t M, int64_t a_begin,
-                         int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale,
-                         const SplitPlan& plan, int col_tiles, float* acc, cudaStream_t stream) {
-    using C = Cfg<D>;
-    const int smem = max(C::kBwdSmem, 120 * 1024);
+cudaError_t launch_bwd_t(const CUtensorMap& tmap, const void* u_all, const float* lse, int64_t M,
+                         int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
+                         float k_scale, const SplitPlan& plan, int col_tiles, float* acc,
+                         cudaStream_t stream) {
+    const int smem = max(BwdCfg<D>::kSmem, 120 * 1024);
     auto kern = tc_bwd_kernel<D, MODE, kTwoExp>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
-    kern<<<grid, kThreads, smem, stream>>>(tmap, lse, M, a_begin, a_count, b_begin, b_count, k_scale,
-                                          (int)(plan.cols_per_split / kTile), col_tiles, acc);
+    kern<<<grid, BwdCfg<D>::kThreads, smem, stream>>>(tmap, (const __nv_bfloat16*)u_all, lse, M, a_begin,
+                                                     a_count, b_begin, b_count, k_scale,
+                                                     (int)(plan.cols_per_split / kTile), col_tiles, acc);
     return cudaGetLastError();
 }
 
 template <int D>
-cudaError_t launch_bwd_d(const CUtensorMap& tmap, const float* lse, int64_t M, int64_t a_begin,
-                         int64_t a_count, int64_t b_begin, int64_t b_count, float k_scale, int mode,
-                         bool two_exp, const SplitPlan& plan, int col_tiles, float* acc,
-                         cudaStream_t stream) {
+cudaError_t launch_bwd_d(const CUtensorMap& tmap, const void* u_all, const float* lse, int64_t M,
+                         int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
+                         float k_scale, int mode, bool two_exp, const SplitPlan& plan, int col_tiles,
+                         float* acc, cudaStream_t stream) {
 #define NTX_BWD(MODE, TWO) \
-    launch_bwd_t<D, MODE, TWO>(tmap, lse, M, a_begin, a_count, b_begin, b_count, k_scale, plan, col_tiles, acc, stream)
+    launch_bwd_t<D, MODE, TWO>(tmap, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, plan, col_tiles, acc, stream)
     if (mode == kRow) return NTX_BWD(kRow, false);
     if (mode == kCol) return NTX_BWD(kCol, false);
     return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
@@ -529,10 +590,10 @@ cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, in
     const bool two_exp = (flags & 4u) || k_scale > kFixedMaxLimit;
     const int col_tiles = (int)((b_count + kTile - 1) / kTile);
     switch (D) {
-        case 64: return launch_bwd_d<64>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 128: return launch_bwd_d<128>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 192: return launch_bwd_d<192>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 256: return launch_bwd_d<256>(tmap, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 64: return launch_bwd_d<64>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 128: return launch_bwd_d<128>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 192: return launch_bwd_d<192>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 256: return launch_bwd_d<256>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
         default: return cudaErrorNotSupported;
     }
 }
