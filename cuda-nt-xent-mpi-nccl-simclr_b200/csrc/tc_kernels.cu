@@ -25,7 +25,10 @@ namespace {
 
 constexpr int kTile = 128;                  // rows per row tile = columns per column tile
 constexpr int kAtomBytes = kTile * 128;     // one 128B-swizzle atom: [128 rows x 64 bf16]
-constexpr int kThreads = 192;               // warp 0 TMA, warp 1 MMA, warps 2..5 softmax
+constexpr int kThreads = 192;               // warps 0..3 softmax, warp 4 TMA, warp 5 MMA
+// The issuing warps carry the highest warp ids: the scheduler favours higher ids among ready
+// warps, and a starved MMA issuer (a dozen scalar instructions per tcgen05.mma) stalls everything.
+constexpr int kFwdTmaWarp = 4, kFwdMmaWarp = 5;
 constexpr int kSoftmaxThreads = 128;
 constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
 
@@ -55,6 +58,48 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) 
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
     return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
+}
+
+// One 32-column chunk of an S row folded into the running base-2 (max, sum).
+template <bool kOnline>
+__device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special, int64_t col0,
+                                          int64_t row, int64_t M, float k_scale, float& m_run,
+                                          float& s_run) {
+    if (!kOnline) {
+        float p0 = 0.f, p1 = 0.f;
+        if (!special) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 2) {
+                p0 += ex2(fmaf(__uint_as_float(v[e]), k_scale, -k_scale));
+                p1 += ex2(fmaf(__uint_as_float(v[e + 1]), k_scale, -k_scale));
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                const int64_t col = col0 + e;
+                const float t = fmaf(__uint_as_float(v[e]), k_scale, -k_scale);
+                p0 += (col < M && col != row) ? ex2(t) : 0.f;
+            }
+        }
+        s_run += p0 + p1;
+    } else {
+        float t[32], cmax = -INFINITY;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+            const int64_t col = col0 + e;
+            const bool ok = !special || (col < M && col != row);
+            t[e] = ok ? __uint_as_float(v[e]) * k_scale : -INFINITY;
+            cmax = fmaxf(cmax, t[e]);
+        }
+        const float mn = fmaxf(m_run, cmax);
+        if (mn != -INFINITY) {
+            float part = 0.f;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) part += ex2(t[e] - mn);
+            s_run = s_run * ex2(m_run - mn) + part;
+            m_run = mn;
+        }
+    }
 }
 
 // ------------------------------------------------------------------ forward ---
@@ -91,13 +136,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc<256>(tmem_slot);
+    if (warp == kFwdMmaWarp) tmem_alloc<256>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp == kFwdTmaWarp) {
         if (lane == 0) {
             mbar_arrive_expect_tx(q_full, C::kTileBytes);
             for (int a = 0; a < C::kAtoms; ++a)
@@ -113,17 +158,19 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = idesc_bf16(kTile, kTile, false);
-            const uint32_t q_addr = smem_u32(q_tile);
-            mbar_wait(q_full, 0);
-            for (int it = 0; it < n_tiles; ++it) {
-                const int st = it % NS, buf = it & 1;
-                mbar_wait(&k_full[st], (it / NS) & 1);
-                mbar_wait(&s_empty[buf], ((it >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+    } else if (warp == kFwdMmaWarp) {
+        // the whole warp walks the loop (uniform control flow); one elected lane issues
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = idesc_bf16(kTile, kTile, false);
+        const uint32_t q_addr = smem_u32(q_tile);
+        mbar_wait(q_full, 0);
+        for (int it = 0; it < n_tiles; ++it) {
+            const int st = it % NS, buf = it & 1;
+            mbar_wait(&k_full[st], (it / NS) & 1);
+            mbar_wait(&s_empty[buf], ((it >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
                     mma_ss_f16(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
@@ -131,64 +178,45 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 tc_commit(&k_empty[st]);
                 tc_commit(&s_full[buf]);
             }
+            __syncwarp();
         }
-        __syncwarp();
     } else {
         const int quad = warp & 3;  // TMEM lanes 32*quad .. 32*quad+31 belong to this warp
         const int row_in_tile = quad * 32 + lane;
         const int64_t row = a0 + row_in_tile;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
         float m_run = kOnline ? -INFINITY : k_scale;
         float s_run = 0.f;
+        // 32-column chunks, double-buffered in registers: the load of the next chunk (or of the
+        // next tile's first chunk) is in flight while the current one is exponentiated.
+        uint32_t va[32], vb[32];
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        tmem_ld32(lane_addr, va);
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
             const int64_t j0 = (int64_t)(jt0 + it) * kTile;
             const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > M);
-            mbar_wait(&s_full[buf], (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * kTile;
+            const uint32_t taddr = lane_addr + buf * kTile;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                uint32_t v[32];
-                tmem_ld32(taddr + c * 32, v);
+                uint32_t(&cur)[32] = (c & 1) ? vb : va;
+                uint32_t(&nxt)[32] = (c & 1) ? va : vb;
                 tmem_ld_wait();
-                if (c == 3) {  // the whole S row is in registers: hand the buffer back
+                if (c < 3) {
+                    tmem_ld32(taddr + (c + 1) * 32, nxt);
+                } else {
+                    // the whole S row has left TMEM: hand the buffer back, then prefetch
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&s_empty[buf]);
-                }
-                if (!kOnline) {
-                    float part = 0.f;
-                    if (!special) {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e)
-                            part += ex2(fmaf(__uint_as_float(v[e]), k_scale, -k_scale));
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) {
-                            const int64_t col = j0 + c * 32 + e;
-                            const float t = fmaf(__uint_as_float(v[e]), k_scale, -k_scale);
-                            part += (col < M && col != row) ? ex2(t) : 0.f;
-                        }
-                    }
-                    s_run += part;
-                } else {
-                    float t[32], cmax = -INFINITY;
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        const int64_t col = j0 + c * 32 + e;
-                        const bool ok = !special || (col < M && col != row);
-                        t[e] = ok ? __uint_as_float(v[e]) * k_scale : -INFINITY;
-                        cmax = fmaxf(cmax, t[e]);
-                    }
-                    const float mn = fmaxf(m_run, cmax);
-                    if (mn != -INFINITY) {
-                        float part = 0.f;
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) part += ex2(t[e] - mn);
-                        s_run = s_run * ex2(m_run - mn) + part;
-                        m_run = mn;
+                    if (it + 1 < n_tiles) {
+                        mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
+                        tc_fence_after();
+                        tmem_ld32(lane_addr + (buf ^ 1) * kTile, nxt);
                     }
                 }
+                fwd_chunk<kOnline>(cur, special, j0 + c * 32, row, M, k_scale, m_run, s_run);
             }
         }
         const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
@@ -199,31 +227,41 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<256>(tmem_base);
+    if (warp == kFwdMmaWarp) tmem_dealloc<256>(tmem_base);
 }
 
 // ----------------------------------------------------------------- backward ---
 // MODE: kSym / kRow / kCol (common.cuh).  kTwoExp (kSym only): W = 2^(t-l_a) + 2^(t-l_b) instead
 // of the one-exponential form E (e_a + e_b), E = 2^(t-k), used when 1/tau is too large for it.
 //
-// 320 threads: warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 weight stage.  The weight
-// warps come in two groups of four: warp w works on TMEM lanes 32*(w%4).. (its row) and on
-// columns [64*half, 64*half+64) of every S tile, half = (w-2)/4, so each scheduler always has
-// two of them to interleave.  The row tile U_a never touches shared memory: each thread
+// 576 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 MMA issuer.  TMEM reads
+// (tcgen05.ld, ~53 B/clk/SM measured) and MUFU ex2 (16/clk/SM) are the two ceilings of this
+// stage, both near 1100-1250 clk per 128x128 tile, so the stage is spread over sixteen warps:
+// warp w owns TMEM lanes 32*(w%4).. (one row per thread) and columns [32q, 32q+32) of every S
+// tile, q = w/4.  Four warps per scheduler at different phases keep one warp's TMEM load
+// under the others' exponentials without any software pipelining.  The row tile U_a never touches shared memory: each thread
 // loads its own row from global memory once and parks it in TMEM as the A operand of
 // S = U_a U_b^T (both MMAs read A from TMEM, B from the one shared-memory copy of U_b).
 //
-// TMEM columns: S/W buffers (kSBufs x 128) | acc (D) | U_a (D/2, bf16 pairs).
+// TMEM columns: S buffers (kSBufs x 128) | W (64, D <= 128 only) | acc (D) | U_a (D/2, bf16 pairs).
 template <int D>
 struct BwdCfg {
+    // D <= 128: the weights get their own 64 columns, so an S buffer is free again as soon as
+    // the weight warps have read it and S(it+2) never waits for W(it) U_b to finish.  Wider D
+    // leaves no room for that: there W overwrites the S columns it was computed from and the
+    // single S buffer is released by the second MMA.
+    static constexpr bool kSeparateP = (D <= 128);
     static constexpr int kSBufs = (D <= 128) ? 2 : 1;
-    static constexpr uint32_t kAccCol = kSBufs * 128;
+    static constexpr uint32_t kPCol = kSBufs * 128;
+    static constexpr uint32_t kAccCol = kPCol + (kSeparateP ? 64 : 0);
     static constexpr uint32_t kQCol = kAccCol + D;
     static_assert(kQCol + D / 2 <= 512, "TMEM budget");
     static constexpr int kStages = (D <= 128) ? 4 : 3;
-    static constexpr int kSmem = kStages * Cfg<D>::kTileBytes + 2048 + 2 * kTile * 4;
-    static constexpr int kThreads = 320;
-    static constexpr int kWeightThreads = 256;
+    static constexpr int kCcTiles = 32;  // column constants are staged for this many tiles at once
+    static constexpr int kSmem = kStages * Cfg<D>::kTileBytes + 2048 + kCcTiles * kTile * 4;
+    static constexpr int kThreads = 576;  // 16 weight warps, then the TMA warp, then the MMA warp
+    static constexpr int kTmaWarp = 16, kMmaWarp = 17;
+    static constexpr int kWeightThreads = 512;
 };
 
 template <int MODE, bool kTwoExp, bool kSpecial>
@@ -269,8 +307,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* k_tiles = smem;
-    float* colc = reinterpret_cast<float*>(smem + NS * C::kTileBytes);  // [2][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(colc + 2 * kTile);
+    float* colc = reinterpret_cast<float*>(smem + NS * C::kTileBytes);  // [kCcTiles][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(colc + B::kCcTiles * kTile);
     uint64_t* q_full = bars;
     uint64_t* k_full = bars + 1;
     uint64_t* k_empty = k_full + NS;
@@ -278,7 +316,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     uint64_t* p_full = s_full + 2;
     uint64_t* s_free = p_full + 2;
     uint64_t* acc_full = s_free + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+    uint64_t* p_free = acc_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_free + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t a0 = a_begin + (int64_t)blockIdx.x * kTile;
@@ -288,23 +327,25 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
 
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmap);
-        mbar_init(q_full, 8);
+        mbar_init(q_full, 16);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&s_full[b], 1);
-            mbar_init(&p_full[b], 8);
-            mbar_init(&s_free[b], 1);
+            mbar_init(&p_full[b], 16);
+            // released by the weight warps (separate W) or by the second MMA's commit (aliased W)
+            mbar_init(&s_free[b], B::kSeparateP ? 16 : 1);
         }
         mbar_init(acc_full, 1);
+        mbar_init(p_free, 1);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    if (warp == B::kMmaWarp) tmem_alloc<512>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp == B::kTmaWarp) {
         if (lane == 0) {
             for (int it = 0; it < n_tiles; ++it) {
                 const int st = it % NS;
@@ -316,61 +357,71 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
-            constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
-            mbar_wait(q_full, 0);
+    } else if (warp == B::kMmaWarp) {
+        // the whole warp walks the loop (uniform control flow); one elected lane issues
+        const bool leader = elect_one();
+        constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
+        constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
+        mbar_wait(q_full, 0);
+        tc_fence_after();
+        auto issue_s = [&](int it) {
+            const int st = it % NS, buf = it % NB;
+            mbar_wait(&k_full[st], (it / NS) & 1);
+            mbar_wait(&s_free[buf], ((it / NB) & 1) ^ 1);
             tc_fence_after();
-            auto issue_s = [&](int it) {
-                const int st = it % NS, buf = it % NB;
-                mbar_wait(&k_full[st], (it / NS) & 1);
-                mbar_wait(&s_free[buf], ((it / NB) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
                     mma_ts_f16(tmem_base + buf * kTile, tmem_base + B::kQCol + kk * 8,
                                desc_kmajor(k_addr, kk), idesc_s, kk > 0);
                 tc_commit(&s_full[buf]);
-            };
-            if (NB == 2) issue_s(0);
-            for (int it = 0; it < n_tiles; ++it) {
-                if (NB == 2) {
-                    if (it + 1 < n_tiles) issue_s(it + 1);
-                } else {
-                    issue_s(it);
-                }
-                const int st = it % NS, buf = it % NB;
-                mbar_wait(&p_full[buf], (it / NB) & 1);
-                tc_fence_after();
-                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
-#pragma unroll
-                for (int kk = 0; kk < kTile / 16; ++kk)
-                    // W for K rows [64h, 64h+64) sits at columns [64h, 64h+32) of the buffer
-                    mma_ts_f16(tmem_base + B::kAccCol,
-                               tmem_base + buf * kTile + (kk >> 2) * 64 + (kk & 3) * 8,
-                               desc_mnmajor(k_addr, kk), idesc_pv, (it > 0) || (kk > 0));
-                tc_commit(&k_empty[st]);
-                tc_commit(&s_free[buf]);
             }
-            tc_commit(acc_full);
+            __syncwarp();
+        };
+        if (NB == 2) issue_s(0);
+        for (int it = 0; it < n_tiles; ++it) {
+            if (NB == 2) {
+                if (it + 1 < n_tiles) issue_s(it + 1);
+            } else {
+                issue_s(it);
+            }
+            const int st = it % NS, buf = it % NB;
+            const int pb = B::kSeparateP ? 0 : buf;
+            mbar_wait(&p_full[pb], (B::kSeparateP ? it : it / NB) & 1);
+            tc_fence_after();
+            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            if (leader) {
+#pragma unroll
+                for (int kk = 0; kk < kTile / 16; ++kk) {
+                    // W for K rows [32q, 32q+32): separate W -> columns [16q, 16q+16) of the W
+                    // block; aliased W -> columns [32q, 32q+16) of the S buffer
+                    const uint32_t a_col = B::kSeparateP ? B::kPCol + kk * 8
+                                                         : buf * kTile + (kk >> 1) * 32 + (kk & 1) * 8;
+                    mma_ts_f16(tmem_base + B::kAccCol, tmem_base + a_col, desc_mnmajor(k_addr, kk),
+                               idesc_pv, (it > 0) || (kk > 0));
+                }
+                tc_commit(&k_empty[st]);
+                tc_commit(B::kSeparateP ? p_free : &s_free[buf]);
+            }
+            __syncwarp();
         }
+        if (leader) tc_commit(acc_full);
         __syncwarp();
     } else {
         const int quad = warp & 3;
-        const int half = (warp - 2) >> 2;
+        const int quarter = warp >> 2;  // which 32 columns of every S tile
         const int row_in_tile = quad * 32 + lane;
-        const int wt = threadIdx.x - 64;  // 0..255 among the weight threads
+        const int wt = threadIdx.x;  // 0..511: the weight threads come first
         const int64_t row = a0 + row_in_tile;
         const bool row_ok = row < a_end;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
 
-        // park this thread's half of its U_a row in TMEM (bf16 pairs, D/4 columns per half)
+        // park U_a in TMEM (bf16 pairs): 16-column groups of the row dealt round-robin to the
+        // four warps that share this lane quadrant
         {
-            const uint4* src = reinterpret_cast<const uint4*>(U + row * D + half * (D / 2));
-#pragma unroll
-            for (int g = 0; g < D / 64; ++g) {  // 16 packed columns = 32 bf16 = 4 x uint4 per step
+            const uint4* src = reinterpret_cast<const uint4*>(U + row * D);
+            for (int g = quarter; g < D / 32; g += 4) {  // 16 packed columns = 32 bf16 = 4 x uint4
                 uint32_t p[16];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -378,7 +429,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                     if (row < M) t = __ldg(src + g * 4 + q);
                     p[q * 4 + 0] = t.x; p[q * 4 + 1] = t.y; p[q * 4 + 2] = t.z; p[q * 4 + 3] = t.w;
                 }
-                tmem_st16(lane_addr + B::kQCol + half * (D / 4) + g * 16, p);
+                tmem_st16(lane_addr + B::kQCol + g * 16, p);
             }
             tmem_st_wait();
             tc_fence_before();
@@ -396,59 +447,67 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
             }
         }
-        auto col_const = [&](int it) -> float {
-            if (MODE == kRow || wt >= kTile) return 0.f;
-            const int64_t col = b_begin + (int64_t)(jt0 + it) * kTile + wt;
-            if (it >= n_tiles || col >= b_end) return (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
-            const float l2 = lse[col] * kLog2e;
-            return (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+        // column constants (l_b in base-2 units, or e_b), staged kCcTiles tiles at a time
+        auto stage_cc = [&](int it0) {
+            named_bar_sync(1, B::kWeightThreads);  // everyone is done with the previous block
+            const int ncols = min(B::kCcTiles, n_tiles - it0) * kTile;
+            const int64_t c0 = b_begin + (int64_t)(jt0 + it0) * kTile;
+            for (int c = wt; c < ncols; c += B::kWeightThreads) {
+                float val = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
+                if (c0 + c < b_end) {
+                    const float l2 = __ldg(lse + c0 + c) * kLog2e;
+                    val = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+                }
+                colc[c] = val;
+            }
+            named_bar_sync(1, B::kWeightThreads);
         };
-        float next_colc = col_const(0);
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it % NB;
             const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
             const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
-            if (MODE != kRow) {
-                if (wt < kTile) colc[(it & 1) * kTile + wt] = next_colc;
-                next_colc = col_const(it + 1);  // in flight while this tile is processed
-                named_bar_sync(1, B::kWeightThreads);
-            }
-            const float* cc = colc + (it & 1) * kTile + half * 64;
+            if (MODE != kRow && (it % B::kCcTiles) == 0) stage_cc(it);
+            const float* cc = colc + (it % B::kCcTiles) * kTile + quarter * 32;
+            // S columns [32q, 32q+32) of this row; the weights go back as bf16 pairs into
+            // columns [32q, 32q+16) of the same buffer (only this warp ever touches them)
+            const uint32_t taddr = lane_addr + buf * kTile + quarter * 32;
+            uint32_t v[32], packed[16];
             mbar_wait(&s_full[buf], (it / NB) & 1);
             tc_fence_after();
-            const uint32_t taddr = lane_addr + buf * kTile + half * 64;
-            uint32_t v0[32], v1[32];
-            tmem_ld32(taddr, v0);
-            tmem_ld32(taddr + 32, v1);
+            tmem_ld32(taddr, v);
             tmem_ld_wait();
-            uint32_t packed[16];
-            if (!special) {
-                weight_chunk<MODE, kTwoExp, false>(v0, packed, cc, k_scale, row_c, 0, 0, 0);
-                tmem_st16(taddr, packed);
-                weight_chunk<MODE, kTwoExp, false>(v1, packed, cc + 32, k_scale, row_c, 0, 0, 0);
-                tmem_st16(taddr + 16, packed);
+            if (B::kSeparateP) {  // S is in registers: the buffer can take S(it+2) already
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_free[buf]);
+            }
+            if (!special)
+                weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
+            else
+                weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
+                                                  b_end);
+            if (B::kSeparateP) {
+                // one W block: the previous tile's second MMA must have consumed it (it was
+                // issued a whole tile ago, so this wait is normally already satisfied)
+                if (it > 0) mbar_wait(p_free, (it - 1) & 1);
+                tc_fence_after();
+                tmem_st16(lane_addr + B::kPCol + quarter * 16, packed);
             } else {
-                weight_chunk<MODE, kTwoExp, true>(v0, packed, cc, k_scale, row_c, j0 + half * 64, row, b_end);
                 tmem_st16(taddr, packed);
-                weight_chunk<MODE, kTwoExp, true>(v1, packed, cc + 32, k_scale, row_c, j0 + half * 64 + 32,
-                                                  row, b_end);
-                tmem_st16(taddr + 16, packed);
             }
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[buf]);
+            if (lane == 0) mbar_arrive(&p_full[B::kSeparateP ? 0 : buf]);
         }
-        // epilogue: raw accumulator rows -> acc_out[split][row][D]; each half stores D/2 columns
+        // epilogue: raw accumulator rows -> acc_out[split][row][D], 32-column groups round-robin
         mbar_wait(acc_full, 0);
         tc_fence_after();
         const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
-        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D + half * (D / 2);
-        const uint32_t aaddr = lane_addr + B::kAccCol + half * (D / 2);
-#pragma unroll 1
-        for (int c = 0; c < D / 64; ++c) {
+        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D;
+        for (int c = quarter; c < D / 32; c += 4) {
             uint32_t v[32];
-            tmem_ld32(aaddr + c * 32, v);
+            tmem_ld32(lane_addr + B::kAccCol + c * 32, v);
             tmem_ld_wait();
             if (r < a_count) {
 #pragma unroll
@@ -461,7 +520,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<512>(tmem_base);
+    if (warp == B::kMmaWarp) tmem_dealloc<512>(tmem_base);
 }
 
 // --------------------------------------------------------------------- host ---
