@@ -25,7 +25,7 @@ EXPORTS = [
     "ntxent_b200_forward_backward", "ntxent_b200_operand_size", "ntxent_b200_normalize",
     "ntxent_b200_rows_workspace_bytes", "ntxent_b200_forward_rows", "ntxent_b200_backward_rows",
     "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
-    "ntxent_b200_plan_info", "ntxent_b200_forward_static",
+    "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
 ]
 
 _lib = None
@@ -78,6 +78,8 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_profile_end.argtypes = [fp, ip, fp, ip]
     L.ntxent_b200_plan_info.restype = ci
     L.ntxent_b200_plan_info.argtypes = [i64, i64, i64, ci, u32, ip, ip, ip]
+    L.ntxent_b200_debug_set_trace.restype = ci
+    L.ntxent_b200_debug_set_trace.argtypes = [vp]
     L.ntxent_b200_forward_static.restype = ci
     L.ntxent_b200_forward_static.argtypes = [vp, i64, i64, f32, ci, u32, vp, vp, vp]
     _lib = L

@@ -280,6 +280,11 @@ int ntxent_b200_profile_end(float* fwd_ms, int* fwd_launches, float* bwd_ms, int
     return rc;
 }
 
+int ntxent_b200_debug_set_trace(void* dev_buffer) {
+    tc_set_trace_buffer((unsigned long long*)dev_buffer);
+    return NTXENT_OK;
+}
+
 int ntxent_b200_plan_info(int64_t M, int64_t D, int64_t row_count, int dtype, unsigned flags,
                           int* uses_tcgen05, int* fwd_splits, int* bwd_splits) {
     if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK || row_count < 1 || row_count > M)

@@ -294,12 +294,22 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
     }
 }
 
+// Optional pipeline trace (tools/trace_bwd.py): CTA (0,0) stamps clock64() at its hand-offs into
+// trace[role][tile][event]; role 0 = MMA warp, 1 = weight warp 0, 2 = weight warp 15.
+constexpr int kTraceTiles = 64, kTraceEvents = 8;
+unsigned long long* g_trace = nullptr;
+#define NTX_TRACE(role, it, ev)                                                                   \
+    do {                                                                                          \
+        if (trace && blockIdx.x == 0 && blockIdx.y == 0 && (it) < kTraceTiles && lane == 0)       \
+            trace[((role)*kTraceTiles + (it)) * kTraceEvents + (ev)] = clock64();                 \
+    } while (0)
+
 template <int D, int MODE, bool kTwoExp>
 __global__ void __launch_bounds__(BwdCfg<D>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __restrict__ U,
               const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int tiles_per_split, int col_tiles,
-              float* __restrict__ acc_out) {
+              float* __restrict__ acc_out, unsigned long long* __restrict__ trace) {
     using C = Cfg<D>;
     using B = BwdCfg<D>;
     constexpr int NS = B::kStages;
@@ -366,9 +376,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         tc_fence_after();
         auto issue_s = [&](int it) {
             const int st = it % NS, buf = it % NB;
+            NTX_TRACE(0, it, 0);
             mbar_wait(&k_full[st], (it / NS) & 1);
+            NTX_TRACE(0, it, 1);
             mbar_wait(&s_free[buf], ((it / NB) & 1) ^ 1);
             tc_fence_after();
+            NTX_TRACE(0, it, 2);
             const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
@@ -378,18 +391,31 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 tc_commit(&s_full[buf]);
             }
             __syncwarp();
+            NTX_TRACE(0, it, 3);
         };
-        if (NB == 2) issue_s(0);
+        // With two S buffers S runs two tiles ahead of the weights (queue order S(it+2), W(it)U,
+        // S(it+3), ...): it only waits for the weight warps to have read S(it), never for the
+        // second MMA of an earlier tile.
+        if (NB == 2) {
+            issue_s(0);
+            if (n_tiles > 1) issue_s(1);
+        }
         for (int it = 0; it < n_tiles; ++it) {
             if (NB == 2) {
-                if (it + 1 < n_tiles) issue_s(it + 1);
+                if (B::kSeparateP) {
+                    if (it + 2 < n_tiles) issue_s(it + 2);
+                } else if (it >= 1 && it + 1 < n_tiles) {
+                    issue_s(it + 1);  // aliased W: the buffer is only free after W(it-1)U
+                }
             } else {
                 issue_s(it);
             }
             const int st = it % NS, buf = it % NB;
             const int pb = B::kSeparateP ? 0 : buf;
+            NTX_TRACE(0, it, 4);
             mbar_wait(&p_full[pb], (B::kSeparateP ? it : it / NB) & 1);
             tc_fence_after();
+            NTX_TRACE(0, it, 5);
             const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
@@ -405,6 +431,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 tc_commit(B::kSeparateP ? p_free : &s_free[buf]);
             }
             __syncwarp();
+            NTX_TRACE(0, it, 6);
         }
         if (leader) tc_commit(acc_full);
         __syncwarp();
@@ -472,10 +499,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             // columns [32q, 32q+16) of the same buffer (only this warp ever touches them)
             const uint32_t taddr = lane_addr + buf * kTile + quarter * 32;
             uint32_t v[32], packed[16];
+            const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
+            if (trole < 3) NTX_TRACE(trole, it, 0);
             mbar_wait(&s_full[buf], (it / NB) & 1);
             tc_fence_after();
+            if (trole < 3) NTX_TRACE(trole, it, 1);
             tmem_ld32(taddr, v);
             tmem_ld_wait();
+            if (trole < 3) NTX_TRACE(trole, it, 2);
             if (B::kSeparateP) {  // S is in registers: the buffer can take S(it+2) already
                 tc_fence_before();
                 __syncwarp();
@@ -489,8 +520,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             if (B::kSeparateP) {
                 // one W block: the previous tile's second MMA must have consumed it (it was
                 // issued a whole tile ago, so this wait is normally already satisfied)
+                if (trole < 3) NTX_TRACE(trole, it, 3);
                 if (it > 0) mbar_wait(p_free, (it - 1) & 1);
                 tc_fence_after();
+                if (trole < 3) NTX_TRACE(trole, it, 4);
                 tmem_st16(lane_addr + B::kPCol + quarter * 16, packed);
             } else {
                 tmem_st16(taddr, packed);
@@ -499,6 +532,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[B::kSeparateP ? 0 : buf]);
+            if (trole < 3) NTX_TRACE(trole, it, 5);
         }
         // epilogue: raw accumulator rows -> acc_out[split][row][D], 32-column groups round-robin
         mbar_wait(acc_full, 0);
@@ -581,7 +615,8 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const void* u_all, const float
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
     kern<<<grid, BwdCfg<D>::kThreads, smem, stream>>>(tmap, (const __nv_bfloat16*)u_all, lse, M, a_begin,
                                                      a_count, b_begin, b_count, k_scale,
-                                                     (int)(plan.cols_per_split / kTile), col_tiles, acc);
+                                                     (int)(plan.cols_per_split / kTile), col_tiles, acc,
+                                                     g_trace);
     return cudaGetLastError();
 }
 
@@ -599,6 +634,8 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const void* u_all, const float
 }
 
 }  // namespace
+
+void tc_set_trace_buffer(unsigned long long* dev_ptr) { g_trace = dev_ptr; }
 
 bool tc_supported(int64_t D, bool op_bf16) {
     return op_bf16 && (D == 64 || D == 128 || D == 192 || D == 256);

@@ -19,4 +19,8 @@ cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, in
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
                           cudaStream_t stream);
 
+// Debug aid: CTA (0,0) of the backward tile kernel stamps its pipeline hand-offs into this
+// device buffer ([3 roles][64 tiles][8 events] of clock64 values); nullptr turns it off.
+void tc_set_trace_buffer(unsigned long long* dev_ptr);
+
 }  // namespace ntxent_b200

@@ -1,0 +1,28 @@
+"""Prints the pipeline timeline of CTA (0,0) of the tcgen05 backward kernel (clock64 deltas)."""
+import sys, os, ctypes
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import ntxent_b200
+from ntxent_b200 import capi
+M, D, tau = 32768, 128, 0.1
+z = torch.from_numpy(np.random.default_rng(2).standard_normal((M, D)).astype(np.float32)).cuda().to(torch.bfloat16)
+ws = capi.workspace(M, D, z, 0)
+for _ in range(2):
+    capi.forward_backward(z, tau, ws=ws)
+torch.cuda.synchronize()
+trace = torch.zeros(3 * 64 * 8, dtype=torch.int64, device="cuda")
+capi.lib().ntxent_b200_debug_set_trace(ctypes.c_void_p(trace.data_ptr()))
+capi.forward_backward(z, tau, ws=ws)
+torch.cuda.synchronize()
+capi.lib().ntxent_b200_debug_set_trace(None)
+t = trace.cpu().numpy().reshape(3, 64, 8)
+t0 = t[0, 0, 0]
+names = ["MMA", "W0 ", "W15"]
+ev = {0: ["S:start", "kfull", "sfree", "S:issued", "PV:start", "pfull", "PV:issued"],
+      1: ["start", "sfull", "ld", "computed", "pfree", "arrived"], 2: ["start", "sfull", "ld", "computed", "pfree", "arrived"]}
+for it in list(range(0, 6)) + list(range(20, 26)):
+    for r in range(3):
+        vals = [(ev[r][e], int(t[r, it, e] - t0)) for e in range(len(ev[r])) if t[r, it, e]]
+        print(f"tile {it:2d} {names[r]}: " + "  ".join(f"{n}={v}" for n, v in vals))
+per_tile = (t[1, 40, 5] - t[1, 10, 5]) / 30
+print("steady-state clk per tile (W0 arrivals, tiles 10..40):", per_tile)
