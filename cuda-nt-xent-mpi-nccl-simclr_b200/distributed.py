@@ -1,0 +1,173 @@
+"""Row-partitioned (data-parallel) NT-Xent over torch.distributed -- SURVEY.md section 8e.
+
+The reference names MPI/NCCL only as CMake link options (CMakeLists.txt:13-14,41-47,115-121) and
+has no communicator, no collective and no multi-GPU test; this module is the new work that
+BASELINE.json's north_star describes: one process per GPU, rank r owns rows
+[r*M/R, (r+1)*M/R) of the stacked batch.
+
+  forward   K0 normalise the shard -> all-gather U (operand dtype, 1 MiB per rank at 32768x128/8)
+            -> forward tile pass over (own rows x all columns) -> l[own rows], partial loss
+            -> all-gather l (M floats) + all-reduce of the partial loss (one float)
+  backward  symmetric : dU_I = (G + G^T)_{I,:} U / tau from the gathered l; no second collective
+            contract  : row term G_{I,:} U locally, column term G_{I,:}^T U_I for every global row
+                        -> reduce-scatter (sum) -> add (the formulation the north_star words)
+            then the normalisation Jacobian on the shard.
+
+All compute goes through the C-ABI building blocks (capi.normalize / forward_rows /
+backward_rows / finalize_dz).  The compute backend is an object so that the CPU tests can drive
+the orchestration under gloo with a test double; the product default is the CUDA backend and
+there is no CPU implementation behind it.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import capi
+
+
+class CudaBackend:
+    """The only product backend: hand-written sm_100a kernels behind the C-ABI."""
+
+    launches = {"normalize": 1, "forward_rows": 2, "backward_rows_symmetric": 2,
+                "backward_rows_contract": 4, "finalize_dz": 1}
+
+    def __init__(self, flags: int = 0):
+        self.flags = flags
+        capi.lib()  # fail loudly now if the library is missing
+
+    def normalize(self, z_rows):
+        return capi.normalize(z_rows, self.flags)
+
+    def forward_rows(self, u_all, row_begin, row_count, tau, ws=None):
+        return capi.forward_rows(u_all, row_begin, row_count, tau, self.flags, ws)
+
+    def backward_rows(self, u_all, lse_all, row_begin, row_count, tau, mode, ws=None):
+        return capi.backward_rows(u_all, lse_all, row_begin, row_count, tau, mode, self.flags, ws)
+
+    def finalize_dz(self, du_rows, z_rows, inv_norm, grad_out):
+        return capi.finalize_dz(du_rows, z_rows, inv_norm, grad_out)
+
+    def rows_workspace(self, M, D, rows, u_all):
+        return capi.rows_workspace(M, D, rows, u_all, self.flags)
+
+
+def _reduce_scatter_sum(out: torch.Tensor, inp: torch.Tensor, group) -> None:
+    """Sum-reduce-scatter; backends without the primitive (gloo) get all-reduce + slice."""
+    try:
+        dist.reduce_scatter_tensor(out, inp, op=dist.ReduceOp.SUM, group=group)
+    except (RuntimeError, NotImplementedError):
+        dist.all_reduce(inp, op=dist.ReduceOp.SUM, group=group)
+        r = dist.get_rank(group)
+        out.copy_(inp.view(dist.get_world_size(group), -1)[r].view_as(out))
+
+
+class RowPartitionedNTXent:
+    """Fused forward+backward of the global NT-Xent loss from each rank's row shard.
+
+    `forward_backward(z_local)` returns (loss[1] -- the GLOBAL mean loss, identical on every
+    rank --, dz_local -- d loss / d z_local).  Buffers for the collectives are allocated once.
+    """
+
+    def __init__(self, M: int, D: int, tau: float, dtype: torch.dtype, device, group=None,
+                 backward_mode: str = "symmetric", flags: int = 0, backend=None,
+                 use_mixed_precision: bool = False):
+        if backward_mode not in ("symmetric", "contract"):
+            raise ValueError("backward_mode must be 'symmetric' or 'contract'")
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if M % 2 or M % self.world:
+            raise ValueError(f"global batch M={M} must divide evenly over {self.world} ranks")
+        self.M, self.D, self.tau = int(M), int(D), float(tau)
+        self.rows = self.M // self.world
+        self.row_begin = self.rank * self.rows
+        self.mode = backward_mode
+        if use_mixed_precision:
+            flags |= capi.FLAG_MIXED_PRECISION
+        self.backend = backend if backend is not None else CudaBackend(flags)
+        self.device = torch.device(device)
+        op_dtype = torch.bfloat16 if (dtype == torch.bfloat16 or use_mixed_precision) else torch.float32
+        if hasattr(self.backend, "operand_dtype"):  # test doubles may keep wider operands
+            op_dtype = self.backend.operand_dtype(dtype)
+        self.u_all = torch.empty(self.M, self.D, dtype=op_dtype, device=self.device)
+        self.lse_all = torch.empty(self.M, dtype=torch.float32, device=self.device)
+        self.du_col_local = torch.empty(self.rows, self.D, dtype=torch.float32, device=self.device)
+        self.ws = (self.backend.rows_workspace(self.M, self.D, self.rows, self.u_all)
+                   if hasattr(self.backend, "rows_workspace") else None)
+        sym = backward_mode == "symmetric"
+        lc = getattr(self.backend, "launches", None)
+        self.launches_per_step = (lc["normalize"] + lc["forward_rows"] + lc["finalize_dz"] +
+                                  lc["backward_rows_symmetric" if sym else "backward_rows_contract"]
+                                  ) if lc else 0
+
+    # -- forward -------------------------------------------------------------------------
+    def forward(self, z_local: torch.Tensor):
+        """-> (loss[1] global mean, state) ; state feeds backward()."""
+        if tuple(z_local.shape) != (self.rows, self.D):
+            raise ValueError(f"rank {self.rank} expects a [{self.rows}, {self.D}] shard, got {tuple(z_local.shape)}")
+        u_local, inv_norm = self.backend.normalize(z_local)
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.u_all, u_local.contiguous(), group=self.group)
+        else:
+            self.u_all.copy_(u_local)
+        lse_local, loss_partial = self.backend.forward_rows(self.u_all, self.row_begin, self.rows,
+                                                            self.tau, self.ws)
+        loss = loss_partial.clone()
+        if self.world > 1:
+            dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
+            if self.mode == "symmetric":
+                dist.all_gather_into_tensor(self.lse_all, lse_local.contiguous(), group=self.group)
+            else:  # contract: a rank only ever needs its own l
+                self.lse_all[self.row_begin:self.row_begin + self.rows].copy_(lse_local)
+        else:
+            self.lse_all.copy_(lse_local)
+        loss = loss / self.M
+        return loss, (z_local, inv_norm)
+
+    # -- backward ------------------------------------------------------------------------
+    def backward(self, state, grad_out: torch.Tensor | None = None) -> torch.Tensor:
+        z_local, inv_norm = state
+        if self.mode == "symmetric":
+            du_rows, _ = self.backend.backward_rows(self.u_all, self.lse_all, self.row_begin, self.rows,
+                                                    self.tau, capi.BWD_SYMMETRIC, self.ws)
+        else:
+            du_rows, du_cols = self.backend.backward_rows(self.u_all, self.lse_all, self.row_begin,
+                                                          self.rows, self.tau, capi.BWD_CONTRACT, self.ws)
+            if self.world > 1:
+                _reduce_scatter_sum(self.du_col_local, du_cols, self.group)
+                du_rows = du_rows + self.du_col_local
+            else:
+                du_rows = du_rows + du_cols
+        return self.backend.finalize_dz(du_rows, z_local, inv_norm, grad_out)
+
+    def forward_backward(self, z_local: torch.Tensor, grad_out: torch.Tensor | None = None):
+        loss, state = self.forward(z_local)
+        return loss, self.backward(state, grad_out)
+
+
+class _DistributedNTXentFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z_local, engine):
+        loss, state = engine.forward(z_local.detach())
+        ctx.engine, ctx.state = engine, state
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        return ctx.engine.backward(ctx.state, grad_loss), None
+
+
+def distributed_ntxent_loss(z_local: torch.Tensor, temperature: float = 0.07,
+                            use_mixed_precision: bool = False, group=None,
+                            backward_mode: str = "symmetric", engine: RowPartitionedNTXent | None = None):
+    """Differentiable global NT-Xent loss (0-dim) from this rank's [M/R, D] shard.
+
+    The value is the mean over all M global rows (the same on every rank); the gradient that
+    flows to z_local is d(global loss)/d z_local.  Pass a prebuilt `engine` to reuse its buffers."""
+    if engine is None:
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        engine = RowPartitionedNTXent(z_local.shape[0] * world, z_local.shape[1], temperature, z_local.dtype,
+                                      z_local.device, group=group, backward_mode=backward_mode,
+                                      use_mixed_precision=use_mixed_precision)
+    return _DistributedNTXentFunction.apply(z_local, engine).squeeze(0)
