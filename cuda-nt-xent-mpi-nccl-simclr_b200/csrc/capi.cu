@@ -3,6 +3,8 @@
 #include "../../include/ntxent_b200.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -159,10 +161,20 @@ int check_shape(int64_t M, int64_t D, float tau, int dtype) {
     return NTXENT_OK;
 }
 
-#define NTX_TRY(expr)                                  \
-    do {                                               \
-        cudaError_t e__ = (expr);                      \
-        if (e__ != cudaSuccess) return (int)e__;       \
+// NTXENT_DEBUG=1 in the environment names the failing launch on stderr.
+inline bool debug_on() {
+    static const bool on = [] { const char* v = getenv("NTXENT_DEBUG"); return v && v[0] == '1'; }();
+    return on;
+}
+#define NTX_TRY(expr)                                                                         \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            if (debug_on())                                                                   \
+                fprintf(stderr, "[ntxent_b200] %s:%d: %s -> %s\n", __FILE__, __LINE__, #expr, \
+                        cudaGetErrorString(e__));                                             \
+            return (int)e__;                                                                  \
+        }                                                                                     \
     } while (0)
 
 int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,

@@ -14,6 +14,8 @@
 
 #include <cudaTypedefs.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "tc_ptx.cuh"
@@ -580,9 +582,21 @@ cudaError_t make_tmap(const void* u_all, int64_t M, int64_t D, CUtensorMap* out)
     cuuint64_t strides[1] = {(cuuint64_t)D * 2};
     cuuint32_t box[2] = {64, (cuuint32_t)kTile};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(u_all), dims, strides, box,
-                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    auto encode = [&] {
+        return fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(u_all), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    };
+    CUresult r = encode();
+    if (r == CUDA_ERROR_INVALID_CONTEXT) {
+        // a host thread that has not touched the runtime yet (an autograd worker thread, say) has
+        // no driver context bound: let the runtime bind the current device's primary context
+        (void)cudaFree(nullptr);
+        r = encode();
+    }
+    if (r != CUDA_SUCCESS && getenv("NTXENT_DEBUG"))
+        fprintf(stderr, "[ntxent_b200] cuTensorMapEncodeTiled(ptr=%p, M=%lld, D=%lld) -> CUresult %d\n", u_all,
+                (long long)M, (long long)D, (int)r);
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
