@@ -102,7 +102,52 @@ def build_binding(force: bool = False) -> str:
     return BINDING_PATH
 
 
+def _torch_cxx_flags():
+    import torch
+    from torch.utils import cpp_extension
+    inc = []
+    for p in cpp_extension.include_paths("cuda"):
+        inc += ["-isystem", p]
+    inc += ["-isystem", sysconfig.get_paths()["include"]]
+    torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    return inc, torch_lib, abi
+
+
+def build_cpp_tools(force: bool = False):
+    """g++ -> tests/cpp/test_ntxent_ops (the reference's C++ operator tests, re-stated) and
+    csrc/ntxent_benchmark (the C++ benchmark).  Both link ntxent_cuda.so through an rpath."""
+    build_binding()
+    inc, torch_lib, abi = _torch_cxx_flags()
+    pyver = f"python{sys.version_info.major}.{sys.version_info.minor}"
+    pylibdir = sysconfig.get_config_var("LIBDIR")
+    targets = [
+        (os.path.join(REPO_DIR, "tests", "cpp", "test_ntxent_ops"),
+         [os.path.join(REPO_DIR, "tests", "cpp", "test_ntxent_ops.cpp")],
+         [os.path.join(REPO_DIR, "tests", "cpp", "mini_test.hpp")]),
+        (os.path.join(PKG_DIR, "ntxent_benchmark"), [os.path.join(CSRC, "benchmark.cpp")], []),
+    ]
+    built = []
+    for exe, srcs, extra_deps in targets:
+        deps = srcs + extra_deps + [BINDING_PATH, os.path.join(REPO_DIR, "include", "ntxent_kernel.cuh")]
+        if force or _stale(exe, deps):
+            cmd = ["/usr/bin/g++", "-O2", "-std=c++17", f"-D_GLIBCXX_USE_CXX11_ABI={abi}",
+                   "-I", os.path.join(REPO_DIR, "include"), "-I", os.path.join(REPO_DIR, "tests", "cpp"), *inc,
+                   *srcs, "-o", exe, BINDING_PATH, "-L", PKG_DIR, "-lntxent_b200",
+                   "-L", torch_lib, "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_cuda", "-lc10_cuda",
+                   "-ltorch_python", "-L", pylibdir, f"-l{pyver}", "-L", "/usr/local/cuda/lib64", "-lcudart",
+                   f"-Wl,-rpath,{PKG_DIR}", f"-Wl,-rpath,{torch_lib}", f"-Wl,-rpath,{pylibdir}",
+                   "-Wl,--no-as-needed", "-Wl,--allow-shlib-undefined"]
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"build of {exe} failed:\n" + r.stdout[-4000:])
+        built.append(exe)
+    return built
+
+
 if __name__ == "__main__":
     build_library(force="--force" in sys.argv, verbose="-v" in sys.argv)
     if "--binding" in sys.argv:
         build_binding(force="--force" in sys.argv)
+    if "--tools" in sys.argv:
+        print(build_cpp_tools(force="--force" in sys.argv))
