@@ -33,6 +33,14 @@ constexpr int kThreads = 192;               // warps 0..3 softmax, warp 4 TMA, w
 constexpr int kFwdTmaWarp = 4, kFwdMmaWarp = 5;
 constexpr int kSoftmaxThreads = 128;
 constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
+// of every 8 exponentials in the fixed-max paths, this many are evaluated by ex2_poly
+#ifndef NTX_FWD_POLY
+#define NTX_FWD_POLY 3
+#endif
+#ifndef NTX_BWD_POLY
+#define NTX_BWD_POLY 2
+#endif
+constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
 
 template <int D>
 struct Cfg {
@@ -72,8 +80,8 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
         if (!special) {
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
-                p0 += ex2(fmaf(__uint_as_float(v[e]), k_scale, -k_scale));
-                p1 += ex2(fmaf(__uint_as_float(v[e + 1]), k_scale, -k_scale));
+                p0 += ex2_mix<kFwdPoly>(fmaf(__uint_as_float(v[e]), k_scale, -k_scale), e);
+                p1 += ex2_mix<kFwdPoly>(fmaf(__uint_as_float(v[e + 1]), k_scale, -k_scale), e + 1);
             }
         } else {
 #pragma unroll
@@ -236,33 +244,39 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 // MODE: kSym / kRow / kCol (common.cuh).  kTwoExp (kSym only): W = 2^(t-l_a) + 2^(t-l_b) instead
 // of the one-exponential form E (e_a + e_b), E = 2^(t-k), used when 1/tau is too large for it.
 //
-// 576 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 MMA issuer.  TMEM reads
-// (tcgen05.ld, ~53 B/clk/SM measured) and MUFU ex2 (16/clk/SM) are the two ceilings of this
-// stage, both near 1100-1250 clk per 128x128 tile, so the stage is spread over sixteen warps:
+// 608 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 issues S = U_a U_b^T,
+// warp 18 issues acc += W U_b.  Per 128x128
+// tile the weight stage needs 16384 ex2 (MUFU: 16/clk/SM -> 1024 clk) and the tensor pipe 2 x 512
+// clk, so the two must overlap completely and the weight warps must not move in lock-step:
 // warp w owns TMEM lanes 32*(w%4).. (one row per thread) and columns [32q, 32q+32) of every S
-// tile, q = w/4.  Four warps per scheduler at different phases keep one warp's TMEM load
-// under the others' exponentials without any software pipelining.  The row tile U_a never touches shared memory: each thread
-// loads its own row from global memory once and parks it in TMEM as the A operand of
-// S = U_a U_b^T (both MMAs read A from TMEM, B from the one shared-memory copy of U_b).
+// tile, q = w/4 -- four warps per scheduler that drift apart by up to half a tile, so one warp's
+// barrier checks and TMEM traffic hide under the others' exponentials.
 //
-// TMEM columns: S buffers (kSBufs x 128) | W (64, D <= 128 only) | acc (D) | U_a (D/2, bf16 pairs).
+// The row tile U_a never touches shared memory: each thread loads its own row from global
+// memory once and parks it in TMEM as the A operand of S = U_a U_b^T; both MMAs read A from TMEM
+// and B from the one shared-memory copy of U_b (K-major for S, MN-major for W U_b).
+//
+// TMEM columns, D <= 128:  S (128) | W0 (64) | W1 (64) | acc (D) | U_a (D/2)
+//   S is handed back as soon as all weight warps have pulled their columns into registers, so
+//   S(it+1) is computed while tile it is exponentiated; the bf16 weights alternate between two
+//   blocks, so storing W(it) never waits for the second MMA of tile it-1.
+// TMEM columns, D  > 128:  S/W (128, W overwrites the S columns it came from) | acc (D) | U_a (D/2)
+//   no room for separate W blocks: S(it+1) has to wait for the second MMA of tile it.
 template <int D>
 struct BwdCfg {
-    // D <= 128: the weights get their own 64 columns, so an S buffer is free again as soon as
-    // the weight warps have read it and S(it+2) never waits for W(it) U_b to finish.  Wider D
-    // leaves no room for that: there W overwrites the S columns it was computed from and the
-    // single S buffer is released by the second MMA.
     static constexpr bool kSeparateP = (D <= 128);
-    static constexpr int kSBufs = (D <= 128) ? 2 : 1;
-    static constexpr uint32_t kPCol = kSBufs * 128;
-    static constexpr uint32_t kAccCol = kPCol + (kSeparateP ? 64 : 0);
+    static constexpr uint32_t kPCol = 128;
+    static constexpr uint32_t kAccCol = kSeparateP ? 256 : 128;
     static constexpr uint32_t kQCol = kAccCol + D;
     static_assert(kQCol + D / 2 <= 512, "TMEM budget");
     static constexpr int kStages = (D <= 128) ? 4 : 3;
     static constexpr int kCcTiles = 32;  // column constants are staged for this many tiles at once
     static constexpr int kSmem = kStages * Cfg<D>::kTileBytes + 2048 + kCcTiles * kTile * 4;
-    static constexpr int kThreads = 576;  // 16 weight warps, then the TMA warp, then the MMA warp
-    static constexpr int kTmaWarp = 16, kMmaWarp = 17;
+    // 16 weight warps, the TMA warp, then two MMA issuers: tcgen05.mma issue blocks while the
+    // pipe is busy, so one thread issuing both S(it+1) and W(it) U would tie the two hand-off
+    // chains together (S(it+1) could not go out until W(it-1) U had been fed in)
+    static constexpr int kThreads = 608;
+    static constexpr int kTmaWarp = 16, kMmaWarp = 17, kMmaPvWarp = 18;
     static constexpr int kWeightThreads = 512;
 };
 
@@ -284,7 +298,7 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
             } else if (kTwoExp) {
                 x = ex2(fmaf(s, k_scale, -row_c)) + ex2(fmaf(s, k_scale, -cc[e + h]));
             } else {
-                x = ex2(fmaf(s, k_scale, -k_scale)) * (row_c + cc[e + h]);
+                x = ex2_mix<kBwdPoly>(fmaf(s, k_scale, -k_scale), e + h) * (row_c + cc[e + h]);
             }
             if (kSpecial) {
                 const int64_t col = col0 + e + h;
@@ -315,7 +329,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     using C = Cfg<D>;
     using B = BwdCfg<D>;
     constexpr int NS = B::kStages;
-    constexpr int NB = B::kSBufs;
+    constexpr bool SEP = B::kSeparateP;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
     uint8_t* k_tiles = smem;
@@ -324,12 +338,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     uint64_t* q_full = bars;
     uint64_t* k_full = bars + 1;
     uint64_t* k_empty = k_full + NS;
-    uint64_t* s_full = k_empty + NS;
-    uint64_t* p_full = s_full + 2;
-    uint64_t* s_free = p_full + 2;
-    uint64_t* acc_full = s_free + 2;
-    uint64_t* p_free = acc_full + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_free + 1);
+    uint64_t* s_full = k_empty + NS;   // S tile complete (MMA commit)
+    uint64_t* s_free = s_full + 1;     // S buffer reusable: weight warps (SEP) or second MMA (aliased W)
+    uint64_t* p_full = s_free + 1;     // [2] weights stored by all sixteen warps
+    uint64_t* p_free = p_full + 2;     // [2] second MMA has consumed the W block (SEP only)
+    uint64_t* acc_full = p_free + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t a0 = a_begin + (int64_t)blockIdx.x * kTile;
@@ -341,14 +355,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         prefetch_tensormap(&tmap);
         mbar_init(q_full, 16);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&s_full[b], 1);
-            mbar_init(&p_full[b], 16);
-            // released by the weight warps (separate W) or by the second MMA's commit (aliased W)
-            mbar_init(&s_free[b], B::kSeparateP ? 16 : 1);
-        }
+        mbar_init(s_full, 1);
+        mbar_init(s_free, SEP ? 16 : 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], 16); mbar_init(&p_free[b], 1); }
         mbar_init(acc_full, 1);
-        mbar_init(p_free, 1);
         fence_mbar_init();
     }
     if (warp == B::kMmaWarp) tmem_alloc<512>(tmem_slot);
@@ -370,67 +380,54 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         }
         __syncwarp();
     } else if (warp == B::kMmaWarp) {
-        // the whole warp walks the loop (uniform control flow); one elected lane issues
+        // S issuer.  The whole warp walks the loop (uniform control flow); one elected lane issues.
         const bool leader = elect_one();
         constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
-        constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
         mbar_wait(q_full, 0);
         tc_fence_after();
-        auto issue_s = [&](int it) {
-            const int st = it % NS, buf = it % NB;
+        for (int it = 0; it < n_tiles; ++it) {
+            const int st = it % NS;
             NTX_TRACE(0, it, 0);
             mbar_wait(&k_full[st], (it / NS) & 1);
-            NTX_TRACE(0, it, 1);
-            mbar_wait(&s_free[buf], ((it / NB) & 1) ^ 1);
+            // separate W blocks: free once the weight warps have read S(it-1); aliased W: free
+            // once the second MMA of tile it-1 has consumed the weights stored over it
+            mbar_wait(s_free, (it & 1) ^ 1);
             tc_fence_after();
             NTX_TRACE(0, it, 2);
             const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
-                    mma_ts_f16(tmem_base + buf * kTile, tmem_base + B::kQCol + kk * 8,
-                               desc_kmajor(k_addr, kk), idesc_s, kk > 0);
-                tc_commit(&s_full[buf]);
+                    mma_ts_f16(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk), idesc_s,
+                               kk > 0);
+                tc_commit(s_full);
             }
             __syncwarp();
             NTX_TRACE(0, it, 3);
-        };
-        // With two S buffers S runs two tiles ahead of the weights (queue order S(it+2), W(it)U,
-        // S(it+3), ...): it only waits for the weight warps to have read S(it), never for the
-        // second MMA of an earlier tile.
-        if (NB == 2) {
-            issue_s(0);
-            if (n_tiles > 1) issue_s(1);
         }
+    } else if (warp == B::kMmaPvWarp) {
+        // acc += W(it) U_b issuer
+        const bool leader = elect_one();
+        constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
         for (int it = 0; it < n_tiles; ++it) {
-            if (NB == 2) {
-                if (B::kSeparateP) {
-                    if (it + 2 < n_tiles) issue_s(it + 2);
-                } else if (it >= 1 && it + 1 < n_tiles) {
-                    issue_s(it + 1);  // aliased W: the buffer is only free after W(it-1)U
-                }
-            } else {
-                issue_s(it);
-            }
-            const int st = it % NS, buf = it % NB;
-            const int pb = B::kSeparateP ? 0 : buf;
+            const int st = it % NS;
+            const int pb = SEP ? (it & 1) : 0;
             NTX_TRACE(0, it, 4);
-            mbar_wait(&p_full[pb], (B::kSeparateP ? it : it / NB) & 1);
+            mbar_wait(&p_full[pb], (SEP ? (it >> 1) : it) & 1);
             tc_fence_after();
             NTX_TRACE(0, it, 5);
             const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < kTile / 16; ++kk) {
-                    // W for K rows [32q, 32q+32): separate W -> columns [16q, 16q+16) of the W
-                    // block; aliased W -> columns [32q, 32q+16) of the S buffer
-                    const uint32_t a_col = B::kSeparateP ? B::kPCol + kk * 8
-                                                         : buf * kTile + (kk >> 1) * 32 + (kk & 1) * 8;
-                    mma_ts_f16(tmem_base + B::kAccCol, tmem_base + a_col, desc_mnmajor(k_addr, kk),
-                               idesc_pv, (it > 0) || (kk > 0));
+                    // W for K rows [32q, 32q+32): separate -> columns [16q, 16q+16) of block pb;
+                    // aliased -> columns [32q, 32q+16) of the S buffer
+                    const uint32_t a_col = SEP ? B::kPCol + pb * 64 + kk * 8 : (kk >> 1) * 32 + (kk & 1) * 8;
+                    mma_ts_f16(tmem_base + B::kAccCol, tmem_base + a_col, desc_mnmajor(k_addr, kk), idesc_pv,
+                               (it > 0) || (kk > 0));
                 }
                 tc_commit(&k_empty[st]);
-                tc_commit(B::kSeparateP ? p_free : &s_free[buf]);
+                tc_commit(SEP ? &p_free[pb] : s_free);
             }
             __syncwarp();
             NTX_TRACE(0, it, 6);
@@ -445,6 +442,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         const int64_t row = a0 + row_in_tile;
         const bool row_ok = row < a_end;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+        const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
 
         // park U_a in TMEM (bf16 pairs): 16-column groups of the row dealt round-robin to the
         // four warps that share this lane quadrant
@@ -492,49 +490,45 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             named_bar_sync(1, B::kWeightThreads);
         };
         for (int it = 0; it < n_tiles; ++it) {
-            const int buf = it % NB;
+            const int pb = SEP ? (it & 1) : 0;
             const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
             const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
             if (MODE != kRow && (it % B::kCcTiles) == 0) stage_cc(it);
             const float* cc = colc + (it % B::kCcTiles) * kTile + quarter * 32;
-            // S columns [32q, 32q+32) of this row; the weights go back as bf16 pairs into
-            // columns [32q, 32q+16) of the same buffer (only this warp ever touches them)
-            const uint32_t taddr = lane_addr + buf * kTile + quarter * 32;
+            const uint32_t taddr = lane_addr + quarter * 32;  // this warp's 32 S columns
             uint32_t v[32], packed[16];
-            const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
-            if (trole < 3) NTX_TRACE(trole, it, 0);
-            mbar_wait(&s_full[buf], (it / NB) & 1);
+            NTX_TRACE(trole, it, 0);
+            mbar_wait(s_full, it & 1);
             tc_fence_after();
-            if (trole < 3) NTX_TRACE(trole, it, 1);
+            NTX_TRACE(trole, it, 1);
             tmem_ld32(taddr, v);
             tmem_ld_wait();
-            if (trole < 3) NTX_TRACE(trole, it, 2);
-            if (B::kSeparateP) {  // S is in registers: the buffer can take S(it+2) already
+            if (SEP) {  // S is in registers: the buffer can take S(it+1) already
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&s_free[buf]);
+                if (lane == 0) mbar_arrive(s_free);
             }
+            NTX_TRACE(trole, it, 2);
             if (!special)
                 weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
             else
                 weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
                                                   b_end);
-            if (B::kSeparateP) {
-                // one W block: the previous tile's second MMA must have consumed it (it was
-                // issued a whole tile ago, so this wait is normally already satisfied)
-                if (trole < 3) NTX_TRACE(trole, it, 3);
-                if (it > 0) mbar_wait(p_free, (it - 1) & 1);
+            NTX_TRACE(trole, it, 3);
+            if (SEP) {
+                // block pb was last read by the second MMA of tile it-2, issued a whole tile ago
+                if (it >= 2) mbar_wait(&p_free[pb], ((it - 2) >> 1) & 1);
                 tc_fence_after();
-                if (trole < 3) NTX_TRACE(trole, it, 4);
-                tmem_st16(lane_addr + B::kPCol + quarter * 16, packed);
+                NTX_TRACE(trole, it, 4);
+                tmem_st16(lane_addr + B::kPCol + pb * 64 + quarter * 16, packed);
             } else {
-                tmem_st16(taddr, packed);
+                tmem_st16(taddr, packed);  // over the S columns just consumed
             }
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[B::kSeparateP ? 0 : buf]);
-            if (trole < 3) NTX_TRACE(trole, it, 5);
+            if (lane == 0) mbar_arrive(&p_full[pb]);
+            NTX_TRACE(trole, it, 5);
         }
         // epilogue: raw accumulator rows -> acc_out[split][row][D], 32-column groups round-robin
         mbar_wait(acc_full, 0);

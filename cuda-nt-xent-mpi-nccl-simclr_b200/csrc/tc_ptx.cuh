@@ -160,6 +160,25 @@ __device__ __forceinline__ float ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// 2^t for t in [-126, 0] on the FMA/ALU pipes instead of the MUFU: round-to-nearest split
+// t = n + r via the 1.5*2^23 magic constant, degree-3 polynomial for 2^r on [-0.5, 0.5]
+// (max relative error 7.5e-5), exponent patched in with one integer add.  The tile kernels
+// send a fixed fraction of their exponentials this way because MUFU ex2 (16/clk/SM) is their
+// tightest pipe while the FMA pipe (128/clk/SM) has room.
+__device__ __forceinline__ float ex2_poly(float t) {
+    const float magic = 12582912.0f;
+    const float tf = t + magic;
+    const float r = t - (tf - magic);
+    float p = fmaf(0.055171460f, r, 0.24261086f);
+    p = fmaf(p, r, 0.69326097f);
+    p = fmaf(p, r, 0.99992812f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(tf) << 23));
+}
+// ex2 for element e of a chunk: kPoly of every 8 consecutive elements take the polynomial.
+template <int kPoly>
+__device__ __forceinline__ float ex2_mix(float t, int e) {
+    return ((e & 7) < kPoly) ? ex2_poly(t) : ex2(t);
+}
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     uint32_t r;
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
