@@ -70,7 +70,10 @@ __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
     return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
 }
 
-// One 32-column chunk of an S row folded into the running base-2 (max, sum).
+// One 32-column chunk of an S row folded into the running base-2 (max, sum).  The values are
+// already t = log2(e)/tau * u_a.u_b: the A operand was scaled by k = log2(e)/tau when it was
+// staged, which saves one FFMA per logit.  The fixed-max form sums 2^t as is (t <= k <= 50, so
+// M terms of at most 2^50 stay far inside fp32) and reports max = 0.
 template <bool kOnline>
 __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special, int64_t col0,
                                           int64_t row, int64_t M, float k_scale, float& m_run,
@@ -80,15 +83,14 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
         if (!special) {
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
-                p0 += ex2_mix<kFwdPoly>(fmaf(__uint_as_float(v[e]), k_scale, -k_scale), e);
-                p1 += ex2_mix<kFwdPoly>(fmaf(__uint_as_float(v[e + 1]), k_scale, -k_scale), e + 1);
+                p0 += ex2_mix<kFwdPoly>(__uint_as_float(v[e]), e);
+                p1 += ex2_mix<kFwdPoly>(__uint_as_float(v[e + 1]), e + 1);
             }
         } else {
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
                 const int64_t col = col0 + e;
-                const float t = fmaf(__uint_as_float(v[e]), k_scale, -k_scale);
-                p0 += (col < M && col != row) ? ex2(t) : 0.f;
+                p0 += (col < M && col != row) ? ex2(__uint_as_float(v[e])) : 0.f;
             }
         }
         s_run += p0 + p1;
@@ -98,7 +100,7 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
         for (int e = 0; e < 32; ++e) {
             const int64_t col = col0 + e;
             const bool ok = !special || (col < M && col != row);
-            t[e] = ok ? __uint_as_float(v[e]) * k_scale : -INFINITY;
+            t[e] = ok ? __uint_as_float(v[e]) : -INFINITY;
             cmax = fmaxf(cmax, t[e]);
         }
         const float mn = fmaxf(m_run, cmax);
@@ -130,7 +132,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     uint64_t* k_empty = k_full + NS;
     uint64_t* s_full = k_empty + NS;
     uint64_t* s_empty = s_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 2);
+    uint64_t* q_ready = s_empty + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *counter = 0u;
@@ -144,6 +147,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         mbar_init(q_full, 1);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
+        mbar_init(q_ready, 4);
         fence_mbar_init();
     }
     if (warp == kFwdMmaWarp) tmem_alloc<256>(tmem_slot);
@@ -173,7 +177,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         const bool leader = elect_one();
         constexpr uint32_t idesc = idesc_bf16(kTile, kTile, false);
         const uint32_t q_addr = smem_u32(q_tile);
-        mbar_wait(q_full, 0);
+        mbar_wait(q_ready, 0);
         for (int it = 0; it < n_tiles; ++it) {
             const int st = it % NS, buf = it & 1;
             mbar_wait(&k_full[st], (it / NS) & 1);
@@ -195,8 +199,28 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         const int row_in_tile = quad * 32 + lane;
         const int64_t row = a0 + row_in_tile;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-        float m_run = kOnline ? -INFINITY : k_scale;
+        float m_run = kOnline ? -INFINITY : 0.f;
         float s_run = 0.f;
+        // scale the row tile by k = log2(e)/tau where TMA put it (elementwise, so the swizzle is
+        // irrelevant), then publish it to the tensor core's (async-proxy) view of shared memory
+        {
+            mbar_wait(q_full, 0);
+            uint4* q4 = reinterpret_cast<uint4*>(q_tile);
+            for (int i = threadIdx.x; i < C::kTileBytes / 16; i += kSoftmaxThreads) {
+                uint4 w = q4[i];
+                uint32_t* p = reinterpret_cast<uint32_t*>(&w);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float lo = __uint_as_float(p[j] << 16) * k_scale;
+                    const float hi = __uint_as_float(p[j] & 0xffff0000u) * k_scale;
+                    p[j] = pack_bf16(lo, hi);
+                }
+                q4[i] = w;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
         // 32-column chunks, double-buffered in registers: the load of the next chunk (or of the
         // next tile's first chunk) is in flight while the current one is exponentiated.
         uint32_t va[32], vb[32];
@@ -242,7 +266,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 
 // ----------------------------------------------------------------- backward ---
 // MODE: kSym / kRow / kCol (common.cuh).  kTwoExp (kSym only): W = 2^(t-l_a) + 2^(t-l_b) instead
-// of the one-exponential form E (e_a + e_b), E = 2^(t-k), used when 1/tau is too large for it.
+// of the one-exponential form 2^t (2^-l_a + 2^-l_b), used when k = log2(e)/tau is so large that
+// 2^t alone could leave the fp32 range.  t = k u_a.u_b comes straight out of the first MMA: the
+// A operand is scaled by k when it is parked in TMEM.
 //
 // 608 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 issues S = U_a U_b^T,
 // warp 18 issues acc += W U_b.  Per 128x128
@@ -289,16 +315,16 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
         float w[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const float s = __uint_as_float(v[e + h]);
+            const float t = __uint_as_float(v[e + h]);  // k u_a.u_b (the A operand carries k)
             float x;
             if (MODE == kRow) {
-                x = ex2(fmaf(s, k_scale, -row_c));
+                x = ex2(t - row_c);
             } else if (MODE == kCol) {
-                x = ex2(fmaf(s, k_scale, -cc[e + h]));
+                x = ex2(t - cc[e + h]);
             } else if (kTwoExp) {
-                x = ex2(fmaf(s, k_scale, -row_c)) + ex2(fmaf(s, k_scale, -cc[e + h]));
+                x = ex2(t - row_c) + ex2(t - cc[e + h]);
             } else {
-                x = ex2_mix<kBwdPoly>(fmaf(s, k_scale, -k_scale), e + h) * (row_c + cc[e + h]);
+                x = ex2_mix<kBwdPoly>(t, e + h) * (row_c + cc[e + h]);  // 2^t (2^-l_a + 2^-l_b)
             }
             if (kSpecial) {
                 const int64_t col = col0 + e + h;
@@ -454,7 +480,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 for (int q = 0; q < 4; ++q) {
                     uint4 t = make_uint4(0u, 0u, 0u, 0u);
                     if (row < M) t = __ldg(src + g * 4 + q);
-                    p[q * 4 + 0] = t.x; p[q * 4 + 1] = t.y; p[q * 4 + 2] = t.z; p[q * 4 + 3] = t.w;
+                    const uint32_t raw[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)  // scaled by k = log2(e)/tau: S comes out as k u_a.u_b
+                        p[q * 4 + j] = pack_bf16(__uint_as_float(raw[j] << 16) * k_scale,
+                                                 __uint_as_float(raw[j] & 0xffff0000u) * k_scale);
                 }
                 tmem_st16(lane_addr + B::kQCol + g * 16, p);
             }
@@ -464,12 +494,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             if (lane == 0) mbar_arrive(q_full);
         }
 
-        // per-row constant: l_a in base-2 units, or e_a = 2^(k - l_a) for the one-exponential form
+        // per-row constant: l_a in base-2 units, or 2^-l_a for the one-exponential form
         float row_c = 0.f;
         if (MODE != kCol) {
             if (row_ok) {
                 const float l2 = lse[row] * kLog2e;
-                row_c = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+                row_c = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
             } else {
                 row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
             }
@@ -483,7 +513,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 float val = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
                 if (c0 + c < b_end) {
                     const float l2 = __ldg(lse + c0 + c) * kLog2e;
-                    val = (MODE == kSym && !kTwoExp) ? ex2(k_scale - l2) : l2;
+                    val = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
                 }
                 colc[c] = val;
             }
