@@ -38,7 +38,7 @@ constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)
 #define NTX_FWD_POLY 3
 #endif
 #ifndef NTX_BWD_POLY
-#define NTX_BWD_POLY 2
+#define NTX_BWD_POLY 0
 #endif
 constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
 
