@@ -66,6 +66,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="multi-GPU: issue every launch from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
@@ -245,7 +247,8 @@ def run_native(args):
         launches_per_step = 5  # normalise, forward tiles, forward finalize, backward tiles, epilogue
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent
-        engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags)
+        engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
+                                      use_cuda_graph=not args.no_graph)
 
         def step(zin):
             return engine.forward_backward(zin)[0]
@@ -305,6 +308,8 @@ def run_native(args):
         total_ms, e2e_ms, prof["fwd_ms"], prof["bwd_ms"] = [float(x) for x in t.tolist()]
 
     loss_val = float(loss_host.item())
+    if world > 1:
+        engine.release()  # a live CUDA graph with NCCL kernels would hang the communicator teardown
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -346,7 +351,8 @@ def run_native(args):
         "config": {"workload": f"ntxent_fwd_bwd_M{M}_D{D}_tau{tau}_{dt}", "M": M, "D": D, "tau": tau,
                    "rows_per_gpu": rows, "flop_model": "8*M^2*D per step (BASELINE.md section 3)",
                    "l2_flush_between_steps": flush is not None, "plan": plan,
-                   "backward_mode": "symmetric" if world == 1 else args.bwd_mode},
+                   "backward_mode": "symmetric" if world == 1 else args.bwd_mode,
+                   "cuda_graph": bool(world > 1 and not args.no_graph)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": z_host.numel() * z_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": launches_per_step * args.steps,

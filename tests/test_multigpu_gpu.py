@@ -44,6 +44,15 @@ def _worker(rank, world, port, M, D, tau, mode, dtype_name, out_dir):
         l2 = distributed_ntxent_loss(zr, tau, engine=eng)
         l2.backward()
         torch.cuda.synchronize()
+        # the CUDA-graph replay of the same step must reproduce the eager result bit for bit
+        eng_g = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
+                                     use_cuda_graph=True)
+        for _ in range(2):
+            loss_g, dz_g = eng_g.forward_backward(shard)
+        torch.cuda.synchronize()
+        same = torch.equal(loss_g, loss) and torch.equal(dz_g, dz)
+        eng_g.release()
+        assert same
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), loss=loss.float().cpu().numpy(),
                  dz=dz.float().cpu().numpy(), dz_ag=zr.grad.float().cpu().numpy())
     finally:

@@ -1,0 +1,45 @@
+"""Per-phase GPU timing of the row-partitioned step (run under torchrun)."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch, torch.distributed as dist
+import ntxent_b200
+from ntxent_b200 import capi
+from ntxent_b200.distributed import RowPartitionedNTXent
+
+rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dev = torch.device("cuda", lr)
+dist.init_process_group("nccl", device_id=dev)
+M, D, tau = 32768, 128, 0.1
+rows = M // world
+z = torch.from_numpy(np.random.default_rng(1234).standard_normal((M, D), dtype=np.float32)).to(torch.bfloat16)
+zl = z[rank * rows:(rank + 1) * rows].to(dev)
+eng = RowPartitionedNTXent(M, D, tau, torch.bfloat16, dev)
+be = eng.backend
+
+def ev():
+    e = torch.cuda.Event(enable_timing=True); e.record(); return e
+
+for _ in range(5):
+    eng.forward_backward(zl)
+torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+names = ["normalize", "allgather_U", "forward_rows", "allreduce+allgather_lse", "backward_rows", "finalize_dz"]
+acc = np.zeros(len(names)); n = 20
+t_cpu = 0.0
+for _ in range(n):
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e = [ev()]
+    u, inv = be.normalize(zl); e.append(ev())
+    dist.all_gather_into_tensor(eng.u_all, u); e.append(ev())
+    lse, lp = be.forward_rows(eng.u_all, eng.row_begin, rows, tau, eng.ws); e.append(ev())
+    loss = lp.clone(); dist.all_reduce(loss); dist.all_gather_into_tensor(eng.lse_all, lse); e.append(ev())
+    du, _ = be.backward_rows(eng.u_all, eng.lse_all, eng.row_begin, rows, tau, 0, eng.ws); e.append(ev())
+    dz = be.finalize_dz(du, zl, inv, None); e.append(ev())
+    t_cpu += time.perf_counter() - t0
+    torch.cuda.synchronize()
+    acc += np.array([e[i].elapsed_time(e[i + 1]) for i in range(len(names))])
+if rank == 0:
+    print(f"world={world} per-phase GPU ms:", {k: round(v / n, 4) for k, v in zip(names, acc)}, "sum", round(acc.sum() / n, 4),
+          "cpu issue ms", round(1e3 * t_cpu / n, 4))
+dist.destroy_process_group()
