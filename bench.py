@@ -85,6 +85,23 @@ def make_input(M, D):
     return np.random.default_rng(1234).standard_normal((M, D), dtype=np.float32)
 
 
+def ncu_dram_traffic(kernel_tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel at the C4
+    workload, from the committed `ncu --set full` summary (profiles/); None if it is not there."""
+    path = os.path.join(ROOT, "profiles", f"r1_ncu_{kernel_tag}_summary.csv")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    try:
+        for line in open(path):
+            f = line.strip().split(",")
+            if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                total += float(f[2]) * scale.get(f[1], 1.0)
+                seen += 1
+    except OSError:
+        return None
+    return total if seen == 2 else None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -335,7 +352,10 @@ def run_native(args):
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
         "peak_source": f"{peak_kind} MEASURED_PEAKS.json bf16_tflops (burst)"
                        + ("" if dt == "bf16" or args.simt else " / 2 for tf32"),
-        "traffic": None,
+        # DRAM bytes of one launch from the committed ncu capture (same workload, 1 GPU); the
+        # kernel is tensor-bound: its operands (8 MB of U) live in L2 for the whole launch
+        "traffic": ncu_dram_traffic("k_bwd") if (world == 1 and (M, D, dt) == (32768, 128, "bf16")
+                                                   and not args.simt) else None,
         "flop_per_launch": bwd_flop_per_launch, "ms_per_launch": bwd_ms,
         "fwd_kernel": {"ms_per_launch": fwd_ms, "flop_per_launch": 2.0 * rows * M * D,
                        "achieved": (2.0 * rows * M * D / (fwd_ms * 1e-3) / 1e12) if fwd_ms > 0 else 0.0},
