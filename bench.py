@@ -261,7 +261,7 @@ def run_native(args):
 
         def step(zin):
             return capi.forward_backward(zin, tau, None, False, flags, ws, out)[0]
-        launches_per_step = 5  # normalise, forward tiles, forward finalize, backward tiles, epilogue
+        launches_per_step = 6  # normalise, forward tiles, finalize, loss reduce, backward tiles, epilogue
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent
         engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,

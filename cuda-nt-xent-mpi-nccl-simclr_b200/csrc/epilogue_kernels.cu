@@ -1,5 +1,5 @@
 // epilogue_kernels.cu -- the small HBM-bound kernels either side of the tile passes:
-//   fwd_finalize : split partials -> l_i, positive logit, deterministic loss reduction
+//   fwd_finalize : split partials -> l_i, positive logit; loss_reduce: deterministic loss sum
 //                  (replaces compute_loss_kernel, src/ntxent_kernel.cu:105-134, and its
 //                   single-block diagonal walk);
 //   bwd_epilogue : split partials -> dU (positive term, 1/(tau M)), optionally the
@@ -12,42 +12,52 @@ namespace ntxent_b200 {
 constexpr int kMaxDChunks = 8;  // D <= 1024: each lane holds 4 floats per 128-wide chunk
 
 // -------------------------------------------------------------- fwd finalize ---
+constexpr int kFinalizeRowsPerWarp = 4;                       // independent rows in flight per warp
+constexpr int kFinalizeRowsPerCta = 8 * kFinalizeRowsPerWarp;  // fewer CTAs -> fewer fence+atomic round trips
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
                     float inv_tau, int nsplit, const float* __restrict__ part_m,
                     const float* __restrict__ part_s, float* __restrict__ lse_rows,
-                    float* __restrict__ block_partials, unsigned* __restrict__ counter,
-                    float* __restrict__ loss_out, float loss_scale) {
+                    float* __restrict__ block_partials) {
     __shared__ float warp_contrib[8];
-    __shared__ double red[256];
-    __shared__ bool is_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+    const int64_t r0 = (int64_t)blockIdx.x * kFinalizeRowsPerCta + warp * kFinalizeRowsPerWarp;
+    float m[kFinalizeRowsPerWarp], s[kFinalizeRowsPerWarp], dot[kFinalizeRowsPerWarp];
+    // all loads of the warp's four rows are issued before any of them is consumed
+#pragma unroll
+    for (int q = 0; q < kFinalizeRowsPerWarp; ++q) {
+        const int64_t r = r0 + q;
+        m[q] = -INFINITY; s[q] = 0.f; dot[q] = 0.f;
+        if (r < row_count) {
+            for (int sp = lane; sp < nsplit; sp += 32)
+                lse2_merge(m[q], s[q], part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
+            const int64_t row = row_begin + r;
+            const T* ui = U + row * D;
+            const T* up = U + ((row + M / 2) % M) * D;
+            for (int k = lane * 4; k < D; k += 128) {
+                const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
+                dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+            }
+        }
+    }
     float contrib = 0.f;
-    if (r < row_count) {
-        float m = -INFINITY, s = 0.f;
-        for (int sp = lane; sp < nsplit; sp += 32)
-            lse2_merge(m, s, part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
+#pragma unroll
+    for (int q = 0; q < kFinalizeRowsPerWarp; ++q) {
+        const int64_t r = r0 + q;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-            const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
-            const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
-            lse2_merge(m, s, m2, s2);
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[q], o);
+            const float s2 = __shfl_xor_sync(0xffffffffu, s[q], o);
+            lse2_merge(m[q], s[q], m2, s2);
         }
-        const float l = (m + log2f(s)) * kLn2;
-        const int64_t row = row_begin + r;
-        const int64_t pos = (row + M / 2) % M;
-        const T* ui = U + row * D;
-        const T* up = U + pos * D;
-        float dot = 0.f;
-        for (int k = lane * 4; k < D; k += 128) {
-            const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
-            dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        const float d = warp_sum(dot[q]);
+        if (r < row_count) {
+            const float l = (m[q] + log2f(s[q])) * kLn2;
+            if (lane == 0) lse_rows[r] = l;
+            contrib += l - d * inv_tau;
         }
-        dot = warp_sum(dot);
-        if (lane == 0) lse_rows[r] = l;
-        contrib = l - dot * inv_tau;
     }
     if (lane == 0) warp_contrib[warp] = contrib;
     __syncthreads();
@@ -56,26 +66,24 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
 #pragma unroll
         for (int w = 0; w < 8; ++w) bsum += warp_contrib[w];
         block_partials[blockIdx.x] = bsum;
-        __threadfence();
-        const unsigned done = atomicAdd(counter, 1u);
-        is_last = (done == gridDim.x - 1);
     }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    // the last CTA reduces the per-CTA partials in a fixed order (run-to-run deterministic)
+}
+
+// One CTA sums the per-CTA partials in a fixed order (run-to-run deterministic).  A separate
+// launch costs less than the fence + same-address atomic of a last-CTA-done scheme here.
+__global__ void __launch_bounds__(1024)
+loss_reduce_kernel(const float* __restrict__ block_partials, int n, float* __restrict__ loss_out,
+                   float loss_scale) {
+    __shared__ double red[1024];
     double acc = 0.0;
-    for (unsigned b = threadIdx.x; b < gridDim.x; b += 256) acc += (double)block_partials[b];
+    for (int b = threadIdx.x; b < n; b += 1024) acc += (double)block_partials[b];
     red[threadIdx.x] = acc;
     __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
+    for (int o = 512; o > 0; o >>= 1) {
         if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) {
-        *loss_out = (float)(red[0] * (double)loss_scale);
-        *counter = 0u;
-    }
+    if (threadIdx.x == 0) *loss_out = (float)(red[0] * (double)loss_scale);
 }
 
 cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
@@ -83,15 +91,19 @@ cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int6
                                 const float* part_m, const float* part_s, float* lse_rows,
                                 float* block_partials, unsigned* counter, float* loss_out,
                                 float loss_scale, cudaStream_t stream) {
-    dim3 grid((unsigned)((row_count + 7) / 8)), block(256);
+    dim3 grid((unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta)), block(256);
     if (op_bf16)
         fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
             (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
-            part_s, lse_rows, block_partials, counter, loss_out, loss_scale);
+            part_s, lse_rows, block_partials);
     else
         fwd_finalize_kernel<float><<<grid, block, 0, stream>>>(
             (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m, part_s,
-            lse_rows, block_partials, counter, loss_out, loss_scale);
+            lse_rows, block_partials);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    (void)counter;
+    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_out, loss_scale);
     return cudaGetLastError();
 }
 

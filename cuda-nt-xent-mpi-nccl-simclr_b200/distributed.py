@@ -29,7 +29,7 @@ from . import capi
 class CudaBackend:
     """The only product backend: hand-written sm_100a kernels behind the C-ABI."""
 
-    launches = {"normalize": 1, "forward_rows": 2, "backward_rows_symmetric": 2,
+    launches = {"normalize": 1, "forward_rows": 3, "backward_rows_symmetric": 2,
                 "backward_rows_contract": 4, "finalize_dz": 1}
 
     def __init__(self, flags: int = 0):
