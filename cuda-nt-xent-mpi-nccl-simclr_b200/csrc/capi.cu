@@ -77,26 +77,35 @@ inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 inline bool op_is_bf16(int dtype, unsigned flags) {
     return dtype == NTXENT_BF16 || (flags & NTXENT_FLAG_MIXED_PRECISION);
 }
-inline bool want_tc(int64_t D, bool op_bf16, unsigned flags) {
-    return !(flags & NTXENT_FLAG_FORCE_SIMT) && tc_supported(D, op_bf16);
+// tf32 tiles for fp32 operands only while log2(e)/tau <= 24 (tau >= 0.06): their error in dz grows
+// with 1/tau (measured 1e-5 at tau 0.5, 5.5e-5 at 0.07 against the 1e-4 bound); colder than that
+// the exact fp32-FMA kernels run.  tau < 0 means "not known yet" (workspace sizing).
+constexpr float kTf32MinTau = 0.06f;
+inline bool want_tc(int64_t M, int64_t D, bool op_bf16, unsigned flags, float tau) {
+    if (flags & NTXENT_FLAG_FORCE_SIMT) return false;
+    if (!op_bf16 && tau >= 0.f && tau < kTf32MinTau) return false;
+    return tc_supported(M, D, op_bf16);
 }
 
 struct Plans {
     SplitPlan fwd, bwd_rows, bwd_cols;
     bool tc;
     unsigned flags;
+    size_t ut_bytes;
 };
 
 // All split decisions in one place so that sizing and launching can never disagree.
-Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned flags) {
+Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned flags, float tau) {
     Plans p;
     p.flags = flags;
-    p.tc = want_tc(D, op_bf16, flags);
+    p.ut_bytes = 0;
+    p.tc = want_tc(M, D, op_bf16, flags, tau);
     const int sms = device_sm_count();
     if (p.tc) {
-        p.fwd = tc_plan_fwd(M, D, row_count, sms);
+        p.fwd = tc_plan_fwd(M, D, row_count, op_bf16, sms);
         p.bwd_rows = tc_plan_bwd(M, D, row_count, M, sms);
         p.bwd_cols = tc_plan_bwd(M, D, M, row_count, sms);
+        p.ut_bytes = tc_bwd_scratch_bytes(M, D, op_bf16);
     } else {
         p.fwd = plan_splits(row_count, M, 64, 64, sms * 4, kMaxSplit);
         p.bwd_rows = plan_splits(row_count, M, 64, 64, sms * 2, kMaxSplit);
@@ -112,6 +121,7 @@ struct RowsWs {
     float* part_s;
     float* acc_rows;
     float* acc_cols;
+    float* ut;  // tf32 tile kernels: transposed copy of U
     size_t bytes;
 };
 
@@ -130,6 +140,7 @@ RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Pla
     w.part_s = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.acc_rows = (float*)take(sizeof(float) * (size_t)p.bwd_rows.nsplit * row_count * D);
     if (with_cols) w.acc_cols = (float*)take(sizeof(float) * (size_t)p.bwd_cols.nsplit * M * D);
+    if (p.ut_bytes) w.ut = (float*)take(p.ut_bytes);
     w.bytes = off;
     return w;
 }
@@ -182,7 +193,7 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
                      float* loss_out, float loss_scale, cudaStream_t st) {
     g_timer.start(0, st);
     if (p.tc)
-        NTX_TRY(tc_launch_fwd(u_all, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
+        NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
                               w.part_s, w.counter, st));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
@@ -196,11 +207,12 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
 
 int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                   int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float tau,
-                  int mode, const Plans& p, const SplitPlan& plan, float* acc, cudaStream_t st) {
+                  int mode, const Plans& p, const SplitPlan& plan, float* acc, float* ut,
+                  cudaStream_t st) {
     g_timer.start(1, st);
     if (p.tc)
-        NTX_TRY(tc_launch_bwd(u_all, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau, mode,
-                              p.flags, plan, acc, st));
+        NTX_TRY(tc_launch_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau,
+                              mode, p.flags, plan, acc, ut, st));
     else
         NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
                                 tau, mode, plan, acc, st));
@@ -212,7 +224,7 @@ int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_b
                         const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
                         void* dz_out, float* pos_prob_out, cudaStream_t st) {
     int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows,
-                           w.rows.acc_rows, st);
+                           w.rows.acc_rows, w.rows.ut, st);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
     e.acc = w.rows.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = w.U; e.op_bf16 = op_bf16;
@@ -301,7 +313,7 @@ int ntxent_b200_plan_info(int64_t M, int64_t D, int64_t row_count, int dtype, un
                           int* uses_tcgen05, int* fwd_splits, int* bwd_splits) {
     if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK || row_count < 1 || row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
-    const Plans p = make_plans(M, D, row_count, op_is_bf16(dtype, flags), flags);
+    const Plans p = make_plans(M, D, row_count, op_is_bf16(dtype, flags), flags, -1.f);
     if (uses_tcgen05) *uses_tcgen05 = p.tc ? 1 : 0;
     if (fwd_splits) *fwd_splits = p.fwd.nsplit;
     if (bwd_splits) *bwd_splits = p.bwd_rows.nsplit;
@@ -313,14 +325,22 @@ int ntxent_b200_operand_size(int dtype, unsigned flags) { return op_is_bf16(dtyp
 size_t ntxent_b200_workspace_bytes(int64_t M, int64_t D, int dtype, unsigned flags) {
     if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK) return 0;
     const bool opb = op_is_bf16(dtype, flags);
-    return carve_device(nullptr, M, D, opb, make_plans(M, D, M, opb, flags)).bytes;
+    // fp32 operands may run on either kernel family depending on tau: size for the larger one
+    const size_t a = carve_device(nullptr, M, D, opb, make_plans(M, D, M, opb, flags, -1.f)).bytes;
+    const size_t b = carve_device(nullptr, M, D, opb,
+                                  make_plans(M, D, M, opb, flags | NTXENT_FLAG_FORCE_SIMT, -1.f)).bytes;
+    return std::max(a, b);
 }
 
 size_t ntxent_b200_rows_workspace_bytes(int64_t M, int64_t D, int64_t row_count, int dtype,
                                         unsigned flags) {
     if (check_shape(M, D, 1.0f, dtype) != NTXENT_OK || row_count < 1 || row_count > M) return 0;
     const bool opb = op_is_bf16(dtype, flags);
-    return carve_rows(nullptr, M, D, row_count, make_plans(M, D, row_count, opb, flags), true).bytes;
+    const size_t a = carve_rows(nullptr, M, D, row_count, make_plans(M, D, row_count, opb, flags, -1.f), true).bytes;
+    const size_t b = carve_rows(nullptr, M, D, row_count,
+                                make_plans(M, D, row_count, opb, flags | NTXENT_FLAG_FORCE_SIMT, -1.f), true)
+                         .bytes;
+    return std::max(a, b);
 }
 
 int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
@@ -340,7 +360,7 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, M, opb, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
@@ -356,7 +376,7 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, M, opb, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
@@ -372,7 +392,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, M, opb, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
@@ -394,7 +414,7 @@ int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t ro
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, row_count, opb, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     return run_forward_rows(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_rows_out,
@@ -414,12 +434,12 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, row_count, opb, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     const bool sym = (mode == NTXENT_BWD_SYMMETRIC);
     rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau,
-                       sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, stream);
+                       sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, w.ut, stream);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
     e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = u_all; e.op_bf16 = opb;
@@ -430,7 +450,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     NTX_TRY(launch_bwd_epilogue(e, stream));
     if (!sym) {
         rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p,
-                           p.bwd_cols, w.acc_cols, stream);
+                           p.bwd_cols, w.acc_cols, w.ut, stream);
         if (rc != NTXENT_OK) return rc;
         BwdEpilogueArgs c{};
         c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit; c.u_all = u_all; c.op_bf16 = opb;
@@ -508,7 +528,7 @@ extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, f
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, M, opb, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
     if (forward_scratch_bytes(M, D, opb, p) > (size_t)NTXENT_STATIC_SCRATCH_BYTES)
         return NTXENT_ERR_STATIC_SCRATCH_EXCEEDED;
     char* base = nullptr;

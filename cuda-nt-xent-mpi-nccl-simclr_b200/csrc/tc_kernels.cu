@@ -33,6 +33,7 @@ constexpr int kThreads = 192;               // warps 0..3 softmax, warp 4 TMA, w
 constexpr int kFwdTmaWarp = 4, kFwdMmaWarp = 5;
 constexpr int kSoftmaxThreads = 128;
 constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
+constexpr int64_t kTf32MinRows = 1024;      // fp32 operands take the tf32 tiles from this many rows on
 // of every 8 exponentials in the fixed-max paths, this many are evaluated by ex2_poly
 #ifndef NTX_FWD_POLY
 #define NTX_FWD_POLY 3
@@ -42,28 +43,36 @@ constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)
 #endif
 constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
 
-template <int D>
+// TF32 = false: bf16 operands, .kind::f16 (K = 16 per MMA).  TF32 = true: fp32 operands read as
+// tf32, .kind::tf32 (K = 8 per MMA).  Either way one MMA consumes 32 bytes of every operand row
+// and a 128-byte swizzle row holds four such slices, so the descriptor arithmetic is shared.
+template <int D, bool TF32 = false>
 struct Cfg {
-    static_assert(D % 64 == 0 && D >= 64 && D <= 256, "tcgen05 tiles cover D in {64,128,192,256}");
-    static constexpr int kAtoms = D / 64;
+    static_assert(D % 64 == 0 && D >= 64 && D <= (TF32 ? 128 : 256),
+                  "tcgen05 tiles cover D in {64,128,192,256} (bf16) or {64,128} (tf32)");
+    static constexpr int kElemBytes = TF32 ? 4 : 2;
+    static constexpr int kAtoms = D * kElemBytes / 128;
+    static constexpr int kAtomCols = 128 / kElemBytes;  // elements per 128-byte swizzle row
     static constexpr int kTileBytes = kAtoms * kAtomBytes;
-    static constexpr int kKSteps = D / 16;  // MMAs per S tile (K = 16 bf16 each)
+    static constexpr int kKSteps = D * kElemBytes / 32;  // MMAs per S tile
+    static constexpr int kKPerMma = 32 / kElemBytes;
     // forward: two CTAs per SM when the tiles allow it
-    static constexpr int kFwdStages = (D <= 64) ? 3 : 2;
+    static constexpr int kFwdStages = (kTileBytes <= 16 * 1024) ? 3 : 2;
     static constexpr int kFwdSmem = (1 + kFwdStages) * kTileBytes + 2048;
     static constexpr int kFwdCtasPerSm = (kFwdSmem <= 112 * 1024) ? 2 : 1;
 };
 
-// K-major operand (rows = M or N index, 64 bf16 = 128 B per row, 8-row groups 1024 B apart).
+// K-major operand (rows = M or N index, 128 B of K per row, 8-row groups 1024 B apart).
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
-    // kstep counts 16-element K slices: 4 per swizzle atom, 32 B each inside the 128 B row
+    // kstep counts 32-byte K slices: 4 per swizzle atom
     const uint32_t addr = tile_addr + (kstep >> 2) * kAtomBytes + (kstep & 3) * 32;
     return smem_desc_sw128(addr, 16, 1024);
 }
-// MN-major view of the same tile (K index = tile row): 16 K rows per MMA = 2048 B; the next
-// 64 N elements live one atom (16 KB) further: LBO = atom stride, SBO = 8-row group stride.
+// MN-major view of the same tile (K index = tile row): 16 (bf16) or 8 (tf32) K rows per MMA; the
+// next 128 bytes of N live one atom (16 KB) further: LBO = atom stride, SBO = 8-row group stride.
+template <bool TF32 = false>
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
-    return smem_desc_sw128(tile_addr + kstep * 2048, kAtomBytes, 1024);
+    return smem_desc_sw128(tile_addr + kstep * (TF32 ? 1024 : 2048), kAtomBytes, 1024);
 }
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
@@ -115,12 +124,12 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
 }
 
 // ------------------------------------------------------------------ forward ---
-template <int D, bool kOnline>
-__global__ void __launch_bounds__(kThreads, Cfg<D>::kFwdCtasPerSm)
+template <int D, bool TF32, bool kOnline>
+__global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
               int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
               float* __restrict__ part_m, float* __restrict__ part_s, unsigned* __restrict__ counter) {
-    using C = Cfg<D>;
+    using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
@@ -160,22 +169,22 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         if (lane == 0) {
             mbar_arrive_expect_tx(q_full, C::kTileBytes);
             for (int a = 0; a < C::kAtoms; ++a)
-                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * 64, (int32_t)a0);
+                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * C::kAtomCols, (int32_t)a0);
             for (int it = 0; it < n_tiles; ++it) {
                 const int st = it % NS;
                 const uint32_t ph = (it / NS) & 1;
                 mbar_wait(&k_empty[st], ph ^ 1);
                 mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                 for (int a = 0; a < C::kAtoms; ++a)
-                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st], a * 64,
-                                (jt0 + it) * kTile);
+                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
+                                a * C::kAtomCols, (jt0 + it) * kTile);
             }
         }
         __syncwarp();
     } else if (warp == kFwdMmaWarp) {
         // the whole warp walks the loop (uniform control flow); one elected lane issues
         const bool leader = elect_one();
-        constexpr uint32_t idesc = idesc_bf16(kTile, kTile, false);
+        constexpr uint32_t idesc = idesc_op<TF32>(kTile, kTile, false);
         const uint32_t q_addr = smem_u32(q_tile);
         mbar_wait(q_ready, 0);
         for (int it = 0; it < n_tiles; ++it) {
@@ -187,8 +196,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
             if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
-                    mma_ss_f16(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
-                               idesc, kk > 0);
+                    mma_ss_f16<TF32>(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
+                                     idesc, kk > 0);
                 tc_commit(&k_empty[st]);
                 tc_commit(&s_full[buf]);
             }
@@ -211,9 +220,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 uint32_t* p = reinterpret_cast<uint32_t*>(&w);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float lo = __uint_as_float(p[j] << 16) * k_scale;
-                    const float hi = __uint_as_float(p[j] & 0xffff0000u) * k_scale;
-                    p[j] = pack_bf16(lo, hi);
+                    if (TF32) {
+                        p[j] = to_tf32(__uint_as_float(p[j]) * k_scale);
+                    } else {
+                        const float lo = __uint_as_float(p[j] << 16) * k_scale;
+                        const float hi = __uint_as_float(p[j] & 0xffff0000u) * k_scale;
+                        p[j] = pack_bf16(lo, hi);
+                    }
                 }
                 q4[i] = w;
             }
@@ -288,16 +301,28 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 //   blocks, so storing W(it) never waits for the second MMA of tile it-1.
 // TMEM columns, D  > 128:  S/W (128, W overwrites the S columns it came from) | acc (D) | U_a (D/2)
 //   no room for separate W blocks: S(it+1) has to wait for the second MMA of tile it.
-template <int D>
+// tf32 (fp32 operands): the weights stay 32-bit, so W always overwrites S in place (128 columns)
+// and U_a takes D columns:  S/W (128) | acc (D) | U_a (D).
+template <int D, bool TF32 = false>
 struct BwdCfg {
-    static constexpr bool kSeparateP = (D <= 128);
+    static constexpr bool kSeparateP = !TF32 && (D <= 128);
     static constexpr uint32_t kPCol = 128;
     static constexpr uint32_t kAccCol = kSeparateP ? 256 : 128;
     static constexpr uint32_t kQCol = kAccCol + D;
-    static_assert(kQCol + D / 2 <= 512, "TMEM budget");
-    static constexpr int kStages = (D <= 128) ? 4 : 3;
+    static constexpr uint32_t kQCols = TF32 ? D : D / 2;
+    static_assert(kQCol + kQCols <= 512, "TMEM budget");
+    // bf16: one ring of U_b tiles feeds both MMAs (the second one reads the tile MN-major).
+    // tf32: 32-bit operands cannot be read transposed out of a 16-byte-swizzled tile, so the
+    // second MMA gets its B operand K-major from a transposed copy U^T: a one-deep ring of U_b
+    // tiles (free again right after the S MMA) plus a ring of U^T tiles (free after W U).
+    static constexpr int kStages = TF32 ? 1 : ((Cfg<D, TF32>::kTileBytes <= 32 * 1024) ? 4 : 3);
+    static constexpr int kTStages = TF32 ? 2 : 0;
+    static constexpr int kTAtomBytes = D * 128;             // U^T atom: [D rows x 32 fp32]
+    static constexpr int kTTileBytes = 4 * kTAtomBytes;     // [D rows x 128 columns of the tile]
     static constexpr int kCcTiles = 32;  // column constants are staged for this many tiles at once
-    static constexpr int kSmem = kStages * Cfg<D>::kTileBytes + 2048 + kCcTiles * kTile * 4;
+    static constexpr int kSmem =
+        kStages * Cfg<D, TF32>::kTileBytes + kTStages * kTTileBytes + 2048 + kCcTiles * kTile * 4;
+    static_assert(kSmem <= 227 * 1024, "shared memory budget");
     // 16 weight warps, the TMA warp, then two MMA issuers: tcgen05.mma issue blocks while the
     // pipe is busy, so one thread issuing both S(it+1) and W(it) U would tie the two hand-off
     // chains together (S(it+1) could not go out until W(it-1) U had been fed in)
@@ -306,10 +331,13 @@ struct BwdCfg {
     static constexpr int kWeightThreads = 512;
 };
 
-template <int MODE, bool kTwoExp, bool kSpecial>
-__device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (&packed)[16],
+// kPacked: bf16 pairs into out[0..15]; otherwise 32 fp32/tf32 weights into out[0..31] (in place
+// over the S values when out aliases v).
+template <int MODE, bool kTwoExp, bool kSpecial, bool kPacked = true, int NOUT = 16>
+__device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (&packed)[NOUT],
                                              const float* __restrict__ cc, float k_scale, float row_c,
                                              int64_t col0, int64_t row, int64_t b_end) {
+    static_assert(NOUT == (kPacked ? 16 : 32), "output size");
 #pragma unroll
     for (int e = 0; e < 32; e += 2) {
         float w[2];
@@ -332,7 +360,12 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
             }
             w[h] = x;
         }
-        packed[e >> 1] = pack_bf16(w[0], w[1]);
+        if (kPacked) {
+            packed[e >> 1] = pack_bf16(w[0], w[1]);
+        } else {
+            packed[e] = to_tf32(w[0]);
+            packed[e + 1] = to_tf32(w[1]);
+        }
     }
 }
 
@@ -346,25 +379,30 @@ unsigned long long* g_trace = nullptr;
             trace[((role)*kTraceTiles + (it)) * kTraceEvents + (ev)] = clock64();                 \
     } while (0)
 
-template <int D, int MODE, bool kTwoExp>
-__global__ void __launch_bounds__(BwdCfg<D>::kThreads, 1)
-tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __restrict__ U,
+template <int D, bool TF32, int MODE, bool kTwoExp>
+__global__ void __launch_bounds__(BwdCfg<D, TF32>::kThreads, 1)
+tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_t,
+              const void* __restrict__ U_raw,
               const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int tiles_per_split, int col_tiles,
               float* __restrict__ acc_out, unsigned long long* __restrict__ trace) {
-    using C = Cfg<D>;
-    using B = BwdCfg<D>;
+    using C = Cfg<D, TF32>;
+    using B = BwdCfg<D, TF32>;
     constexpr int NS = B::kStages;
     constexpr bool SEP = B::kSeparateP;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align1024(smem_raw);
+    constexpr int NT = B::kTStages;
     uint8_t* k_tiles = smem;
-    float* colc = reinterpret_cast<float*>(smem + NS * C::kTileBytes);  // [kCcTiles][128]
+    uint8_t* kt_tiles = smem + NS * C::kTileBytes;  // tf32 only: U^T tiles for the second MMA
+    float* colc = reinterpret_cast<float*>(kt_tiles + NT * B::kTTileBytes);  // [kCcTiles][128]
     uint64_t* bars = reinterpret_cast<uint64_t*>(colc + B::kCcTiles * kTile);
     uint64_t* q_full = bars;
     uint64_t* k_full = bars + 1;
     uint64_t* k_empty = k_full + NS;
-    uint64_t* s_full = k_empty + NS;   // S tile complete (MMA commit)
+    uint64_t* kt_full = k_empty + NS;   // [2] (tf32)
+    uint64_t* kt_empty = kt_full + 2;   // [2] (tf32)
+    uint64_t* s_full = kt_empty + 2;    // S tile complete (MMA commit)
     uint64_t* s_free = s_full + 1;     // S buffer reusable: weight warps (SEP) or second MMA (aliased W)
     uint64_t* p_full = s_free + 1;     // [2] weights stored by all sixteen warps
     uint64_t* p_free = p_full + 2;     // [2] second MMA has consumed the W block (SEP only)
@@ -381,6 +419,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         prefetch_tensormap(&tmap);
         mbar_init(q_full, 16);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&kt_full[s], 1); mbar_init(&kt_empty[s], 1); }
         mbar_init(s_full, 1);
         mbar_init(s_free, SEP ? 16 : 1);
         for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], 16); mbar_init(&p_free[b], 1); }
@@ -400,15 +439,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 mbar_wait(&k_empty[st], ((it / NS) & 1) ^ 1);
                 mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                 for (int a = 0; a < C::kAtoms; ++a)
-                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st], a * 64,
-                                (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile));
+                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
+                                a * C::kAtomCols, (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile));
+                if (TF32) {  // the same columns of U^T: four [D rows x 32 columns] atoms
+                    const int tt = it & 1;
+                    mbar_wait(&kt_empty[tt], ((it >> 1) & 1) ^ 1);
+                    mbar_arrive_expect_tx(&kt_full[tt], B::kTTileBytes);
+                    for (int a = 0; a < 4; ++a)
+                        tma_load_2d(kt_tiles + tt * B::kTTileBytes + a * B::kTAtomBytes, &tmap_t, &kt_full[tt],
+                                    (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile) + a * 32, 0);
+                }
             }
         }
         __syncwarp();
     } else if (warp == B::kMmaWarp) {
         // S issuer.  The whole warp walks the loop (uniform control flow); one elected lane issues.
         const bool leader = elect_one();
-        constexpr uint32_t idesc_s = idesc_bf16(kTile, kTile, false);
+        constexpr uint32_t idesc_s = idesc_op<TF32>(kTile, kTile, false);
         mbar_wait(q_full, 0);
         tc_fence_after();
         for (int it = 0; it < n_tiles; ++it) {
@@ -424,8 +471,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             if (leader) {
 #pragma unroll
                 for (int kk = 0; kk < C::kKSteps; ++kk)
-                    mma_ts_f16(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk), idesc_s,
-                               kk > 0);
+                    mma_ts_f16<TF32>(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk),
+                                     idesc_s, kk > 0);
+                if (TF32) tc_commit(&k_empty[st]);  // tf32: only this MMA reads the U_b tile
                 tc_commit(s_full);
             }
             __syncwarp();
@@ -434,7 +482,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
     } else if (warp == B::kMmaPvWarp) {
         // acc += W(it) U_b issuer
         const bool leader = elect_one();
-        constexpr uint32_t idesc_pv = idesc_bf16(kTile, D, true);
+        constexpr uint32_t idesc_pv = idesc_op<TF32>(kTile, D, /*b_mn_major=*/!TF32);
+        constexpr int kPvSteps = kTile / C::kKPerMma;  // 8 (bf16) or 16 (tf32) MMAs over the tile's 128 K rows
         for (int it = 0; it < n_tiles; ++it) {
             const int st = it % NS;
             const int pb = SEP ? (it & 1) : 0;
@@ -442,17 +491,26 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             mbar_wait(&p_full[pb], (SEP ? (it >> 1) : it) & 1);
             tc_fence_after();
             NTX_TRACE(0, it, 5);
-            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            if (TF32) mbar_wait(&kt_full[it & 1], (it >> 1) & 1);
+            const uint32_t k_addr = TF32 ? smem_u32(kt_tiles + (it & 1) * B::kTTileBytes)
+                                         : smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
-                for (int kk = 0; kk < kTile / 16; ++kk) {
+                for (int kk = 0; kk < kPvSteps; ++kk) {
                     // W for K rows [32q, 32q+32): separate -> columns [16q, 16q+16) of block pb;
-                    // aliased -> columns [32q, 32q+16) of the S buffer
-                    const uint32_t a_col = SEP ? B::kPCol + pb * 64 + kk * 8 : (kk >> 1) * 32 + (kk & 1) * 8;
-                    mma_ts_f16(tmem_base + B::kAccCol, tmem_base + a_col, desc_mnmajor(k_addr, kk), idesc_pv,
-                               (it > 0) || (kk > 0));
+                    // aliased bf16 -> columns [32q, 32q+16) of the S buffer; tf32 -> column = K row
+                    const uint32_t a_col = TF32 ? kk * 8
+                                                : (SEP ? B::kPCol + pb * 64 + kk * 8
+                                                       : (kk >> 1) * 32 + (kk & 1) * 8);
+                    // B: bf16 -> the U_b tile read MN-major; tf32 -> the U^T tile, K-major (rows = d,
+                    // 32-byte slices of 8 tile columns, atoms of D rows)
+                    const uint64_t b_desc =
+                        TF32 ? smem_desc_sw128(k_addr + (kk >> 2) * B::kTAtomBytes + (kk & 3) * 32, 16, 1024)
+                             : desc_mnmajor<false>(k_addr, kk);
+                    mma_ts_f16<TF32>(tmem_base + B::kAccCol, tmem_base + a_col, b_desc, idesc_pv,
+                                     (it > 0) || (kk > 0));
                 }
-                tc_commit(&k_empty[st]);
+                tc_commit(TF32 ? &kt_empty[it & 1] : &k_empty[st]);
                 tc_commit(SEP ? &p_free[pb] : s_free);
             }
             __syncwarp();
@@ -470,10 +528,26 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
         const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
 
-        // park U_a in TMEM (bf16 pairs): 16-column groups of the row dealt round-robin to the
-        // four warps that share this lane quadrant
-        {
-            const uint4* src = reinterpret_cast<const uint4*>(U + row * D);
+        // park k U_a in TMEM (bf16 pairs, or fp32 for tf32): column groups of the row dealt
+        // round-robin to the four warps that share this lane quadrant
+        if (TF32) {
+            const float4* src = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + row * D);
+            for (int g = quarter; g < D / 32; g += 4) {  // 32 columns = 32 floats = 8 x float4
+                uint32_t p[32];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (row < M) t = __ldg(src + g * 8 + q);
+                    p[q * 4 + 0] = to_tf32(t.x * k_scale);
+                    p[q * 4 + 1] = to_tf32(t.y * k_scale);
+                    p[q * 4 + 2] = to_tf32(t.z * k_scale);
+                    p[q * 4 + 3] = to_tf32(t.w * k_scale);
+                }
+                tmem_st32(lane_addr + B::kQCol + g * 32, p);
+            }
+        } else {
+            const uint4* src =
+                reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(U_raw) + row * D);
             for (int g = quarter; g < D / 32; g += 4) {  // 16 packed columns = 32 bf16 = 4 x uint4
                 uint32_t p[16];
 #pragma unroll
@@ -488,6 +562,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 }
                 tmem_st16(lane_addr + B::kQCol + g * 16, p);
             }
+        }
+        {
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
@@ -527,6 +603,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
             const float* cc = colc + (it % B::kCcTiles) * kTile + quarter * 32;
             const uint32_t taddr = lane_addr + quarter * 32;  // this warp's 32 S columns
             uint32_t v[32], packed[16];
+            (void)packed;
             NTX_TRACE(trole, it, 0);
             mbar_wait(s_full, it & 1);
             tc_fence_after();
@@ -539,11 +616,18 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 if (lane == 0) mbar_arrive(s_free);
             }
             NTX_TRACE(trole, it, 2);
-            if (!special)
+            if (TF32) {  // 32-bit weights, in place over the S values
+                if (!special)
+                    weight_chunk<MODE, kTwoExp, false, false, 32>(v, v, cc, k_scale, row_c, 0, 0, 0);
+                else
+                    weight_chunk<MODE, kTwoExp, true, false, 32>(v, v, cc, k_scale, row_c, j0 + quarter * 32,
+                                                                 row, b_end);
+            } else if (!special) {
                 weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
-            else
+            } else {
                 weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
                                                   b_end);
+            }
             NTX_TRACE(trole, it, 3);
             if (SEP) {
                 // block pb was last read by the second MMA of tile it-2, issued a whole tile ago
@@ -551,6 +635,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __nv_bfloat16* __r
                 tc_fence_after();
                 NTX_TRACE(trole, it, 4);
                 tmem_st16(lane_addr + B::kPCol + pb * 64 + quarter * 16, packed);
+            } else if (TF32) {
+                tmem_st32(taddr, v);  // 32 tf32 weights over the 32 S columns just consumed
             } else {
                 tmem_st16(taddr, packed);  // over the S columns just consumed
             }
@@ -598,17 +684,23 @@ PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
     return fn;
 }
 
-// [M, D] bf16 row-major, box = [128 rows x 64 columns], 128-byte swizzle, zero fill past the edge.
-cudaError_t make_tmap(const void* u_all, int64_t M, int64_t D, CUtensorMap* out) {
+// [M, D] row-major (bf16 or fp32), box = [128 rows x 128 bytes], 128-byte swizzle, zero fill past
+// the edge.
+cudaError_t make_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols, int box_rows,
+                         CUtensorMap* out) {
     auto fn = encode_fn();
     if (!fn) return cudaErrorNotSupported;
+    const void* u_all = base;
+    const int64_t M = rows, D = cols;
+    const int eb = tf32 ? 4 : 2;
     cuuint64_t dims[2] = {(cuuint64_t)D, (cuuint64_t)M};
-    cuuint64_t strides[1] = {(cuuint64_t)D * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)kTile};
+    cuuint64_t strides[1] = {(cuuint64_t)D * eb};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     auto encode = [&] {
-        return fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(u_all), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+        return fn(out, tf32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(u_all), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     };
     CUresult r = encode();
@@ -624,14 +716,18 @@ cudaError_t make_tmap(const void* u_all, int64_t M, int64_t D, CUtensorMap* out)
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-template <int D, bool kOnline>
+cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtensorMap* out) {
+    return make_tmap_2d(u_all, tf32, M, D, kTile, out);
+}
+
+template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
                          float* part_s, unsigned* counter, cudaStream_t stream) {
-    using C = Cfg<D>;
+    using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
     const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
-    auto kern = tc_fwd_kernel<D, kOnline>;
+    auto kern = tc_fwd_kernel<D, TF32, kOnline>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
@@ -641,30 +737,47 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
     return cudaGetLastError();
 }
 
-template <int D, int MODE, bool kTwoExp>
-cudaError_t launch_bwd_t(const CUtensorMap& tmap, const void* u_all, const float* lse, int64_t M,
+// U [M, D] fp32 -> UT [D, Mpad] (Mpad = M rounded up to 4, pad columns zero): the K-major B operand
+// of the tf32 second MMA.  32x32 shared-memory transpose; 2 x 4 MB of traffic at 8192 x 128.
+__global__ void __launch_bounds__(256) transpose_f32_kernel(const float* __restrict__ U, int64_t M, int D,
+                                                            int64_t Mpad, float* __restrict__ UT) {
+    __shared__ float tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.x * 32;
+    const int d0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int i = ty; i < 32; i += 8) tile[i][tx] = (r0 + i < M) ? U[(r0 + i) * D + d0 + tx] : 0.f;
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8)
+        if (r0 + tx < Mpad) UT[(int64_t)(d0 + i) * Mpad + r0 + tx] = tile[tx][i];
+}
+
+template <int D, bool TF32, int MODE, bool kTwoExp>
+cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, const void* u_all,
+                         const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* acc,
                          cudaStream_t stream) {
-    const int smem = max(BwdCfg<D>::kSmem, 120 * 1024);
-    auto kern = tc_bwd_kernel<D, MODE, kTwoExp>;
+    using B = BwdCfg<D, TF32>;
+    const int smem = max(B::kSmem, 120 * 1024);
+    auto kern = tc_bwd_kernel<D, TF32, MODE, kTwoExp>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
-    kern<<<grid, BwdCfg<D>::kThreads, smem, stream>>>(tmap, (const __nv_bfloat16*)u_all, lse, M, a_begin,
-                                                     a_count, b_begin, b_count, k_scale,
-                                                     (int)(plan.cols_per_split / kTile), col_tiles, acc,
-                                                     g_trace);
+    kern<<<grid, B::kThreads, smem, stream>>>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count,
+                                             k_scale, (int)(plan.cols_per_split / kTile), col_tiles, acc,
+                                             g_trace);
     return cudaGetLastError();
 }
 
-template <int D>
-cudaError_t launch_bwd_d(const CUtensorMap& tmap, const void* u_all, const float* lse, int64_t M,
+template <int D, bool TF32>
+cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, const void* u_all,
+                         const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, int mode, bool two_exp, const SplitPlan& plan, int col_tiles,
                          float* acc, cudaStream_t stream) {
-#define NTX_BWD(MODE, TWO) \
-    launch_bwd_t<D, MODE, TWO>(tmap, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, plan, col_tiles, acc, stream)
+#define NTX_BWD(MODE, TWO)                                                                               \
+    launch_bwd_t<D, TF32, MODE, TWO>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, \
+                                     plan, col_tiles, acc, stream)
     if (mode == kRow) return NTX_BWD(kRow, false);
     if (mode == kCol) return NTX_BWD(kCol, false);
     return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
@@ -675,12 +788,23 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const void* u_all, const float
 
 void tc_set_trace_buffer(unsigned long long* dev_ptr) { g_trace = dev_ptr; }
 
-bool tc_supported(int64_t D, bool op_bf16) {
-    return op_bf16 && (D == 64 || D == 128 || D == 192 || D == 256);
+int64_t tc_ut_cols(int64_t M) { return (M + 3) / 4 * 4; }
+
+size_t tc_bwd_scratch_bytes(int64_t M, int64_t D, bool op_bf16) {
+    return op_bf16 ? 0 : (size_t)tc_ut_cols(M) * D * sizeof(float);
 }
 
-SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, int num_sms) {
-    const int per_sm = (D <= 128) ? 2 : 1;
+bool tc_supported(int64_t M, int64_t D, bool op_bf16) {
+    if (op_bf16) return D == 64 || D == 128 || D == 192 || D == 256;
+    // fp32 operands run as tf32 on the tensor cores once the problem is large enough for speed to
+    // matter; below that (and for D the tf32 tiles do not cover) the exact fp32-FMA kernels run
+    return (D == 64 || D == 128) && M >= kTf32MinRows;
+}
+
+SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, bool op_bf16, int num_sms) {
+    const int tile_bytes = (int)(D * (op_bf16 ? 2 : 4) * kTile);
+    const int stages = tile_bytes <= 16 * 1024 ? 3 : 2;
+    const int per_sm = ((1 + stages) * tile_bytes + 2048 <= 112 * 1024) ? 2 : 1;
     return plan_splits(row_count, M, kTile, kTile, num_sms * per_sm, 32);
 }
 
@@ -689,47 +813,76 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
     return plan_splits(a_count, b_count, kTile, kTile, num_sms, 32);
 }
 
-cudaError_t tc_launch_fwd(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, unsigned* counter, cudaStream_t stream) {
     CUtensorMap tmap;
-    cudaError_t e = make_tmap(u_all, M, D, &tmap);
+    cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
     const float k_scale = kLog2e / tau;
     const bool online = (flags & 4u) || k_scale > kFixedMaxLimit;
     const int col_tiles = (int)((M + kTile - 1) / kTile);
-#define NTX_FWD(DD)                                                                                   \
-    (online ? launch_fwd_t<DD, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                     part_s, counter, stream)                                         \
-            : launch_fwd_t<DD, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                      part_s, counter, stream))
+#define NTX_FWD(DD, TF)                                                                                    \
+    (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m,  \
+                                         part_s, counter, stream)                                          \
+            : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
+                                          part_s, counter, stream))
+    if (!op_bf16) {
+        switch (D) {
+            case 64: return NTX_FWD(64, true);
+            case 128: return NTX_FWD(128, true);
+            default: return cudaErrorNotSupported;
+        }
+    }
     switch (D) {
-        case 64: return NTX_FWD(64);
-        case 128: return NTX_FWD(128);
-        case 192: return NTX_FWD(192);
-        case 256: return NTX_FWD(256);
+        case 64: return NTX_FWD(64, false);
+        case 128: return NTX_FWD(128, false);
+        case 192: return NTX_FWD(192, false);
+        case 256: return NTX_FWD(256, false);
         default: return cudaErrorNotSupported;
     }
 #undef NTX_FWD
 }
 
-cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          cudaStream_t stream) {
-    CUtensorMap tmap;
-    cudaError_t e = make_tmap(u_all, M, D, &tmap);
+                          float* ut_scratch, cudaStream_t stream) {
+    CUtensorMap tmap, tmap_t;
+    cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
+    tmap_t = tmap;  // unused by the bf16 kernels
+    if (!op_bf16) {
+        if (!ut_scratch) return cudaErrorInvalidValue;
+        const int64_t Mpad = tc_ut_cols(M);
+        dim3 tgrid((unsigned)((Mpad + 31) / 32), (unsigned)(D / 32));
+        transpose_f32_kernel<<<tgrid, 256, 0, stream>>>((const float*)u_all, M, (int)D, Mpad, ut_scratch);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        e = make_tmap_2d(ut_scratch, true, /*rows=*/D, /*cols=*/Mpad, /*box_rows=*/D, &tmap_t);
+        if (e != cudaSuccess) return e;
+    }
     const float k_scale = kLog2e / tau;
     const bool two_exp = (flags & 4u) || k_scale > kFixedMaxLimit;
     const int col_tiles = (int)((b_count + kTile - 1) / kTile);
+#define NTX_BWD_D(DD, TF)                                                                                   \
+    launch_bwd_d<DD, TF>(tmap, tmap_t, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, \
+                         two_exp, plan, col_tiles, acc, stream)
+    if (!op_bf16) {
+        switch (D) {
+            case 64: return NTX_BWD_D(64, true);
+            case 128: return NTX_BWD_D(128, true);
+            default: return cudaErrorNotSupported;
+        }
+    }
     switch (D) {
-        case 64: return launch_bwd_d<64>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 128: return launch_bwd_d<128>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 192: return launch_bwd_d<192>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
-        case 256: return launch_bwd_d<256>(tmap, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, two_exp, plan, col_tiles, acc, stream);
+        case 64: return NTX_BWD_D(64, false);
+        case 128: return NTX_BWD_D(128, false);
+        case 192: return NTX_BWD_D(192, false);
+        case 256: return NTX_BWD_D(256, false);
         default: return cudaErrorNotSupported;
     }
+#undef NTX_BWD_D
 }
 
 }  // namespace ntxent_b200

@@ -4,20 +4,26 @@
 
 namespace ntxent_b200 {
 
-// True when the tcgen05 tile kernels cover this embedding width / operand type.
-bool tc_supported(int64_t D, bool op_bf16);
+// True when the tcgen05 tile kernels cover this problem: bf16 operands with D in {64,128,192,256}
+// (.kind::f16), or fp32 operands with D in {64,128} and M >= 1024 (.kind::tf32).
+bool tc_supported(int64_t M, int64_t D, bool op_bf16);
 
-SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, int num_sms);
+SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, bool op_bf16, int num_sms);
 SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, int num_sms);
 
-cudaError_t tc_launch_fwd(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, unsigned* counter, cudaStream_t stream);
 
-cudaError_t tc_launch_bwd(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          cudaStream_t stream);
+                          float* ut_scratch, cudaStream_t stream);
+
+// Scratch the tf32 backward needs for its transposed copy of U ([D, M rounded up to 4] fp32);
+// zero for bf16 operands.
+size_t tc_bwd_scratch_bytes(int64_t M, int64_t D, bool op_bf16);
+int64_t tc_ut_cols(int64_t M);
 
 // Debug aid: CTA (0,0) of the backward tile kernel stamps its pipeline hand-offs into this
 // device buffer ([3 roles][64 tiles][8 events] of clock64 values); nullptr turns it off.

@@ -105,23 +105,39 @@ __device__ __forceinline__ void tc_commit(uint64_t* bar) {
                      smem_u32(bar))
                  : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]
+// D[tmem] (+)= A[smem] * B[smem]; kind::f16 (bf16 operands) or kind::tf32 (fp32 operands)
+template <bool TF32 = false>
 __device__ __forceinline__ void mma_ss_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                            uint32_t idesc, bool accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
-        : "memory");
+    if (TF32)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+            : "memory");
 }
 // D[tmem] (+)= A[tmem] * B[smem]
+template <bool TF32 = false>
 __device__ __forceinline__ void mma_ts_f16(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
                                            uint32_t idesc, bool accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
-        : "memory");
+    if (TF32)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+            : "memory");
 }
 
 // TMEM -> registers: each lane reads its own TMEM lane, 32 consecutive 32-bit columns.
@@ -151,6 +167,19 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
           "r"(r[15])
         : "memory");
 }
+// registers -> TMEM: 32 consecutive 32-bit columns of the lane's own TMEM lane.
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]),
+          "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]),
+          "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]),
+          "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+          "r"(r[31])
+        : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() {
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
@@ -178,6 +207,13 @@ __device__ __forceinline__ float ex2_poly(float t) {
 template <int kPoly>
 __device__ __forceinline__ float ex2_mix(float t, int e) {
     return ((e & 7) < kPoly) ? ex2_poly(t) : ex2(t);
+}
+// fp32 -> tf32 with round-to-nearest (the tensor core would otherwise just drop the low 13 bits,
+// which biases every product towards zero)
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
 }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     uint32_t r;
@@ -210,6 +246,15 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr, uint32_t
 __host__ __device__ constexpr uint32_t idesc_bf16(uint32_t M, uint32_t N, bool b_mn_major) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((N >> 3) << 17) |
            ((M >> 4) << 24);
+}
+// Same for .kind::tf32: A/B format 2 (tf32: fp32 storage, the top 19 bits are used).
+__host__ __device__ constexpr uint32_t idesc_tf32(uint32_t M, uint32_t N, bool b_mn_major) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((N >> 3) << 17) |
+           ((M >> 4) << 24);
+}
+template <bool TF32>
+__host__ __device__ constexpr uint32_t idesc_op(uint32_t M, uint32_t N, bool b_mn_major) {
+    return TF32 ? idesc_tf32(M, N, b_mn_major) : idesc_bf16(M, N, b_mn_major);
 }
 
 }  // namespace ptx

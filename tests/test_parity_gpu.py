@@ -92,6 +92,23 @@ def test_config_c3_fp32(oracle):
     assert dz_err(dz, rdz) <= DZ_TOL_F32
 
 
+@pytest.mark.parametrize("M,D,tau", [(2048, 128, 0.5), (2048, 128, 0.1), (1030, 64, 0.07), (4096, 128, 0.2)])
+def test_tf32_tiles_meet_the_fp32_tolerance(oracle, M, D, tau):
+    """fp32 z at M >= 1024, D in {64,128}, tau >= 0.06 runs on the tcgen05 .kind::tf32 tiles
+    (north_star: "loss within 1e-5 relative and dZ within 1e-4 for fp32/tf32")."""
+    assert capi.plan_info(M, D, M, capi.F32)["tcgen05"] is True
+    z = seeded_z(M, D, seed=M + D)
+    loss, lse, dz, _ = run_gpu(dev(z), tau, grad_out=0.75)
+    rl, rlse, rdz = oracle.forward_backward(z.astype(np.float64), tau, grad_out=0.75)
+    assert loss == pytest.approx(rl, rel=LOSS_RTOL_F32)
+    assert dz_err(dz, rdz) <= DZ_TOL_F32
+    # colder than tau = 0.06 the exact fp32 kernels take over (tf32 error grows with 1/tau)
+    loss_c, _, dz_c, _ = run_gpu(dev(z), 0.03)
+    rl_c, _, rdz_c = oracle.forward_backward(z.astype(np.float64), 0.03)
+    assert loss_c == pytest.approx(rl_c, rel=LOSS_RTOL_F32)
+    assert dz_err(dz_c, rdz_c) <= DZ_TOL_F32
+
+
 def test_config_c4_full_size_properties(oracle):
     """configs[3] at full size (2N=32768, D=128, bf16): properties that need no O(M^2) oracle,
     plus an oracle check of a row sample (the fp32 row-block form, 256 rows)."""
