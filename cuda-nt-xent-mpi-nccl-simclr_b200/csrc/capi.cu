@@ -3,6 +3,7 @@
 #include "../../include/ntxent_b200.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
@@ -77,13 +78,14 @@ inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 inline bool op_is_bf16(int dtype, unsigned flags) {
     return dtype == NTXENT_BF16 || (flags & NTXENT_FLAG_MIXED_PRECISION);
 }
-// tf32 tiles for fp32 operands only while log2(e)/tau <= 24 (tau >= 0.06): their error in dz grows
-// with 1/tau (measured 1e-5 at tau 0.5, 5.5e-5 at 0.07 against the 1e-4 bound); colder than that
-// the exact fp32-FMA kernels run.  tau < 0 means "not known yet" (workspace sizing).
-constexpr float kTf32MinTau = 0.06f;
+// tf32 tiles for fp32 operands only while log2(e)/(tau sqrt(D)) <= 1.7 (tau >= 0.075 at D = 128,
+// >= 0.106 at D = 64): their error in dz grows with 1/tau and shrinks with sqrt(D) (measured against
+// the fp64 oracle: 6e-5 at D 128 / tau 0.07, 1.2e-4..2.4e-4 at D 64 / tau 0.07, bound 1e-4); colder
+// than that the exact fp32-FMA kernels run.  tau < 0 means "not known yet" (workspace sizing).
+constexpr float kTf32MaxScaledK = 1.7f;
 inline bool want_tc(int64_t M, int64_t D, bool op_bf16, unsigned flags, float tau) {
     if (flags & NTXENT_FLAG_FORCE_SIMT) return false;
-    if (!op_bf16 && tau >= 0.f && tau < kTf32MinTau) return false;
+    if (!op_bf16 && tau >= 0.f && kLog2e / (tau * sqrtf((float)D)) > kTf32MaxScaledK) return false;
     return tc_supported(M, D, op_bf16);
 }
 

@@ -17,8 +17,9 @@
  *            accumulation when dtype is BF16 or NTXENT_FLAG_MIXED_PRECISION is
  *            set (the reference's `use_mixed_precision`, include/ntxent_kernel.cuh:34,51,
  *            which it never reads); otherwise on fp32 operands: as tf32 on the
- *            tensor cores when M >= 1024, D is 64 or 128 and tau >= 0.06 (loss
- *            within 1e-5, dz within 1e-4 of fp64), else in exact fp32 FMA
+ *            tensor cores when M >= 1024, D is 64 or 128 and tau is not too
+ *            cold (log2(e)/(tau sqrt(D)) <= 1.7, i.e. tau >= 0.075 at D = 128;
+ *            loss within 1e-5, dz within 1e-4 of fp64), else in exact fp32 FMA
  *            arithmetic (also what NTXENT_FLAG_FORCE_SIMT selects).
  *   return   0 on success; negative NTXENT_ERR_* for argument errors; positive
  *            values are cudaError_t codes.  Nothing throws.
