@@ -300,11 +300,27 @@ def run_native(args):
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    capi.profile_begin()
+    graph_mode = world > 1 and not args.no_graph
+    if not graph_mode:
+        capi.profile_begin()
     t_steps = timed(lambda: step(z_dev), args.steps)
-    prof = capi.profile_end()
+    if not graph_mode:
+        prof = capi.profile_end()
     clocks = sampler.stop() if rank == 0 else {}
     total_ms = sum(t_steps)
+    if graph_mode:
+        # events cannot be recorded inside a replayed graph: take the per-kernel times from a
+        # short eager pass of the same step (outside the timed region)
+        engine.use_cuda_graph = False
+        for _ in range(2):
+            step(z_dev)
+        sync_all()
+        capi.profile_begin()
+        for _ in range(5):
+            step(z_dev)
+        sync_all()
+        prof = capi.profile_end()
+        engine.use_cuda_graph = True
 
     # --- end to end: pinned host z -> device -> fused op -> loss back on the host -------
     z_stage = torch.empty_like(z_dev)
@@ -343,7 +359,8 @@ def run_native(args):
     plan = capi.plan_info(M, D, rows, capi.BF16 if dt == "bf16" else capi.F32, flags)
     # executed tensor FLOPs of the backward tile pass on this rank: S recompute + W.U
     bwd_factor = 4.0 if (world == 1 or args.bwd_mode == "symmetric") else 8.0
-    bwd_flop_per_launch = bwd_factor * rows * M * D / max(1, prof["bwd_launches"] // args.steps)
+    prof_steps = 5 if graph_mode else args.steps
+    bwd_flop_per_launch = bwd_factor * rows * M * D / max(1, prof["bwd_launches"] // prof_steps)
     bwd_ms = prof["bwd_ms"] / max(1, prof["bwd_launches"])
     fwd_ms = prof["fwd_ms"] / max(1, prof["fwd_launches"])
     achieved = bwd_flop_per_launch / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else 0.0

@@ -107,7 +107,9 @@ class RowPartitionedNTXent:
 
     # -- forward -------------------------------------------------------------------------
     def forward(self, z_local: torch.Tensor):
-        """-> (loss[1] global mean, state) ; state feeds backward()."""
+        """-> (loss[1], state); state feeds backward().  With more than one rank the returned loss
+        is this rank's partial sum with its all-reduce still in flight: pass it through
+        `_join_loss` (forward_backward and the autograd wrapper do) to get the global mean."""
         if tuple(z_local.shape) != (self.rows, self.D):
             raise ValueError(f"rank {self.rank} expects a [{self.rows}, {self.D}] shard, got {tuple(z_local.shape)}")
         u_local, inv_norm = self.backend.normalize(z_local)
@@ -123,13 +125,20 @@ class RowPartitionedNTXent:
                 dist.all_gather_into_tensor(self.lse_all, lse_local.contiguous(), group=self.group)
             else:  # contract: a rank only ever needs its own l
                 self.lse_all[self.row_begin:self.row_begin + self.rows].copy_(lse_local)
-            # nothing in the backward needs the loss value: its all-reduce goes last in the
-            # forward so that the backward tiles queue up behind the l exchange, not behind it
-            dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
+            # nothing in the backward needs the loss value: its all-reduce is issued
+            # asynchronously and joined by whoever reads the loss (`_LazyLoss`, or the end of
+            # forward_backward), so the backward tiles never queue up behind it
+            work = dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._pending_loss = work
         else:
             self.lse_all.copy_(lse_local)
-        loss = loss / self.M
         return loss, (z_local, inv_norm)
+
+    def _join_loss(self, loss: torch.Tensor) -> torch.Tensor:
+        work, self._pending_loss = getattr(self, "_pending_loss", None), None
+        if work is not None:
+            work.wait()  # makes the current stream wait for the collective; no host sync
+        return loss / self.M
 
     # -- backward ------------------------------------------------------------------------
     def backward(self, state, grad_out: torch.Tensor | None = None) -> torch.Tensor:
@@ -151,7 +160,8 @@ class RowPartitionedNTXent:
         if self.use_cuda_graph and z_local.is_cuda:
             return self._replay(z_local, grad_out)
         loss, state = self.forward(z_local)
-        return loss, self.backward(state, grad_out)
+        dz = self.backward(state, grad_out)
+        return self._join_loss(loss), dz
 
     def release(self) -> None:
         """Drop the captured graph and its static buffers.  Call this before
@@ -174,12 +184,14 @@ class RowPartitionedNTXent:
                 for _ in range(3):  # warm-up on the side stream (NCCL communicators, lazy inits)
                     loss, state = self.forward(self._z_static)
                     self.backward(state, self._g_static)
+                    self._join_loss(loss)
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 loss, state = self.forward(self._z_static)
                 dz = self.backward(state, self._g_static)
+                loss = self._join_loss(loss)
             self._graph, self._loss_static, self._dz_static = graph, loss, dz
         self._z_static.copy_(z_local, non_blocking=True)
         if grad_out is None:
@@ -195,7 +207,7 @@ class _DistributedNTXentFunction(torch.autograd.Function):
     def forward(ctx, z_local, engine):
         loss, state = engine.forward(z_local.detach())
         ctx.engine, ctx.state = engine, state
-        return loss
+        return engine._join_loss(loss)
 
     @staticmethod
     def backward(ctx, grad_loss):
