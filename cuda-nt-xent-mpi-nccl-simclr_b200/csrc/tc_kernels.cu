@@ -27,11 +27,11 @@ namespace {
 
 constexpr int kTile = 128;                  // rows per row tile = columns per column tile
 constexpr int kAtomBytes = kTile * 128;     // one 128B-swizzle atom: [128 rows x 64 bf16]
-constexpr int kThreads = 192;               // warps 0..3 softmax, warp 4 TMA, warp 5 MMA
+constexpr int kThreads = 320;               // warps 0..7 softmax, warp 8 TMA, warp 9 MMA
 // The issuing warps carry the highest warp ids: the scheduler favours higher ids among ready
 // warps, and a starved MMA issuer (a dozen scalar instructions per tcgen05.mma) stalls everything.
-constexpr int kFwdTmaWarp = 4, kFwdMmaWarp = 5;
-constexpr int kSoftmaxThreads = 128;
+constexpr int kFwdTmaWarp = 8, kFwdMmaWarp = 9;
+constexpr int kSoftmaxThreads = 256;        // two warps per TMEM lane quadrant, 64 columns each
 constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
 constexpr int64_t kTf32MinRows = 1024;      // fp32 operands take the tf32 tiles from this many rows on
 // of every 8 exponentials in the fixed-max paths, this many are evaluated by ex2_poly
@@ -155,8 +155,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         prefetch_tensormap(&tmap);
         mbar_init(q_full, 1);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 4); }
-        mbar_init(q_ready, 4);
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 8); }
+        mbar_init(q_ready, 8);
         fence_mbar_init();
     }
     if (warp == kFwdMmaWarp) tmem_alloc<256>(tmem_slot);
@@ -204,10 +204,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
             __syncwarp();
         }
     } else {
-        const int quad = warp & 3;  // TMEM lanes 32*quad .. 32*quad+31 belong to this warp
+        // eight softmax warps: warp w owns TMEM lanes 32*(w%4).. (one row per thread) and the
+        // 64 columns [64h, 64h+64) of every S tile, h = w/4; with two CTAs per SM that is four warps
+        // per scheduler, enough to cover each other's TMEM loads and barrier checks
+        const int quad = warp & 3;
+        const int half = warp >> 2;
         const int row_in_tile = quad * 32 + lane;
         const int64_t row = a0 + row_in_tile;
-        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + half * 64;
         float m_run = kOnline ? -INFINITY : 0.f;
         float s_run = 0.f;
         // scale the row tile by k = log2(e)/tau where TMA put it (elementwise, so the swizzle is
@@ -234,40 +238,43 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
             __syncwarp();
             if (lane == 0) mbar_arrive(q_ready);
         }
-        // 32-column chunks, double-buffered in registers: the load of the next chunk (or of the
-        // next tile's first chunk) is in flight while the current one is exponentiated.
+        // two 32-column chunks per tile, double-buffered in registers: the load of the next chunk
+        // (or of the next tile's first chunk) is in flight while the current one is exponentiated
         uint32_t va[32], vb[32];
         mbar_wait(&s_full[0], 0);
         tc_fence_after();
         tmem_ld32(lane_addr, va);
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
-            const int64_t j0 = (int64_t)(jt0 + it) * kTile;
-            const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > M);
+            const int64_t j0 = (int64_t)(jt0 + it) * kTile + half * 64;
+            const bool special = (j0 < a0 + kTile && j0 + 64 > a0) || (j0 + 64 > M);
             const uint32_t taddr = lane_addr + buf * kTile;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t(&cur)[32] = (c & 1) ? vb : va;
-                uint32_t(&nxt)[32] = (c & 1) ? va : vb;
-                tmem_ld_wait();
-                if (c < 3) {
-                    tmem_ld32(taddr + (c + 1) * 32, nxt);
-                } else {
-                    // the whole S row has left TMEM: hand the buffer back, then prefetch
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&s_empty[buf]);
-                    if (it + 1 < n_tiles) {
-                        mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
-                        tc_fence_after();
-                        tmem_ld32(lane_addr + (buf ^ 1) * kTile, nxt);
-                    }
-                }
-                fwd_chunk<kOnline>(cur, special, j0 + c * 32, row, M, k_scale, m_run, s_run);
+            tmem_ld_wait();
+            tmem_ld32(taddr + 32, vb);
+            fwd_chunk<kOnline>(va, special, j0, row, M, k_scale, m_run, s_run);
+            tmem_ld_wait();
+            // this warp's S columns have left TMEM: hand the buffer back, then prefetch
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[buf]);
+            if (it + 1 < n_tiles) {
+                mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32(lane_addr + (buf ^ 1) * kTile, va);
             }
+            fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, k_scale, m_run, s_run);
+        }
+        // merge the two column halves of each row (upper half hands over through shared memory)
+        float2* halves = reinterpret_cast<float2*>(q_tile);  // the row tile is no longer needed:
+        named_bar_sync(1, kSoftmaxThreads);                  // every MMA that read it has completed
+        if (half == 1) halves[row_in_tile] = make_float2(m_run, s_run);
+        named_bar_sync(1, kSoftmaxThreads);
+        if (half == 0) {
+            const float2 o = halves[row_in_tile];
+            lse2_merge(m_run, s_run, o.x, o.y);
         }
         const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
-        if (r < row_count) {
+        if (half == 0 && r < row_count) {
             part_m[(int64_t)blockIdx.y * row_count + r] = m_run;
             part_s[(int64_t)blockIdx.y * row_count + r] = s_run;
         }
