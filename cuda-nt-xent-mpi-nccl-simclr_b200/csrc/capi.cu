@@ -179,6 +179,9 @@ inline bool debug_on() {
     static const bool on = [] { const char* v = getenv("NTXENT_DEBUG"); return v && v[0] == '1'; }();
     return on;
 }
+// TMA and the vector loads want 16-byte aligned rows; workspaces are carved in 256-byte units.
+inline bool aligned(const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
 #define NTX_TRY(expr)                                                                         \
     do {                                                                                      \
         cudaError_t e__ = (expr);                                                             \
@@ -263,7 +266,8 @@ const char* ntxent_b200_strerror(int code) {
     switch (code) {
         case NTXENT_OK: return "ok";
         case NTXENT_ERR_INVALID_ARGUMENT:
-            return "invalid argument (null pointer, odd or too small M, tau <= 0, unknown dtype/mode)";
+            return "invalid argument (null or misaligned pointer, odd or too small M, tau <= 0, unknown "
+                   "dtype/mode; tensors need 16-byte, workspaces 256-byte alignment)";
         case NTXENT_ERR_UNSUPPORTED_DEVICE: return "device is not sm_100 (B200)";
         case NTXENT_ERR_WORKSPACE_TOO_SMALL:
             return "workspace smaller than ntxent_b200_*workspace_bytes()";
@@ -347,7 +351,7 @@ size_t ntxent_b200_rows_workspace_bytes(int64_t M, int64_t D, int64_t row_count,
 
 int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
                           void* u_out, float* inv_norm_out, ntxent_stream_t stream) {
-    if (!z || !u_out || rows < 0) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!z || !u_out || rows < 0 || !aligned(z, 16) || !aligned(u_out, 16)) return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, rows, D, u_out, op_is_bf16(dtype, flags),
@@ -359,6 +363,7 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
                         void* workspace, size_t workspace_bytes, float* loss_out, float* lse_out,
                         ntxent_stream_t stream) {
     if (!z || !workspace || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(z, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
@@ -375,6 +380,7 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
                          size_t workspace_bytes, void* dz_out, float* pos_prob_out,
                          ntxent_stream_t stream) {
     if (!z || !lse || !workspace || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
@@ -391,6 +397,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
                                  size_t workspace_bytes, float* loss_out, float* lse_out,
                                  void* dz_out, float* pos_prob_out, ntxent_stream_t stream) {
     if (!z || !workspace || !loss_out || !lse_out || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
@@ -411,6 +418,7 @@ int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t ro
                              float* loss_partial_out, ntxent_stream_t stream) {
     if (!u_all || !workspace || !lse_rows_out || !loss_partial_out)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(u_all, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
@@ -428,6 +436,9 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
                               unsigned flags, void* workspace, size_t workspace_bytes,
                               float* du_rows_out, float* du_cols_out, ntxent_stream_t stream) {
     if (!u_all || !lse_all || !workspace || !du_rows_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(u_all, 16) || !aligned(workspace, 256) || !aligned(du_rows_out, 16) ||
+        !aligned(du_cols_out, 16))
+        return NTXENT_ERR_INVALID_ARGUMENT;
     if (mode != NTXENT_BWD_SYMMETRIC && mode != NTXENT_BWD_CONTRACT)
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (mode == NTXENT_BWD_CONTRACT && !du_cols_out) return NTXENT_ERR_INVALID_ARGUMENT;
@@ -468,7 +479,8 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
 int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,
                             const float* grad_out, int64_t rows, int64_t D, int dtype, void* dz_out,
                             ntxent_stream_t stream) {
-    if (!du_rows || !z_rows || !inv_norm_rows || !dz_out || rows < 0)
+    if (!du_rows || !z_rows || !inv_norm_rows || !dz_out || rows < 0 || !aligned(du_rows, 16) ||
+        !aligned(z_rows, 16) || !aligned(dz_out, 16))
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
@@ -526,7 +538,7 @@ size_t forward_scratch_bytes(int64_t M, int64_t D, bool op_bf16, const Plans& p)
 extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, float tau, int dtype,
                                           unsigned flags, float* loss_out, float* lse_out,
                                           ntxent_stream_t stream) {
-    if (!z || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!z || !loss_out || !lse_out || !aligned(z, 16)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);

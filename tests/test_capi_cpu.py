@@ -62,6 +62,9 @@ def test_argument_errors_return_codes_without_touching_the_device():
     L = capi.lib()
     null = ctypes.c_void_p(None)
     one = ctypes.c_void_p(256)  # never dereferenced: argument checks come first
+    odd = ctypes.c_void_p(260)  # misaligned
+    assert L.ntxent_b200_forward(odd, 64, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
+    assert L.ntxent_b200_forward(one, 64, 128, 0.5, 0, 0, odd, 1 << 30, one, one, null) == -1
     assert L.ntxent_b200_forward(null, 64, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
     assert L.ntxent_b200_forward(one, 63, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
     assert L.ntxent_b200_forward(one, 64, 128, -1.0, 0, 0, one, 1 << 30, one, one, null) == -1

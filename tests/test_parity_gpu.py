@@ -139,6 +139,24 @@ def test_config_c4_full_size_properties(oracle):
     assert (pp > 0).all() and (pp < 1).all()
 
 
+def test_config_c5_full_size_properties(oracle):
+    """configs[4] at full size on one GPU (2N=131072, D=256, bf16; the dense fp32 logits would be
+    68.7 GB and are never formed): finite, gradient orthogonal to the rows, row-sample oracle check."""
+    M, D, tau = 131072, 256, 0.1
+    z_t = dev(seeded_z(M, D, seed=9), torch.bfloat16)
+    before = torch.cuda.max_memory_allocated()
+    loss, lse, dz, pp = run_gpu(z_t, tau)
+    assert torch.cuda.max_memory_allocated() - before < 2 * 2**30  # O(M*D) working set
+    assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0 and np.isfinite(dz).all()
+    rows = slice(0, 4096)
+    zq = z_t[rows].double().cpu().numpy()
+    assert np.abs((zq * dz[rows]).sum(1)).max() <= 1e-2 * np.abs(dz).max() * np.abs(zq).max()
+    R = 64
+    rlse, _, _, _ = oracle.rowblock_f32(z_t.float().cpu().numpy(), tau, 0, R)
+    np.testing.assert_allclose(lse[:R], rlse, rtol=0, atol=5e-3)
+    assert (pp > 0).all() and (pp < 1).all()
+
+
 # ------------------------------------------------------------------------ edge cases
 @pytest.mark.parametrize("path", list(PATHS))
 @pytest.mark.parametrize("M,D,tau", [
@@ -154,7 +172,8 @@ def test_small_and_ragged_shapes_fp32(oracle, path, M, D, tau):
 
 
 @pytest.mark.parametrize("M,D,tau", [(16, 64, 0.07), (130, 128, 0.1), (1000, 64, 0.2),
-                                      (384, 256, 0.07), (2048, 128, 0.5)])
+                                      (384, 256, 0.07), (2048, 128, 0.5), (640, 192, 0.1),
+                                      (1000, 128, 0.02), (514, 256, 0.5)])
 def test_small_and_ragged_shapes_bf16(oracle, M, D, tau):
     z_t = dev(seeded_z(M, D, seed=M + D), torch.bfloat16)
     loss, lse, dz, _ = run_gpu(z_t, tau)
