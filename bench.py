@@ -66,6 +66,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="single GPU: replay the step as a CUDA graph")
     ap.add_argument("--no-graph", action="store_true",
                     help="multi-GPU: issue every launch from the host instead of replaying a CUDA graph")
     return ap.parse_args()
@@ -259,7 +260,11 @@ def run_native(args):
         out = (torch.empty(1, dtype=torch.float32, device=dev),
                torch.empty(M, dtype=torch.float32, device=dev), torch.empty_like(z_dev))
 
+        graphed = ntxent_b200.GraphedNTXent(M, D, tau, tdtype, dev) if args.graph else None
+
         def step(zin):
+            if graphed is not None:
+                return graphed(zin)[0]
             return capi.forward_backward(zin, tau, None, False, flags, ws, out)[0]
         launches_per_step = 6  # normalise, forward tiles, finalize, loss reduce, backward tiles, epilogue
     else:
@@ -300,7 +305,7 @@ def run_native(args):
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    graph_mode = world > 1 and not args.no_graph
+    graph_mode = (world > 1 and not args.no_graph) or (world == 1 and args.graph)
     if not graph_mode:
         capi.profile_begin()
     t_steps = timed(lambda: step(z_dev), args.steps)
@@ -311,7 +316,10 @@ def run_native(args):
     if graph_mode:
         # events cannot be recorded inside a replayed graph: take the per-kernel times from a
         # short eager pass of the same step (outside the timed region)
-        engine.use_cuda_graph = False
+        if world > 1:
+            engine.use_cuda_graph = False
+        else:
+            graphed, keep = None, graphed
         for _ in range(2):
             step(z_dev)
         sync_all()
@@ -320,7 +328,10 @@ def run_native(args):
             step(z_dev)
         sync_all()
         prof = capi.profile_end()
-        engine.use_cuda_graph = True
+        if world > 1:
+            engine.use_cuda_graph = True
+        else:
+            graphed = keep
 
     # --- end to end: pinned host z -> device -> fused op -> loss back on the host -------
     z_stage = torch.empty_like(z_dev)
@@ -389,7 +400,7 @@ def run_native(args):
                    "rows_per_gpu": rows, "flop_model": "8*M^2*D per step (BASELINE.md section 3)",
                    "l2_flush_between_steps": flush is not None, "plan": plan,
                    "backward_mode": "symmetric" if world == 1 else args.bwd_mode,
-                   "cuda_graph": bool(world > 1 and not args.no_graph)},
+                   "cuda_graph": bool(graph_mode)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": z_host.numel() * z_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": launches_per_step * args.steps,

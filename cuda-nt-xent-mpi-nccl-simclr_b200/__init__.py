@@ -12,8 +12,8 @@ Layers:
   distributed.py       row-partitioned data-parallel loss over torch.distributed (NCCL)
 """
 from . import capi  # noqa: F401
-from .ops import (NTXentLoss, backward, check_tensor_core_support, forward,  # noqa: F401
-                  forward_with_state, ntxent_loss)
+from .ops import (GraphedNTXent, NTXentLoss, backward, check_tensor_core_support,  # noqa: F401
+                  forward, forward_with_state, ntxent_loss)
 
 __all__ = ["capi", "forward", "backward", "forward_with_state", "check_tensor_core_support",
-           "ntxent_loss", "NTXentLoss"]
+           "ntxent_loss", "NTXentLoss", "GraphedNTXent"]
