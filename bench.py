@@ -63,6 +63,8 @@ def parse_args():
     ap.add_argument("--simt", action="store_true", help="force the fp32-FMA tile kernels")
     ap.add_argument("--bwd-mode", default="symmetric", choices=["symmetric", "contract"],
                     help="multi-GPU backward formulation")
+    ap.add_argument("--comm", default="symm", choices=["symm", "nccl"],
+                    help="multi-GPU exchange: kernels push into the peers' symmetric memory, or NCCL collectives")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-flush", action="store_true")
@@ -270,7 +272,7 @@ def run_native(args):
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent
         engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
-                                      use_cuda_graph=not args.no_graph)
+                                      use_cuda_graph=not args.no_graph, comm=args.comm)
 
         def step(zin):
             return engine.forward_backward(zin)[0]
@@ -400,7 +402,7 @@ def run_native(args):
                    "rows_per_gpu": rows, "flop_model": "8*M^2*D per step (BASELINE.md section 3)",
                    "l2_flush_between_steps": flush is not None, "plan": plan,
                    "backward_mode": "symmetric" if world == 1 else args.bwd_mode,
-                   "cuda_graph": bool(graph_mode)},
+                   "cuda_graph": bool(graph_mode), "comm": args.comm if world > 1 else None},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": z_host.numel() * z_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": launches_per_step * args.steps,

@@ -26,9 +26,26 @@ EXPORTS = [
     "ntxent_b200_rows_workspace_bytes", "ntxent_b200_forward_rows", "ntxent_b200_backward_rows",
     "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
     "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
+    "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push",
 ]
 
 _lib = None
+MAX_PEERS = 16
+
+
+class PeerList(ctypes.Structure):
+    """ntxent_peer_list: the same buffer's device pointer on every rank (symmetric memory)."""
+    _fields_ = [("ptr", ctypes.c_void_p * MAX_PEERS), ("count", ctypes.c_int)]
+
+    @classmethod
+    def of(cls, ptrs):
+        if not 1 <= len(ptrs) <= MAX_PEERS:
+            raise NTXentError(f"between 1 and {MAX_PEERS} peers supported, got {len(ptrs)}")
+        pl = cls()
+        for i, p in enumerate(ptrs):
+            pl.ptr[i] = int(p)
+        pl.count = len(ptrs)
+        return pl
 
 
 class NTXentError(RuntimeError):
@@ -78,6 +95,11 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_profile_end.argtypes = [fp, ip, fp, ip]
     L.ntxent_b200_plan_info.restype = ci
     L.ntxent_b200_plan_info.argtypes = [i64, i64, i64, ci, u32, ip, ip, ip]
+    pp = ctypes.POINTER(PeerList)
+    L.ntxent_b200_normalize_push.restype = ci
+    L.ntxent_b200_normalize_push.argtypes = [vp, i64, i64, ci, u32, pp, i64, vp, vp]
+    L.ntxent_b200_forward_rows_push.restype = ci
+    L.ntxent_b200_forward_rows_push.argtypes = [vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, pp, pp, ci, vp]
     L.ntxent_b200_debug_set_trace.restype = ci
     L.ntxent_b200_debug_set_trace.argtypes = [vp]
     L.ntxent_b200_forward_static.restype = ci
@@ -302,3 +324,31 @@ def forward_static(z: torch.Tensor, tau: float, use_mixed_precision: bool = Fals
         check(lib().ntxent_b200_forward_static(_ptr(z), M, D, float(tau), _dtype_code(z), fl,
                                                _ptr(loss), _ptr(lse), _stream()))
     return loss, lse
+
+
+def normalize_push(z_rows: torch.Tensor, u_all_peers: "PeerList", row_begin: int, flags: int = 0,
+                   inv_norm: torch.Tensor | None = None) -> torch.Tensor:
+    """Normalise this rank's rows and store them at `row_begin` of every rank's u_all; -> inv_norm."""
+    _require_cuda(z_rows)
+    z_rows = z_rows.contiguous()
+    rows, D = z_rows.shape
+    with torch.cuda.device(z_rows.device):
+        if inv_norm is None:
+            inv_norm = torch.empty(rows, dtype=torch.float32, device=z_rows.device)
+        check(lib().ntxent_b200_normalize_push(_ptr(z_rows), rows, D, _dtype_code(z_rows), flags,
+                                               ctypes.byref(u_all_peers), row_begin, _ptr(inv_norm), _stream()))
+    return inv_norm
+
+
+def forward_rows_push(u_all: torch.Tensor, row_begin: int, row_count: int, tau: float,
+                      lse_all_peers: "PeerList", loss_parts_peers: "PeerList", rank: int, flags: int = 0,
+                      ws: torch.Tensor | None = None) -> None:
+    """forward_rows whose l_i and partial loss are stored into every rank's lse_all / loss_parts."""
+    _require_cuda(u_all)
+    M, D = u_all.shape
+    with torch.cuda.device(u_all.device):
+        ws = rows_workspace(M, D, row_count, u_all, flags) if ws is None else ws
+        check(lib().ntxent_b200_forward_rows_push(_ptr(u_all), M, D, row_begin, row_count, float(tau),
+                                                  _op_code(u_all), flags, _ptr(ws), ws.numel(),
+                                                  ctypes.byref(lse_all_peers), ctypes.byref(loss_parts_peers),
+                                                  rank, _stream()))

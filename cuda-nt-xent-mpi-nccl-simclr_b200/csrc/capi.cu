@@ -193,9 +193,10 @@ inline bool aligned(const void* p, uintptr_t a) { return (reinterpret_cast<uintp
         }                                                                                     \
     } while (0)
 
-int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
-                     int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
-                     float* loss_out, float loss_scale, cudaStream_t st) {
+int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
+                          int64_t row_count, float tau, const Plans& p, const RowsWs& w,
+                          const PeerList& lse_outs, int64_t lse_offset, const PeerList& loss_outs,
+                          int loss_index, float loss_scale, cudaStream_t st) {
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
@@ -204,10 +205,27 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, w.counter, st));
     g_timer.stop(0, st);
-    NTX_TRY(launch_fwd_finalize(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
-                                w.part_m, w.part_s, lse_rows, w.block_partials, w.counter, loss_out,
-                                loss_scale, st));
+    NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
+                                     w.part_m, w.part_s, lse_outs, lse_offset, w.block_partials, loss_outs,
+                                     loss_index, loss_scale, st));
     return NTXENT_OK;
+}
+
+int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
+                     int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
+                     float* loss_out, float loss_scale, cudaStream_t st) {
+    return run_forward_rows_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p, w,
+                                 single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, st);
+}
+
+bool to_peer_list(const ntxent_peer_list* in, PeerList* out) {
+    if (!in || in->count < 1 || in->count > NTXENT_MAX_PEERS || in->count > kMaxPeers) return false;
+    out->n = in->count;
+    for (int i = 0; i < in->count; ++i) {
+        if (!in->ptr[i] || !aligned(in->ptr[i], 16)) return false;
+        out->p[i] = in->ptr[i];
+    }
+    return true;
 }
 
 int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
@@ -357,6 +375,42 @@ int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, uns
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, rows, D, u_out, op_is_bf16(dtype, flags),
                              inv_norm_out, stream));
     return NTXENT_OK;
+}
+
+int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
+                               const ntxent_peer_list* u_all_peers, int64_t row_begin,
+                               float* inv_norm_out, ntxent_stream_t stream) {
+    PeerList outs{};
+    if (!z || rows < 0 || row_begin < 0 || !aligned(z, 16) || !to_peer_list(u_all_peers, &outs))
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    NTX_TRY(launch_normalize_push(z, dtype == NTXENT_BF16, rows, D, outs, row_begin,
+                                  op_is_bf16(dtype, flags), inv_norm_out, stream));
+    return NTXENT_OK;
+}
+
+int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+                                  int64_t row_count, float tau, int dtype, unsigned flags,
+                                  void* workspace, size_t workspace_bytes,
+                                  const ntxent_peer_list* lse_all_peers,
+                                  const ntxent_peer_list* loss_parts_peers, int loss_index,
+                                  ntxent_stream_t stream) {
+    PeerList lse_outs{}, loss_outs{};
+    if (!u_all || !workspace || !to_peer_list(lse_all_peers, &lse_outs) ||
+        !to_peer_list(loss_parts_peers, &loss_outs) || loss_index < 0)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(u_all, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags, tau);
+    const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    return run_forward_rows_push(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_outs, row_begin,
+                                 loss_outs, loss_index, 1.0f, stream);
 }
 
 int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,

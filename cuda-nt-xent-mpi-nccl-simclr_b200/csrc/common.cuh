@@ -17,6 +17,20 @@ constexpr float kNormEps = 1e-12f;  // torch.nn.functional.normalize's default e
 //   kCol : W_ab = exp(S_ab - l_b)                     (column term G_{I,:}^T U_I, a over all rows)
 enum BwdMode : int { kSym = 0, kRow = 1, kCol = 2 };
 
+// Output fan-out for the multi-GPU "push" path: the same values are stored to up to kMaxPeers
+// buffers (this GPU's own and its peers' symmetric-memory copies, mapped over NVLink).
+constexpr int kMaxPeers = 16;
+struct PeerList {
+    void* p[kMaxPeers];
+    int n;
+};
+inline PeerList single_peer(void* ptr) {
+    PeerList l{};
+    l.p[0] = ptr;
+    l.n = 1;
+    return l;
+}
+
 struct SplitPlan {
     int row_tiles;       // tiles over the A range
     int nsplit;          // column splits (grid.y)
@@ -33,6 +47,10 @@ int device_sm_count();  // SM count of the current device; 148 when there is non
 // ---- launchers (all asynchronous on `stream`; return the launch status) ----------
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
                              bool op_bf16, float* inv_norm, cudaStream_t stream);
+// Same, storing the rows at row `row_offset` of every buffer in `outs`.
+cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
+                                  const PeerList& outs, int64_t row_offset, bool op_bf16,
+                                  float* inv_norm, cudaStream_t stream);
 
 // SIMT (fp32 FMA) tile kernels.
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
@@ -49,6 +67,13 @@ cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int6
                                 const float* part_m, const float* part_s, float* lse_rows,
                                 float* block_partials, unsigned* counter, float* loss_out,
                                 float loss_scale, cudaStream_t stream);
+// Same with fan-out: l_i goes to element lse_offset + i of every buffer in `lse_outs`, the
+// (scaled) loss to element loss_index of every buffer in `loss_outs`.
+cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                                     int64_t row_begin, int64_t row_count, float tau, int nsplit,
+                                     const float* part_m, const float* part_s, const PeerList& lse_outs,
+                                     int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
+                                     int loss_index, float loss_scale, cudaStream_t stream);
 
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b

@@ -19,7 +19,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
                     float inv_tau, int nsplit, const float* __restrict__ part_m,
-                    const float* __restrict__ part_s, float* __restrict__ lse_rows,
+                    const float* __restrict__ part_s, PeerList lse_outs, int64_t lse_offset,
                     float* __restrict__ block_partials) {
     __shared__ float warp_contrib[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -55,7 +55,8 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
         const float d = warp_sum(dot[q]);
         if (r < row_count) {
             const float l = (m[q] + log2f(s[q])) * kLn2;
-            if (lane == 0) lse_rows[r] = l;
+            if (lane == 0)
+                for (int i = 0; i < lse_outs.n; ++i) static_cast<float*>(lse_outs.p[i])[lse_offset + r] = l;
             contrib += l - d * inv_tau;
         }
     }
@@ -72,7 +73,7 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
 // One CTA sums the per-CTA partials in a fixed order (run-to-run deterministic).  A separate
 // launch costs less than the fence + same-address atomic of a last-CTA-done scheme here.
 __global__ void __launch_bounds__(1024)
-loss_reduce_kernel(const float* __restrict__ block_partials, int n, float* __restrict__ loss_out,
+loss_reduce_kernel(const float* __restrict__ block_partials, int n, PeerList loss_outs, int loss_index,
                    float loss_scale) {
     __shared__ double red[1024];
     double acc = 0.0;
@@ -83,7 +84,29 @@ loss_reduce_kernel(const float* __restrict__ block_partials, int n, float* __res
         if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) *loss_out = (float)(red[0] * (double)loss_scale);
+    if (threadIdx.x == 0)
+        for (int i = 0; i < loss_outs.n; ++i)
+            static_cast<float*>(loss_outs.p[i])[loss_index] = (float)(red[0] * (double)loss_scale);
+}
+
+cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
+                                     int64_t row_begin, int64_t row_count, float tau, int nsplit,
+                                     const float* part_m, const float* part_s, const PeerList& lse_outs,
+                                     int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
+                                     int loss_index, float loss_scale, cudaStream_t stream) {
+    dim3 grid((unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta)), block(256);
+    if (op_bf16)
+        fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
+            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
+            part_s, lse_outs, lse_offset, block_partials);
+    else
+        fwd_finalize_kernel<float><<<grid, block, 0, stream>>>(
+            (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m, part_s,
+            lse_outs, lse_offset, block_partials);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_outs, loss_index, loss_scale);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
@@ -91,20 +114,10 @@ cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int6
                                 const float* part_m, const float* part_s, float* lse_rows,
                                 float* block_partials, unsigned* counter, float* loss_out,
                                 float loss_scale, cudaStream_t stream) {
-    dim3 grid((unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta)), block(256);
-    if (op_bf16)
-        fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
-            part_s, lse_rows, block_partials);
-    else
-        fwd_finalize_kernel<float><<<grid, block, 0, stream>>>(
-            (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m, part_s,
-            lse_rows, block_partials);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
     (void)counter;
-    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_out, loss_scale);
-    return cudaGetLastError();
+    return launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, nsplit, part_m, part_s,
+                                    single_peer(lse_rows), 0, block_partials, single_peer(loss_out), 0,
+                                    loss_scale, stream);
 }
 
 // -------------------------------------------------------------- bwd epilogue ---

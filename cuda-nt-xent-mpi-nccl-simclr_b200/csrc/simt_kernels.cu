@@ -19,7 +19,7 @@ namespace ntxent_b200 {
 // rows scaled by 1e-5 .. 1e5 (python/test.py:64) neither underflow nor overflow.
 template <typename TIn, typename TOut>
 __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ z, int64_t rows,
-                                                        int D, TOut* __restrict__ u,
+                                                        int D, PeerList outs, int64_t row_offset,
                                                         float* __restrict__ inv_norm) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -42,31 +42,38 @@ __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ 
     const float nrm = sqrtf(ss) / sc;  // |z|
     const float inv = 1.0f / fmaxf(nrm, kNormEps);
     if (lane == 0 && inv_norm) inv_norm[row] = inv;
-    TOut* ur = u + row * D;
     for (int k = lane * 4; k < D; k += 128) {
         float4 v = Elem<TIn>::ld4(zr + k);
         v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-        Elem<TOut>::st4(ur + k, v);
+        // one local store, or the same row pushed into every rank's gathered copy (peer stores)
+        for (int i = 0; i < outs.n; ++i)
+            Elem<TOut>::st4(static_cast<TOut*>(outs.p[i]) + (row_offset + row) * D + k, v);
     }
 }
 
-cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
-                             bool op_bf16, float* inv_norm, cudaStream_t stream) {
+cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
+                                  const PeerList& outs, int64_t row_offset, bool op_bf16,
+                                  float* inv_norm, cudaStream_t stream) {
     if (rows == 0) return cudaSuccess;
     dim3 grid((unsigned)((rows + 7) / 8)), block(256);
     if (z_bf16 && op_bf16)
         normalize_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)z, rows, (int)D, (__nv_bfloat16*)u_out, inv_norm);
+            (const __nv_bfloat16*)z, rows, (int)D, outs, row_offset, inv_norm);
     else if (z_bf16)
         normalize_kernel<__nv_bfloat16, float><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)z, rows, (int)D, (float*)u_out, inv_norm);
+            (const __nv_bfloat16*)z, rows, (int)D, outs, row_offset, inv_norm);
     else if (op_bf16)
         normalize_kernel<float, __nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const float*)z, rows, (int)D, (__nv_bfloat16*)u_out, inv_norm);
+            (const float*)z, rows, (int)D, outs, row_offset, inv_norm);
     else
-        normalize_kernel<float, float><<<grid, block, 0, stream>>>((const float*)z, rows, (int)D,
-                                                                  (float*)u_out, inv_norm);
+        normalize_kernel<float, float><<<grid, block, 0, stream>>>((const float*)z, rows, (int)D, outs,
+                                                                  row_offset, inv_norm);
     return cudaGetLastError();
+}
+
+cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
+                             bool op_bf16, float* inv_norm, cudaStream_t stream) {
+    return launch_normalize_push(z, z_bf16, rows, D, single_peer(u_out), 0, op_bf16, inv_norm, stream);
 }
 
 // ------------------------------------------------------------- 64x64 S tile ---

@@ -52,6 +52,40 @@ class CudaBackend:
         return capi.rows_workspace(M, D, rows, u_all, self.flags)
 
 
+class _SymmetricBuffers:
+    """Two rotating sets of (u_all, lse_all, loss_parts) in symmetric memory: every rank maps every
+    other rank's copy, so the kernels can store their results into all of them directly
+    (ntxent_b200_normalize_push / _forward_rows_push) and the NCCL all-gather / all-reduce disappear;
+    what remains between producers and consumers is one device-side barrier.  Two sets, because a
+    fast rank may already push step t+1 while a slow one still reads step t."""
+
+    def __init__(self, M, D, op_dtype, world, device, group):
+        import torch.distributed._symmetric_memory as symm_mem
+        item = torch.empty(0, dtype=op_dtype).element_size()
+        al = lambda n: (n + 255) // 256 * 256  # noqa: E731
+        u_bytes, lse_bytes, loss_bytes = al(M * D * item), al(M * 4), 256
+        set_bytes = u_bytes + lse_bytes + loss_bytes
+        self.buf = symm_mem.empty(2 * set_bytes, dtype=torch.uint8, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        bases = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(bases) != world:
+            raise capi.NTXentError("symmetric-memory rendezvous returned an unexpected number of peers")
+        self.sets = []
+        for k in range(2):
+            o = k * set_bytes
+            self.sets.append(dict(
+                u_all=self.buf[o:o + M * D * item].view(op_dtype).view(M, D),
+                lse_all=self.buf[o + u_bytes:o + u_bytes + M * 4].view(torch.float32),
+                loss_parts=self.buf[o + u_bytes + lse_bytes:o + u_bytes + lse_bytes + 4 * world].view(torch.float32),
+                u_peers=capi.PeerList.of([b + o for b in bases]),
+                lse_peers=capi.PeerList.of([b + o + u_bytes for b in bases]),
+                loss_peers=capi.PeerList.of([b + o + u_bytes + lse_bytes for b in bases])))
+        self.step = 0
+
+    def barrier(self, channel: int) -> None:
+        self.hdl.barrier(channel=channel)
+
+
 def _reduce_scatter_sum(out: torch.Tensor, inp: torch.Tensor, group) -> None:
     """Sum-reduce-scatter; backends without the primitive (gloo) get all-reduce + slice."""
     try:
@@ -71,7 +105,7 @@ class RowPartitionedNTXent:
 
     def __init__(self, M: int, D: int, tau: float, dtype: torch.dtype, device, group=None,
                  backward_mode: str = "symmetric", flags: int = 0, backend=None,
-                 use_mixed_precision: bool = False, use_cuda_graph: bool = False):
+                 use_mixed_precision: bool = False, use_cuda_graph: bool = False, comm: str = "nccl"):
         if backward_mode not in ("symmetric", "contract"):
             raise ValueError("backward_mode must be 'symmetric' or 'contract'")
         self.group = group
@@ -90,6 +124,16 @@ class RowPartitionedNTXent:
         op_dtype = torch.bfloat16 if (dtype == torch.bfloat16 or use_mixed_precision) else torch.float32
         if hasattr(self.backend, "operand_dtype"):  # test doubles may keep wider operands
             op_dtype = self.backend.operand_dtype(dtype)
+        if comm not in ("nccl", "symm"):
+            raise ValueError("comm must be 'nccl' (all-gather / all-reduce collectives) or 'symm' "
+                             "(results pushed into the peers' symmetric memory by the kernels)")
+        self.comm = comm if self.world > 1 else "nccl"
+        self.flags = flags
+        self.symm = None
+        if self.comm == "symm":
+            if backend is not None:
+                raise ValueError("comm='symm' needs the CUDA backend")
+            self.symm = _SymmetricBuffers(self.M, self.D, op_dtype, self.world, self.device, group)
         self.u_all = torch.empty(self.M, self.D, dtype=op_dtype, device=self.device)
         self.lse_all = torch.empty(self.M, dtype=torch.float32, device=self.device)
         self.du_col_local = torch.empty(self.rows, self.D, dtype=torch.float32, device=self.device)
@@ -112,6 +156,8 @@ class RowPartitionedNTXent:
         `_join_loss` (forward_backward and the autograd wrapper do) to get the global mean."""
         if tuple(z_local.shape) != (self.rows, self.D):
             raise ValueError(f"rank {self.rank} expects a [{self.rows}, {self.D}] shard, got {tuple(z_local.shape)}")
+        if self.symm is not None:
+            return self._forward_symm(z_local)
         u_local, inv_norm = self.backend.normalize(z_local)
         if self.world > 1:
             dist.all_gather_into_tensor(self.u_all, u_local.contiguous(), group=self.group)
@@ -132,6 +178,20 @@ class RowPartitionedNTXent:
             self._pending_loss = work
         else:
             self.lse_all.copy_(lse_local)
+        return loss, (z_local, inv_norm)
+
+    def _forward_symm(self, z_local: torch.Tensor):
+        """Forward with the collectives fused into the kernels: peer stores + two barriers."""
+        sy = self.symm
+        cur = sy.sets[sy.step & 1]
+        sy.step += 1
+        inv_norm = capi.normalize_push(z_local, cur["u_peers"], self.row_begin, self.flags)
+        sy.barrier(0)  # every rank's rows have landed in this rank's u_all
+        self.u_all, self.lse_all = cur["u_all"], cur["lse_all"]
+        capi.forward_rows_push(self.u_all, self.row_begin, self.rows, self.tau, cur["lse_peers"],
+                               cur["loss_peers"], self.rank, self.flags, self.ws)
+        sy.barrier(1)  # ... and every rank's l and partial loss
+        loss = cur["loss_parts"].sum(dim=0, keepdim=True)
         return loss, (z_local, inv_norm)
 
     def _join_loss(self, loss: torch.Tensor) -> torch.Tensor:

@@ -137,6 +137,37 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
                               int dtype, unsigned flags, void* workspace, size_t workspace_bytes,
                               float* du_rows_out, float* du_cols_out, ntxent_stream_t stream);
 
+/* ---- Peer-memory ("push") variants: the collective fused into the kernel ----
+ * On an NVSwitch box every GPU can map its peers' buffers (symmetric memory).
+ * Instead of producing a local result and all-gathering it with NCCL, these
+ * variants store the result straight into every rank's copy: `peers` lists the
+ * device pointers of the SAME buffer on each rank (this rank's own included),
+ * as mapped into this process.  The caller separates producer and consumers
+ * with one cross-rank barrier.  No counterpart in the reference (it has no
+ * communication code at all, CMakeLists.txt:13-14,41-47). */
+#define NTXENT_MAX_PEERS 16
+typedef struct {
+    void* ptr[NTXENT_MAX_PEERS];
+    int count;
+} ntxent_peer_list;
+
+/* ntxent_b200_normalize whose rows land at row `row_begin` of every rank's
+ * gathered u_all [M, D] (replaces normalise + all-gather of U). */
+int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
+                               const ntxent_peer_list* u_all_peers, int64_t row_begin,
+                               float* inv_norm_out, ntxent_stream_t stream);
+
+/* ntxent_b200_forward_rows whose l_i land at element row_begin + i of every
+ * rank's lse_all float[M] and whose partial loss lands at element `loss_index`
+ * (the rank) of every rank's loss_parts float[ranks] (replaces the all-gather
+ * of l and the all-reduce of the loss). */
+int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
+                                  int64_t row_count, float tau, int dtype, unsigned flags,
+                                  void* workspace, size_t workspace_bytes,
+                                  const ntxent_peer_list* lse_all_peers,
+                                  const ntxent_peer_list* loss_parts_peers, int loss_index,
+                                  ntxent_stream_t stream);
+
 /* Normalisation Jacobian: dz_i = g (dU_i - (dU_i . u_i) u_i) * inv_norm_i with
  * u_i = z_i * inv_norm_i.  z_rows, dz_out in `dtype`; g = *grad_out (NULL: 1). */
 int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,

@@ -53,6 +53,15 @@ def _worker(rank, world, port, M, D, tau, mode, dtype_name, out_dir):
         same = torch.equal(loss_g, loss) and torch.equal(dz_g, dz)
         eng_g.release()
         assert same
+        # peer-memory exchange (kernels store into every rank's symmetric buffers, no NCCL
+        # all-gather / all-reduce): same numbers as the NCCL path, over several steps so that
+        # both rotating buffer sets are used
+        eng_s = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
+                                     comm="symm")
+        for _ in range(3):
+            loss_s, dz_s = eng_s.forward_backward(shard)
+        torch.cuda.synchronize()
+        assert torch.allclose(loss_s, loss, rtol=1e-6) and torch.equal(dz_s, dz)
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), loss=loss.float().cpu().numpy(),
                  dz=dz.float().cpu().numpy(), dz_ag=zr.grad.float().cpu().numpy())
     finally:
