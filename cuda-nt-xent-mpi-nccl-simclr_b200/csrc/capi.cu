@@ -250,7 +250,9 @@ int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_b
                            w.rows.acc_rows, w.rows.ut, st);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
-    e.acc = w.rows.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = w.U; e.op_bf16 = op_bf16;
+    e.acc = w.rows.acc_rows; e.nsplit = p.bwd_rows.nsplit;
+    e.sk_ctas = p.bwd_rows.sk_ctas; e.sk_col_tiles = p.bwd_rows.sk_col_tiles;
+    e.u_all = w.U; e.op_bf16 = op_bf16;
     e.M = M; e.D = D; e.a_begin = 0; e.a_count = M;
     e.pos_coeff = 2.f; e.pos_lo = 0; e.pos_hi = M;
     e.scale = 1.0f / (tau * (float)M);
@@ -509,7 +511,9 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
                        sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, w.ut, stream);
     if (rc != NTXENT_OK) return rc;
     BwdEpilogueArgs e{};
-    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit; e.u_all = u_all; e.op_bf16 = opb;
+    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit;
+    e.sk_ctas = p.bwd_rows.sk_ctas; e.sk_col_tiles = p.bwd_rows.sk_col_tiles;
+    e.u_all = u_all; e.op_bf16 = opb;
     e.M = M; e.D = D; e.a_begin = row_begin; e.a_count = row_count;
     e.pos_coeff = sym ? 2.f : 1.f; e.pos_lo = 0; e.pos_hi = M;
     e.scale = 1.0f / (tau * (float)M);
@@ -520,7 +524,9 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
                            p.bwd_cols, w.acc_cols, w.ut, stream);
         if (rc != NTXENT_OK) return rc;
         BwdEpilogueArgs c{};
-        c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit; c.u_all = u_all; c.op_bf16 = opb;
+        c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit;
+        c.sk_ctas = p.bwd_cols.sk_ctas; c.sk_col_tiles = p.bwd_cols.sk_col_tiles;
+        c.u_all = u_all; c.op_bf16 = opb;
         c.M = M; c.D = D; c.a_begin = 0; c.a_count = M;
         c.pos_coeff = 1.f; c.pos_lo = row_begin; c.pos_hi = row_begin + row_count;
         c.scale = e.scale;

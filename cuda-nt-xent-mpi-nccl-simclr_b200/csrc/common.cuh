@@ -35,6 +35,11 @@ struct SplitPlan {
     int row_tiles;       // tiles over the A range
     int nsplit;          // column splits (grid.y)
     int64_t cols_per_split;  // multiple of the column tile
+    // tcgen05 backward only: the tiles are dealt to `sk_ctas` persistent CTAs in equal contiguous
+    // shares instead of a (row tile, split) grid; nsplit is then the maximum number of partials
+    // of a row tile and sk_col_tiles the column-tile count the dealing was computed with.
+    int sk_ctas;       // 0: plain grid split
+    int sk_col_tiles;
 };
 
 // Column-split heuristic shared by the workspace sizing and the launchers: pick the
@@ -78,6 +83,7 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
     int nsplit;
+    int sk_ctas, sk_col_tiles;  // from the SplitPlan: per-row-tile partial counts when sk_ctas > 0
     const void* u_all;       // [M, D] operands
     bool op_bf16;
     int64_t M, D, a_begin, a_count;

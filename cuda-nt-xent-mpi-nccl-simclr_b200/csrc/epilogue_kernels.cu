@@ -124,6 +124,8 @@ cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int6
 struct BwdEpiDev {
     const float* acc;
     int nsplit;
+    int sk_ctas, sk_col_tiles;  // > 0: the row tile's partial count follows from the tile dealing
+    int64_t sk_total;
     int64_t M, a_begin, a_count;
     int D;
     float pos_coeff;
@@ -149,13 +151,19 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
     const int64_t pos = (row + p.M / 2) % p.M;
     const float pc = (pos >= p.pos_lo && pos < p.pos_hi) ? p.pos_coeff : 0.f;
     const TOp* up = U + pos * D;
+    int nsplit = p.nsplit;
+    if (p.sk_ctas > 0) {  // CTAs whose tile ranges touch this row tile (tc_kernels.cu, BwdUnit)
+        const int64_t first = (r / 128) * p.sk_col_tiles;
+        nsplit = (int)(((first + p.sk_col_tiles) * p.sk_ctas - 1) / p.sk_total -
+                       ((first + 1) * p.sk_ctas - 1) / p.sk_total) + 1;
+    }
     float4 du[kMaxDChunks];
 #pragma unroll
     for (int c = 0; c < kMaxDChunks; ++c) {
         const int k = c * 128 + lane * 4;
         if (k >= D) break;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int sp = 0; sp < p.nsplit; ++sp) {
+        for (int sp = 0; sp < nsplit; ++sp) {
             const float4 t =
                 *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
             v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
@@ -218,6 +226,8 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
 cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
     if (a.a_count == 0) return cudaSuccess;
     BwdEpiDev p;
+    p.sk_ctas = a.sk_ctas; p.sk_col_tiles = a.sk_col_tiles;
+    p.sk_total = (int64_t)((a.a_count + 127) / 128) * a.sk_col_tiles;
     p.acc = a.acc; p.nsplit = a.nsplit; p.M = a.M; p.a_begin = a.a_begin; p.a_count = a.a_count;
     p.D = (int)a.D; p.pos_coeff = a.pos_coeff; p.pos_lo = a.pos_lo; p.pos_hi = a.pos_hi;
     p.scale = a.scale; p.du_out = a.du_out; p.inv_norm = a.inv_norm; p.grad_out = a.grad_out;

@@ -16,6 +16,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <mutex>
 
 #include "tc_ptx.cuh"
@@ -290,8 +291,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 // 2^t alone could leave the fp32 range.  t = k u_a.u_b comes straight out of the first MMA: the
 // A operand is scaled by k when it is parked in TMEM.
 //
-// 608 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 issues S = U_a U_b^T,
-// warp 18 issues acc += W U_b.  Per 128x128
+// 640 threads: warps 0..15 weight stage, warp 16 TMA producer, warp 17 issues S = U_a U_b^T,
+// warp 18 issues acc += W U_b, warp 19 stages the per-column constants a block ahead.  One
+// persistent CTA per SM walks an equal share of the tiles (BwdUnit below).  Per 128x128
 // tile the weight stage needs 16384 ex2 (MUFU: 16/clk/SM -> 1024 clk) and the tensor pipe 2 x 512
 // clk, so the two must overlap completely and the weight warps must not move in lock-step:
 // warp w owns TMEM lanes 32*(w%4).. (one row per thread) and columns [32q, 32q+32) of every S
@@ -326,15 +328,17 @@ struct BwdCfg {
     static constexpr int kTStages = TF32 ? 2 : 0;
     static constexpr int kTAtomBytes = D * 128;             // U^T atom: [D rows x 32 fp32]
     static constexpr int kTTileBytes = 4 * kTAtomBytes;     // [D rows x 128 columns of the tile]
-    static constexpr int kCcTiles = 32;  // column constants are staged for this many tiles at once
+    // column constants (l_b or 2^-l_b) are staged by their own warp, kCcTiles tiles at a time into
+    // one of two blocks, a block ahead of the weight warps
+    static constexpr int kCcTiles = 16;
     static constexpr int kSmem =
-        kStages * Cfg<D, TF32>::kTileBytes + kTStages * kTTileBytes + 2048 + kCcTiles * kTile * 4;
+        kStages * Cfg<D, TF32>::kTileBytes + kTStages * kTTileBytes + 2048 + 2 * kCcTiles * kTile * 4;
     static_assert(kSmem <= 227 * 1024, "shared memory budget");
     // 16 weight warps, the TMA warp, then two MMA issuers: tcgen05.mma issue blocks while the
     // pipe is busy, so one thread issuing both S(it+1) and W(it) U would tie the two hand-off
     // chains together (S(it+1) could not go out until W(it-1) U had been fed in)
-    static constexpr int kThreads = 608;
-    static constexpr int kTmaWarp = 16, kMmaWarp = 17, kMmaPvWarp = 18;
+    static constexpr int kThreads = 640;
+    static constexpr int kTmaWarp = 16, kMmaWarp = 17, kMmaPvWarp = 18, kConstWarp = 19;
     static constexpr int kWeightThreads = 512;
 };
 
@@ -376,22 +380,63 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
     }
 }
 
-// Optional pipeline trace (tools/trace_bwd.py): CTA (0,0) stamps clock64() at its hand-offs into
-// trace[role][tile][event]; role 0 = MMA warp, 1 = weight warp 0, 2 = weight warp 15.
+// Optional pipeline trace (tools/trace_bwd.py): CTA 0 stamps clock64() at its hand-offs into
+// trace[role][tile][event] (5 x 64 x 8 words); role 0 = MMA warps, 1 = weight warp 0, 2 = weight
+// warp 15, 3 = the other weight warps (overwriting each other), all for the CTA's first unit;
+// role 4 = unit-level events of weight warp 0 (row 63: kernel entry / set-up done / exit, with
+// %globaltimer in events 6 and 7 to calibrate the clock).
 constexpr int kTraceTiles = 64, kTraceEvents = 8;
 unsigned long long* g_trace = nullptr;
 #define NTX_TRACE(role, it, ev)                                                                   \
     do {                                                                                          \
-        if (trace && blockIdx.x == 0 && blockIdx.y == 0 && (it) < kTraceTiles && lane == 0)       \
+        if (trace && blockIdx.x == 0 && un == 0 && (it) < kTraceTiles && lane == 0)               \
             trace[((role)*kTraceTiles + (it)) * kTraceEvents + (ev)] = clock64();                 \
     } while (0)
+
+#define NTX_TRACE_U(row, ev, val)                                                                  \
+    do {                                                                                          \
+        if (trace && blockIdx.x == 0 && warp == 0 && lane == 0 && (row) < kTraceTiles)            \
+            trace[(4 * kTraceTiles + (row)) * kTraceEvents + (ev)] = (val);                       \
+    } while (0)
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Work distribution of the backward tile pass.  The (row tile, column tile) pairs are numbered
+// row-major, t = rt * col_tiles + ct, and CTA c of `ctas` takes the contiguous range
+// [c*T/ctas, (c+1)*T/ctas): every CTA gets the same number of tiles to within one, whatever the
+// shape.  A CTA's range is cut at row-tile boundaries into *units*; each unit accumulates its own
+// partial of the row tile's  sum_b W_ab u_b  and stores it to slot  c - (first CTA touching that
+// row tile)  of acc_out, so the epilogue can add the partials of a row in a fixed order.
+struct BwdUnit {
+    int rt;    // row tile
+    int ct0;   // first column tile
+    int n;     // number of column tiles
+    int slot;  // partial slot of this row tile
+};
+__host__ __device__ __forceinline__ int64_t bwd_cta_of_tile(int64_t t, int64_t total, int ctas) {
+    return ((t + 1) * ctas - 1) / total;
+}
+__device__ __forceinline__ bool bwd_next_unit(int64_t& t, int64_t t_end, int col_tiles, int64_t total,
+                                              int ctas, BwdUnit& u) {
+    if (t >= t_end) return false;
+    u.rt = (int)(t / col_tiles);
+    const int64_t first = (int64_t)u.rt * col_tiles;
+    u.ct0 = (int)(t - first);
+    u.n = (int)min((int64_t)(col_tiles - u.ct0), t_end - t);
+    u.slot = (int)blockIdx.x - (int)bwd_cta_of_tile(first, total, ctas);
+    t += u.n;
+    return true;
+}
 
 template <int D, bool TF32, int MODE, bool kTwoExp>
 __global__ void __launch_bounds__(BwdCfg<D, TF32>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_t,
               const void* __restrict__ U_raw,
               const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
-              int64_t b_begin, int64_t b_count, float k_scale, int tiles_per_split, int col_tiles,
+              int64_t b_begin, int64_t b_count, float k_scale, int col_tiles, int64_t total_tiles,
               float* __restrict__ acc_out, unsigned long long* __restrict__ trace) {
     using C = Cfg<D, TF32>;
     using B = BwdCfg<D, TF32>;
@@ -402,8 +447,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     constexpr int NT = B::kTStages;
     uint8_t* k_tiles = smem;
     uint8_t* kt_tiles = smem + NS * C::kTileBytes;  // tf32 only: U^T tiles for the second MMA
-    float* colc = reinterpret_cast<float*>(kt_tiles + NT * B::kTTileBytes);  // [kCcTiles][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(colc + B::kCcTiles * kTile);
+    float* colc = reinterpret_cast<float*>(kt_tiles + NT * B::kTTileBytes);  // [2][kCcTiles][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(colc + 2 * B::kCcTiles * kTile);
     uint64_t* q_full = bars;
     uint64_t* k_full = bars + 1;
     uint64_t* k_empty = k_full + NS;
@@ -413,14 +458,24 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     uint64_t* s_free = s_full + 1;     // S buffer reusable: weight warps (SEP) or second MMA (aliased W)
     uint64_t* p_full = s_free + 1;     // [2] weights stored by all sixteen warps
     uint64_t* p_free = p_full + 2;     // [2] second MMA has consumed the W block (SEP only)
-    uint64_t* acc_full = p_free + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+    uint64_t* acc_full = p_free + 2;   // a unit's accumulator is complete (commit after its last W U)
+    uint64_t* acc_free = acc_full + 1; // ... and has been read out by all sixteen weight warps
+    uint64_t* cc_full = acc_free + 1;  // [2] a block of column constants is staged
+    uint64_t* cc_empty = cc_full + 2;  // [2] ... and all sixteen weight warps are done with it
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cc_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t a0 = a_begin + (int64_t)blockIdx.x * kTile;
+    NTX_TRACE_U(63, 0, clock64());
+    NTX_TRACE_U(63, 6, globaltimer_ns());
     const int64_t a_end = a_begin + a_count, b_end = b_begin + b_count;
-    const int jt0 = blockIdx.y * tiles_per_split;
-    const int n_tiles = min(tiles_per_split, col_tiles - jt0);
+    const int ctas = (int)gridDim.x;
+    const int64_t t_begin = (int64_t)blockIdx.x * total_tiles / ctas;
+    const int64_t t_end = (int64_t)(blockIdx.x + 1) * total_tiles / ctas;
+    // Every role walks the same units; `g` counts tiles across units (ring slots and barrier
+    // phases carry on from one unit to the next), `un` counts units.
+    int64_t t_next = t_begin;
+    BwdUnit u;
+    int g = 0, un = 0;
 
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmap);
@@ -431,6 +486,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         mbar_init(s_free, SEP ? 16 : 1);
         for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], 16); mbar_init(&p_free[b], 1); }
         mbar_init(acc_full, 1);
+        mbar_init(acc_free, 16);
+        for (int b = 0; b < 2; ++b) { mbar_init(&cc_full[b], 1); mbar_init(&cc_empty[b], 16); }
         fence_mbar_init();
     }
     if (warp == B::kMmaWarp) tmem_alloc<512>(tmem_slot);
@@ -438,23 +495,27 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    NTX_TRACE_U(63, 1, clock64());
 
     if (warp == B::kTmaWarp) {
         if (lane == 0) {
-            for (int it = 0; it < n_tiles; ++it) {
-                const int st = it % NS;
-                mbar_wait(&k_empty[st], ((it / NS) & 1) ^ 1);
-                mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
-                for (int a = 0; a < C::kAtoms; ++a)
-                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
-                                a * C::kAtomCols, (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile));
-                if (TF32) {  // the same columns of U^T: four [D rows x 32 columns] atoms
-                    const int tt = it & 1;
-                    mbar_wait(&kt_empty[tt], ((it >> 1) & 1) ^ 1);
-                    mbar_arrive_expect_tx(&kt_full[tt], B::kTTileBytes);
-                    for (int a = 0; a < 4; ++a)
-                        tma_load_2d(kt_tiles + tt * B::kTTileBytes + a * B::kTAtomBytes, &tmap_t, &kt_full[tt],
-                                    (int32_t)(b_begin + (int64_t)(jt0 + it) * kTile) + a * 32, 0);
+            while (bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u)) {
+                for (int it = 0; it < u.n; ++it, ++g) {
+                    const int st = g % NS;
+                    const int32_t col0 = (int32_t)(b_begin + (int64_t)(u.ct0 + it) * kTile);
+                    mbar_wait(&k_empty[st], ((g / NS) & 1) ^ 1);
+                    mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
+                    for (int a = 0; a < C::kAtoms; ++a)
+                        tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
+                                    a * C::kAtomCols, col0);
+                    if (TF32) {  // the same columns of U^T: four [D rows x 32 columns] atoms
+                        const int tt = g & 1;
+                        mbar_wait(&kt_empty[tt], ((g >> 1) & 1) ^ 1);
+                        mbar_arrive_expect_tx(&kt_full[tt], B::kTTileBytes);
+                        for (int a = 0; a < 4; ++a)
+                            tma_load_2d(kt_tiles + tt * B::kTTileBytes + a * B::kTAtomBytes, &tmap_t,
+                                        &kt_full[tt], col0 + a * 32, 0);
+                    }
                 }
             }
         }
@@ -463,43 +524,50 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         // S issuer.  The whole warp walks the loop (uniform control flow); one elected lane issues.
         const bool leader = elect_one();
         constexpr uint32_t idesc_s = idesc_op<TF32>(kTile, kTile, false);
-        mbar_wait(q_full, 0);
-        tc_fence_after();
-        for (int it = 0; it < n_tiles; ++it) {
-            const int st = it % NS;
-            NTX_TRACE(0, it, 0);
-            mbar_wait(&k_full[st], (it / NS) & 1);
-            // separate W blocks: free once the weight warps have read S(it-1); aliased W: free
-            // once the second MMA of tile it-1 has consumed the weights stored over it
-            mbar_wait(s_free, (it & 1) ^ 1);
+        for (; bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u); ++un) {
+            mbar_wait(q_full, un & 1);  // this unit's k U_a is parked in TMEM
             tc_fence_after();
-            NTX_TRACE(0, it, 2);
-            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
-            if (leader) {
+            for (int it = 0; it < u.n; ++it, ++g) {
+                const int st = g % NS;
+                NTX_TRACE(0, it, 0);
+                mbar_wait(&k_full[st], (g / NS) & 1);
+                // separate W blocks: free once the weight warps have read S(g-1); aliased W: free
+                // once the second MMA of tile g-1 has consumed the weights stored over it
+                mbar_wait(s_free, (g & 1) ^ 1);
+                tc_fence_after();
+                NTX_TRACE(0, it, 2);
+                const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+                if (leader) {
 #pragma unroll
-                for (int kk = 0; kk < C::kKSteps; ++kk)
-                    mma_ts_f16<TF32>(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk),
-                                     idesc_s, kk > 0);
-                if (TF32) tc_commit(&k_empty[st]);  // tf32: only this MMA reads the U_b tile
-                tc_commit(s_full);
+                    for (int kk = 0; kk < C::kKSteps; ++kk)
+                        mma_ts_f16<TF32>(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk),
+                                         idesc_s, kk > 0);
+                    if (TF32) tc_commit(&k_empty[st]);  // tf32: only this MMA reads the U_b tile
+                    tc_commit(s_full);
+                }
+                __syncwarp();
+                NTX_TRACE(0, it, 3);
             }
-            __syncwarp();
-            NTX_TRACE(0, it, 3);
         }
     } else if (warp == B::kMmaPvWarp) {
         // acc += W(it) U_b issuer
         const bool leader = elect_one();
         constexpr uint32_t idesc_pv = idesc_op<TF32>(kTile, D, /*b_mn_major=*/!TF32);
         constexpr int kPvSteps = kTile / C::kKPerMma;  // 8 (bf16) or 16 (tf32) MMAs over the tile's 128 K rows
-        for (int it = 0; it < n_tiles; ++it) {
-            const int st = it % NS;
-            const int pb = SEP ? (it & 1) : 0;
+        for (; bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u); ++un) {
+        if (un > 0) {  // the previous unit's accumulator has been read out
+            mbar_wait(acc_free, (un - 1) & 1);
+            tc_fence_after();
+        }
+        for (int it = 0; it < u.n; ++it, ++g) {
+            const int st = g % NS;
+            const int pb = SEP ? (g & 1) : 0;
             NTX_TRACE(0, it, 4);
-            mbar_wait(&p_full[pb], (SEP ? (it >> 1) : it) & 1);
+            mbar_wait(&p_full[pb], (SEP ? (g >> 1) : g) & 1);
             tc_fence_after();
             NTX_TRACE(0, it, 5);
-            if (TF32) mbar_wait(&kt_full[it & 1], (it >> 1) & 1);
-            const uint32_t k_addr = TF32 ? smem_u32(kt_tiles + (it & 1) * B::kTTileBytes)
+            if (TF32) mbar_wait(&kt_full[g & 1], (g >> 1) & 1);
+            const uint32_t k_addr = TF32 ? smem_u32(kt_tiles + (g & 1) * B::kTTileBytes)
                                          : smem_u32(k_tiles + st * C::kTileBytes);
             if (leader) {
 #pragma unroll
@@ -517,7 +585,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                     mma_ts_f16<TF32>(tmem_base + B::kAccCol, tmem_base + a_col, b_desc, idesc_pv,
                                      (it > 0) || (kk > 0));
                 }
-                tc_commit(TF32 ? &kt_empty[it & 1] : &k_empty[st]);
+                tc_commit(TF32 ? &kt_empty[g & 1] : &k_empty[st]);
                 tc_commit(SEP ? &p_free[pb] : s_free);
             }
             __syncwarp();
@@ -525,154 +593,231 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         }
         if (leader) tc_commit(acc_full);
         __syncwarp();
+        }
+    } else if (warp == B::kConstWarp) {
+        // column constants (l_b in base-2 units, or e_b = 2^-l_b), one block of kCcTiles tiles at a
+        // time; `cb` counts blocks across units
+        if (MODE != kRow) {
+            int cb = 0;
+            while (bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u)) {
+                for (int it0 = 0; it0 < u.n; it0 += B::kCcTiles, ++cb) {
+                    float* dst = colc + (cb & 1) * B::kCcTiles * kTile;
+                    const int ncols = min(B::kCcTiles, u.n - it0) * kTile;
+                    const int64_t c0 = b_begin + (int64_t)(u.ct0 + it0) * kTile;
+                    mbar_wait(&cc_empty[cb & 1], ((cb >> 1) & 1) ^ 1);
+                    // four columns per load, eight loads in flight per lane: two round trips per
+                    // full block (scalar loads when the range start is not 16-byte aligned)
+                    auto cval = [&](float l) {
+                        const float l2 = l * kLog2e;  // past the range (INFINITY): W = 0 either way
+                        return (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
+                    };
+                    const bool vec_ok = (c0 & 3) == 0;
+                    for (int base = 0; base < ncols; base += 8 * 128) {
+                        float4 l[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = base + j * 128 + lane * 4;
+                            l[j] = make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+                            if (c < ncols) {
+                                if (vec_ok && c0 + c + 3 < b_end) {
+                                    l[j] = __ldg(reinterpret_cast<const float4*>(lse + c0 + c));
+                                } else {
+                                    if (c0 + c < b_end) l[j].x = __ldg(lse + c0 + c);
+                                    if (c0 + c + 1 < b_end) l[j].y = __ldg(lse + c0 + c + 1);
+                                    if (c0 + c + 2 < b_end) l[j].z = __ldg(lse + c0 + c + 2);
+                                    if (c0 + c + 3 < b_end) l[j].w = __ldg(lse + c0 + c + 3);
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = base + j * 128 + lane * 4;
+                            if (c < ncols)
+                                *reinterpret_cast<float4*>(dst + c) =
+                                    make_float4(cval(l[j].x), cval(l[j].y), cval(l[j].z), cval(l[j].w));
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&cc_full[cb & 1]);
+                }
+            }
+        }
     } else {
         const int quad = warp & 3;
         const int quarter = warp >> 2;  // which 32 columns of every S tile
         const int row_in_tile = quad * 32 + lane;
         const int wt = threadIdx.x;  // 0..511: the weight threads come first
-        const int64_t row = a0 + row_in_tile;
-        const bool row_ok = row < a_end;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
         const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
 
-        // park k U_a in TMEM (bf16 pairs, or fp32 for tf32): column groups of the row dealt
-        // round-robin to the four warps that share this lane quadrant
-        if (TF32) {
-            const float4* src = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + row * D);
-            for (int g = quarter; g < D / 32; g += 4) {  // 32 columns = 32 floats = 8 x float4
-                uint32_t p[32];
+        // park k U_a of row tile `rt` in TMEM (bf16 pairs, or fp32 for tf32): column groups of the
+        // row dealt round-robin to the four warps that share this lane quadrant.  Called for the
+        // next unit once this warp has seen the last S tile of the current one complete, i.e. when
+        // no MMA reads the old rows any more.
+        auto park_q = [&](int rt) {
+            const int64_t row = a_begin + (int64_t)rt * kTile + row_in_tile;
+            if (TF32) {
+                const float4* src = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + row * D);
+                for (int gq = quarter; gq < D / 32; gq += 4) {  // 32 columns = 32 floats = 8 x float4
+                    uint32_t p[32];
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (row < M) t = __ldg(src + g * 8 + q);
-                    p[q * 4 + 0] = to_tf32(t.x * k_scale);
-                    p[q * 4 + 1] = to_tf32(t.y * k_scale);
-                    p[q * 4 + 2] = to_tf32(t.z * k_scale);
-                    p[q * 4 + 3] = to_tf32(t.w * k_scale);
+                    for (int q = 0; q < 8; ++q) {
+                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (row < M) t = __ldg(src + gq * 8 + q);
+                        p[q * 4 + 0] = to_tf32(t.x * k_scale);
+                        p[q * 4 + 1] = to_tf32(t.y * k_scale);
+                        p[q * 4 + 2] = to_tf32(t.z * k_scale);
+                        p[q * 4 + 3] = to_tf32(t.w * k_scale);
+                    }
+                    tmem_st32(lane_addr + B::kQCol + gq * 32, p);
                 }
-                tmem_st32(lane_addr + B::kQCol + g * 32, p);
-            }
-        } else {
-            const uint4* src =
-                reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(U_raw) + row * D);
-            for (int g = quarter; g < D / 32; g += 4) {  // 16 packed columns = 32 bf16 = 4 x uint4
-                uint32_t p[16];
+            } else {
+                const uint4* src =
+                    reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(U_raw) + row * D);
+                for (int gq = quarter; gq < D / 32; gq += 4) {  // 16 packed columns = 32 bf16 = 4 x uint4
+                    uint32_t p[16];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    uint4 t = make_uint4(0u, 0u, 0u, 0u);
-                    if (row < M) t = __ldg(src + g * 4 + q);
-                    const uint32_t raw[4] = {t.x, t.y, t.z, t.w};
+                    for (int q = 0; q < 4; ++q) {
+                        uint4 t = make_uint4(0u, 0u, 0u, 0u);
+                        if (row < M) t = __ldg(src + gq * 4 + q);
+                        const uint32_t raw[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)  // scaled by k = log2(e)/tau: S comes out as k u_a.u_b
-                        p[q * 4 + j] = pack_bf16(__uint_as_float(raw[j] << 16) * k_scale,
-                                                 __uint_as_float(raw[j] & 0xffff0000u) * k_scale);
+                        for (int j = 0; j < 4; ++j)  // scaled by k = log2(e)/tau: S comes out as k u_a.u_b
+                            p[q * 4 + j] = pack_bf16(__uint_as_float(raw[j] << 16) * k_scale,
+                                                     __uint_as_float(raw[j] & 0xffff0000u) * k_scale);
+                    }
+                    tmem_st16(lane_addr + B::kQCol + gq * 16, p);
                 }
-                tmem_st16(lane_addr + B::kQCol + g * 16, p);
             }
-        }
-        {
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(q_full);
-        }
-
-        // per-row constant: l_a in base-2 units, or 2^-l_a for the one-exponential form
-        float row_c = 0.f;
-        if (MODE != kCol) {
-            if (row_ok) {
-                const float l2 = lse[row] * kLog2e;
-                row_c = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
-            } else {
-                row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
-            }
-        }
-        // column constants (l_b in base-2 units, or e_b), staged kCcTiles tiles at a time
-        auto stage_cc = [&](int it0) {
-            named_bar_sync(1, B::kWeightThreads);  // everyone is done with the previous block
-            const int ncols = min(B::kCcTiles, n_tiles - it0) * kTile;
-            const int64_t c0 = b_begin + (int64_t)(jt0 + it0) * kTile;
-            for (int c = wt; c < ncols; c += B::kWeightThreads) {
-                float val = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;
-                if (c0 + c < b_end) {
-                    const float l2 = __ldg(lse + c0 + c) * kLog2e;
-                    val = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
-                }
-                colc[c] = val;
-            }
-            named_bar_sync(1, B::kWeightThreads);
         };
-        for (int it = 0; it < n_tiles; ++it) {
-            const int pb = SEP ? (it & 1) : 0;
-            const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
-            const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
-            if (MODE != kRow && (it % B::kCcTiles) == 0) stage_cc(it);
-            const float* cc = colc + (it % B::kCcTiles) * kTile + quarter * 32;
-            const uint32_t taddr = lane_addr + quarter * 32;  // this warp's 32 S columns
-            uint32_t v[32], packed[16];
-            (void)packed;
-            NTX_TRACE(trole, it, 0);
-            mbar_wait(s_full, it & 1);
-            tc_fence_after();
-            NTX_TRACE(trole, it, 1);
-            tmem_ld32(taddr, v);
-            tmem_ld_wait();
-            if (SEP) {  // S is in registers: the buffer can take S(it+1) already
+
+        bool have = bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u);
+        if (have) park_q(u.rt);
+        int cb = 0;  // column-constant blocks consumed so far
+        while (have) {
+            const int64_t a0 = a_begin + (int64_t)u.rt * kTile;
+            const int64_t row = a0 + row_in_tile;
+            const bool row_ok = row < a_end;
+            const int jt0 = u.ct0, n_tiles = u.n;
+            NTX_TRACE_U(un, 0, clock64());
+            NTX_TRACE_U(un, 7, (unsigned long long)n_tiles);
+
+            // per-row constant: l_a in base-2 units, or 2^-l_a for the one-exponential form
+            float row_c = 0.f;
+            if (MODE != kCol) {
+                if (row_ok) {
+                    const float l2 = lse[row] * kLog2e;
+                    row_c = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
+                } else {
+                    row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
+                }
+            }
+            for (int it = 0; it < n_tiles; ++it, ++g) {
+                const int pb = SEP ? (g & 1) : 0;
+                const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
+                const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
+                if (MODE != kRow && (it % B::kCcTiles) == 0)  // the block staged by the constants warp
+                    mbar_wait(&cc_full[cb & 1], (cb >> 1) & 1);
+                const float* cc = colc + ((cb & 1) * B::kCcTiles + it % B::kCcTiles) * kTile + quarter * 32;
+                const uint32_t taddr = lane_addr + quarter * 32;  // this warp's 32 S columns
+                uint32_t v[32], packed[16];
+                (void)packed;
+                NTX_TRACE(trole, it, 0);
+                mbar_wait(s_full, g & 1);
+                tc_fence_after();
+                NTX_TRACE(trole, it, 1);
+                if (it == 0) NTX_TRACE_U(un, 1, clock64());
+                tmem_ld32(taddr, v);
+                // W block pb was last read by the second MMA of tile g-2, issued a whole tile ago:
+                // checked here so that the barrier's latency hides under the TMEM load
+                if (SEP && g >= 2) mbar_wait(&p_free[pb], ((g - 2) >> 1) & 1);
+                tmem_ld_wait();
+                if (SEP) {  // S is in registers: the buffer can take the next S tile already
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(s_free);
+                }
+                NTX_TRACE(trole, it, 2);
+                if (TF32) {  // 32-bit weights, in place over the S values
+                    if (!special)
+                        weight_chunk<MODE, kTwoExp, false, false, 32>(v, v, cc, k_scale, row_c, 0, 0, 0);
+                    else
+                        weight_chunk<MODE, kTwoExp, true, false, 32>(v, v, cc, k_scale, row_c,
+                                                                     j0 + quarter * 32, row, b_end);
+                } else if (!special) {
+                    weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
+                } else {
+                    weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
+                                                      b_end);
+                }
+                NTX_TRACE(trole, it, 3);
+                if (SEP) {
+                    tc_fence_after();
+                    NTX_TRACE(trole, it, 4);
+                    tmem_st16(lane_addr + B::kPCol + pb * 64 + quarter * 16, packed);
+                } else if (TF32) {
+                    tmem_st32(taddr, v);  // 32 tf32 weights over the 32 S columns just consumed
+                } else {
+                    tmem_st16(taddr, packed);  // over the S columns just consumed
+                }
+                tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(s_free);
+                if (lane == 0) mbar_arrive(&p_full[pb]);
+                NTX_TRACE(trole, it, 5);
+                if (MODE != kRow && ((it + 1) % B::kCcTiles == 0 || it + 1 == n_tiles)) {
+                    if (lane == 0) mbar_arrive(&cc_empty[cb & 1]);  // (after the __syncwarp above)
+                    ++cb;
+                }
             }
-            NTX_TRACE(trole, it, 2);
-            if (TF32) {  // 32-bit weights, in place over the S values
-                if (!special)
-                    weight_chunk<MODE, kTwoExp, false, false, 32>(v, v, cc, k_scale, row_c, 0, 0, 0);
-                else
-                    weight_chunk<MODE, kTwoExp, true, false, 32>(v, v, cc, k_scale, row_c, j0 + quarter * 32,
-                                                                 row, b_end);
-            } else if (!special) {
-                weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
-            } else {
-                weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
-                                                  b_end);
-            }
-            NTX_TRACE(trole, it, 3);
-            if (SEP) {
-                // block pb was last read by the second MMA of tile it-2, issued a whole tile ago
-                if (it >= 2) mbar_wait(&p_free[pb], ((it - 2) >> 1) & 1);
-                tc_fence_after();
-                NTX_TRACE(trole, it, 4);
-                tmem_st16(lane_addr + B::kPCol + pb * 64 + quarter * 16, packed);
-            } else if (TF32) {
-                tmem_st32(taddr, v);  // 32 tf32 weights over the 32 S columns just consumed
-            } else {
-                tmem_st16(taddr, packed);  // over the S columns just consumed
-            }
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[pb]);
-            NTX_TRACE(trole, it, 5);
-        }
-        // epilogue: raw accumulator rows -> acc_out[split][row][D], 32-column groups round-robin
-        mbar_wait(acc_full, 0);
-        tc_fence_after();
-        const int64_t r = (int64_t)blockIdx.x * kTile + row_in_tile;
-        float* dst = acc_out + ((int64_t)blockIdx.y * a_count + r) * D;
-        for (int c = quarter; c < D / 32; c += 4) {
-            uint32_t v[32];
-            tmem_ld32(lane_addr + B::kAccCol + c * 32, v);
-            tmem_ld_wait();
-            if (r < a_count) {
+            // The S issuer can start on the next unit while this one's last W U runs and its
+            // accumulator is read out: hand it the next row tile first.
+            BwdUnit nu;
+            const bool have_next = bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, nu);
+            NTX_TRACE_U(un, 2, clock64());
+            if (have_next) park_q(nu.rt);
+            NTX_TRACE_U(un, 3, clock64());
+
+            // unit epilogue: raw accumulator rows -> acc_out[slot][row][D], 32-column groups
+            // round-robin; the accumulator is handed back as soon as the last group is in registers
+            mbar_wait(acc_full, un & 1);
+            tc_fence_after();
+            NTX_TRACE_U(un, 4, clock64());
+            const int64_t r = (int64_t)u.rt * kTile + row_in_tile;
+            float* dst = acc_out + ((int64_t)u.slot * a_count + r) * D;
+            auto release_acc = [&] {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc_free);
+            };
+            if (quarter >= D / 32) release_acc();
+            for (int c = quarter; c < D / 32; c += 4) {
+                uint32_t v[32];
+                tmem_ld32(lane_addr + B::kAccCol + c * 32, v);
+                tmem_ld_wait();
+                if (c + 4 >= D / 32) release_acc();
+                if (r < a_count) {
 #pragma unroll
-                for (int e = 0; e < 32; e += 4)
-                    *reinterpret_cast<float4*>(dst + c * 32 + e) =
-                        make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
-                                    __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+                    for (int e = 0; e < 32; e += 4)
+                        *reinterpret_cast<float4*>(dst + c * 32 + e) =
+                            make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
+                                        __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+                }
             }
+            NTX_TRACE_U(un, 5, clock64());
+            u = nu;
+            have = have_next;
+            ++un;
         }
     }
     tc_fence_before();
     __syncthreads();
+    NTX_TRACE_U(63, 2, clock64());
+    NTX_TRACE_U(63, 7, globaltimer_ns());
     if (warp == B::kMmaWarp) tmem_dealloc<512>(tmem_base);
 }
 
@@ -769,10 +914,10 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
     auto kern = tc_bwd_kernel<D, TF32, MODE, kTwoExp>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
-    kern<<<grid, B::kThreads, smem, stream>>>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count,
-                                             k_scale, (int)(plan.cols_per_split / kTile), col_tiles, acc,
-                                             g_trace);
+    const int64_t total_tiles = (int64_t)plan.row_tiles * col_tiles;
+    if (plan.sk_ctas < 1 || plan.sk_ctas > total_tiles) return cudaErrorInvalidValue;
+    kern<<<plan.sk_ctas, B::kThreads, smem, stream>>>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin,
+                                                     b_count, k_scale, col_tiles, total_tiles, acc, g_trace);
     return cudaGetLastError();
 }
 
@@ -815,9 +960,25 @@ SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, bool op_bf16, int
     return plan_splits(row_count, M, kTile, kTile, num_sms * per_sm, 32);
 }
 
+// One persistent CTA per SM, each with an equal share of the tiles (see BwdUnit).  nsplit = the
+// largest number of CTAs whose ranges touch one row tile = partial slots the epilogue may have to add.
 SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, int num_sms) {
     (void)M; (void)D;
-    return plan_splits(a_count, b_count, kTile, kTile, num_sms, 32);
+    SplitPlan p{};
+    p.row_tiles = (int)((a_count + kTile - 1) / kTile);
+    const int64_t col_tiles = std::max<int64_t>(1, (b_count + kTile - 1) / kTile);
+    const int64_t total = (int64_t)p.row_tiles * col_tiles;
+    p.sk_ctas = (int)std::min<int64_t>(std::max(num_sms, 1), total);
+    p.sk_col_tiles = (int)col_tiles;
+    p.cols_per_split = col_tiles * kTile;
+    p.nsplit = 1;
+    for (int rt = 0; rt < p.row_tiles; ++rt) {
+        const int64_t first = (int64_t)rt * col_tiles;
+        const int n = (int)(bwd_cta_of_tile(first + col_tiles - 1, total, p.sk_ctas) -
+                            bwd_cta_of_tile(first, total, p.sk_ctas)) + 1;
+        p.nsplit = std::max(p.nsplit, n);
+    }
+    return p;
 }
 
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,

@@ -10,12 +10,12 @@ ws = capi.workspace(M, D, z, 0)
 for _ in range(2):
     capi.forward_backward(z, tau, ws=ws)
 torch.cuda.synchronize()
-trace = torch.zeros(3 * 64 * 8, dtype=torch.int64, device="cuda")
+trace = torch.zeros(5 * 64 * 8, dtype=torch.int64, device="cuda")
 capi.lib().ntxent_b200_debug_set_trace(ctypes.c_void_p(trace.data_ptr()))
 capi.forward_backward(z, tau, ws=ws)
 torch.cuda.synchronize()
 capi.lib().ntxent_b200_debug_set_trace(None)
-t = trace.cpu().numpy().reshape(3, 64, 8)
+t = trace.cpu().numpy().reshape(5, 64, 8)
 t0 = t[0, 0, 0]
 names = ["MMA", "W0 ", "W15"]
 ev = {0: ["S:start", "kfull", "sfree", "S:issued", "PV:start", "pfull", "PV:issued"],
@@ -26,3 +26,15 @@ for it in list(range(0, 6)) + list(range(20, 26)):
         print(f"tile {it:2d} {names[r]}: " + "  ".join(f"{n}={v}" for n, v in vals))
 per_tile = (t[1, 40, 5] - t[1, 10, 5]) / 30
 print("steady-state clk per tile (W0 arrivals, tiles 10..40):", per_tile)
+
+# unit-level timeline of CTA 0 (weight warp 0)
+k = t[4, 63]
+cyc = int(k[2] - k[0]); ns = int(k[7] - k[6])
+print(f"kernel (CTA 0): {cyc} clk in {ns} ns -> {cyc / max(ns, 1):.3f} GHz; set-up {int(k[1] - k[0])} clk")
+for un in range(8):
+    r = t[4, un]
+    if not r[0]:
+        break
+    print(f"unit {un}: tiles={int(r[7])} start={int(r[0] - k[0])} first_S={int(r[1] - r[0])} tiles_done={int(r[2] - r[0])} "
+          f"q_parked=+{int(r[3] - r[2])} acc_full=+{int(r[4] - r[3])} drained=+{int(r[5] - r[4])} "
+          f"clk/tile={(int(r[2] - r[1])) / max(int(r[7]), 1):.1f}")
