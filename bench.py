@@ -63,7 +63,7 @@ def parse_args():
     ap.add_argument("--simt", action="store_true", help="force the fp32-FMA tile kernels")
     ap.add_argument("--bwd-mode", default="symmetric", choices=["symmetric", "contract"],
                     help="multi-GPU backward formulation")
-    ap.add_argument("--comm", default="symm", choices=["symm", "nccl"],
+    ap.add_argument("--comm", default="symm", choices=["symm", "symm-barrier", "nccl"],
                     help="multi-GPU exchange: kernels push into the peers' symmetric memory, or NCCL collectives")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

@@ -26,7 +26,8 @@ EXPORTS = [
     "ntxent_b200_rows_workspace_bytes", "ntxent_b200_forward_rows", "ntxent_b200_backward_rows",
     "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
     "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
-    "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push",
+    "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push", "ntxent_b200_peer_wait",
+    "ntxent_b200_backward_rows_dz",
 ]
 
 _lib = None
@@ -46,6 +47,21 @@ class PeerList(ctypes.Structure):
             pl.ptr[i] = int(p)
         pl.count = len(ptrs)
         return pl
+
+
+class PeerSignal(ctypes.Structure):
+    """ntxent_peer_signal: where a producing call publishes its call number on every rank."""
+    _fields_ = [("flags", PeerList), ("epoch", ctypes.c_void_p), ("rank", ctypes.c_int)]
+
+
+class PeerWait(ctypes.Structure):
+    """ntxent_peer_wait: the local flag array a consuming kernel polls, and the value to reach."""
+    _fields_ = [("flags", ctypes.c_void_p), ("epoch", ctypes.c_void_p), ("ranks", ctypes.c_int),
+                ("rows_per_rank", ctypes.c_int64)]
+
+
+def _ref(struct):
+    return ctypes.byref(struct) if struct is not None else None
 
 
 class NTXentError(RuntimeError):
@@ -97,9 +113,16 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_plan_info.argtypes = [i64, i64, i64, ci, u32, ip, ip, ip]
     pp = ctypes.POINTER(PeerList)
     L.ntxent_b200_normalize_push.restype = ci
-    L.ntxent_b200_normalize_push.argtypes = [vp, i64, i64, ci, u32, pp, i64, vp, vp]
+    ps, pw = ctypes.POINTER(PeerSignal), ctypes.POINTER(PeerWait)
+    L.ntxent_b200_normalize_push.argtypes = [vp, i64, i64, ci, u32, pp, i64, vp, ps, vp]
     L.ntxent_b200_forward_rows_push.restype = ci
-    L.ntxent_b200_forward_rows_push.argtypes = [vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, pp, pp, ci, vp]
+    L.ntxent_b200_forward_rows_push.argtypes = [vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, pp, pp, ci,
+                                                pw, ps, vp]
+    L.ntxent_b200_peer_wait.restype = ci
+    L.ntxent_b200_peer_wait.argtypes = [pw, vp]
+    L.ntxent_b200_backward_rows_dz.restype = ci
+    L.ntxent_b200_backward_rows_dz.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
+                                               vp, pw, vp]
     L.ntxent_b200_debug_set_trace.restype = ci
     L.ntxent_b200_debug_set_trace.argtypes = [vp]
     L.ntxent_b200_forward_static.restype = ci
@@ -327,8 +350,9 @@ def forward_static(z: torch.Tensor, tau: float, use_mixed_precision: bool = Fals
 
 
 def normalize_push(z_rows: torch.Tensor, u_all_peers: "PeerList", row_begin: int, flags: int = 0,
-                   inv_norm: torch.Tensor | None = None) -> torch.Tensor:
-    """Normalise this rank's rows and store them at `row_begin` of every rank's u_all; -> inv_norm."""
+                   inv_norm: torch.Tensor | None = None, signal: "PeerSignal | None" = None) -> torch.Tensor:
+    """Normalise this rank's rows and store them at `row_begin` of every rank's u_all; -> inv_norm.
+    With `signal` the kernel also publishes "rows landed" to every rank's flag array."""
     _require_cuda(z_rows)
     z_rows = z_rows.contiguous()
     rows, D = z_rows.shape
@@ -336,14 +360,18 @@ def normalize_push(z_rows: torch.Tensor, u_all_peers: "PeerList", row_begin: int
         if inv_norm is None:
             inv_norm = torch.empty(rows, dtype=torch.float32, device=z_rows.device)
         check(lib().ntxent_b200_normalize_push(_ptr(z_rows), rows, D, _dtype_code(z_rows), flags,
-                                               ctypes.byref(u_all_peers), row_begin, _ptr(inv_norm), _stream()))
+                                               ctypes.byref(u_all_peers), row_begin, _ptr(inv_norm),
+                                               _ref(signal), _stream()))
     return inv_norm
 
 
 def forward_rows_push(u_all: torch.Tensor, row_begin: int, row_count: int, tau: float,
                       lse_all_peers: "PeerList", loss_parts_peers: "PeerList", rank: int, flags: int = 0,
-                      ws: torch.Tensor | None = None) -> None:
-    """forward_rows whose l_i and partial loss are stored into every rank's lse_all / loss_parts."""
+                      ws: torch.Tensor | None = None, u_ready: "PeerWait | None" = None,
+                      lse_signal: "PeerSignal | None" = None) -> None:
+    """forward_rows whose l_i and partial loss are stored into every rank's lse_all / loss_parts.
+    `u_ready`: the tile kernel waits, tile by tile, for the peers' normalize_push; `lse_signal`:
+    publishes this call's results."""
     _require_cuda(u_all)
     M, D = u_all.shape
     with torch.cuda.device(u_all.device):
@@ -351,4 +379,30 @@ def forward_rows_push(u_all: torch.Tensor, row_begin: int, row_count: int, tau: 
         check(lib().ntxent_b200_forward_rows_push(_ptr(u_all), M, D, row_begin, row_count, float(tau),
                                                   _op_code(u_all), flags, _ptr(ws), ws.numel(),
                                                   ctypes.byref(lse_all_peers), ctypes.byref(loss_parts_peers),
-                                                  rank, _stream()))
+                                                  rank, _ref(u_ready), _ref(lse_signal), _stream()))
+
+
+def peer_wait(ready: "PeerWait", device) -> None:
+    """Make the current stream wait until every slot of `ready` has been published."""
+    with torch.cuda.device(device):
+        check(lib().ntxent_b200_peer_wait(ctypes.byref(ready), _stream()))
+
+
+def backward_rows_dz(u_all: torch.Tensor, lse_all: torch.Tensor, row_begin: int, row_count: int, tau: float,
+                     z_rows: torch.Tensor, inv_norm: torch.Tensor, grad_out: torch.Tensor | None = None,
+                     flags: int = 0, ws: torch.Tensor | None = None,
+                     lse_ready: "PeerWait | None" = None) -> torch.Tensor:
+    """Symmetric-form backward of rows [row_begin, row_begin+row_count) straight to dz (z dtype)."""
+    _require_cuda(u_all, lse_all, z_rows, inv_norm, grad_out)
+    M, D = u_all.shape
+    z_rows = z_rows.contiguous()
+    if grad_out is not None:
+        grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+    with torch.cuda.device(u_all.device):
+        ws = rows_workspace(M, D, row_count, u_all, flags) if ws is None else ws
+        dz = torch.empty_like(z_rows)
+        check(lib().ntxent_b200_backward_rows_dz(_ptr(u_all), _ptr(lse_all), M, D, row_begin, row_count,
+                                                 float(tau), _dtype_code(z_rows), flags, _ptr(ws), ws.numel(),
+                                                 _ptr(z_rows), _ptr(inv_norm), _ptr(grad_out), _ptr(dz),
+                                                 _ref(lse_ready), _stream()))
+    return dz

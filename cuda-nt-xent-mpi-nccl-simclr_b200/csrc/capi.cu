@@ -196,18 +196,19 @@ inline bool aligned(const void* p, uintptr_t a) { return (reinterpret_cast<uintp
 int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, const Plans& p, const RowsWs& w,
                           const PeerList& lse_outs, int64_t lse_offset, const PeerList& loss_outs,
-                          int loss_index, float loss_scale, cudaStream_t st) {
+                          int loss_index, float loss_scale, const PeerWait& u_ready,
+                          const PeerSignal& lse_signal, cudaStream_t st) {
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, w.counter, st));
+                              w.part_s, w.counter, u_ready, st));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
-                                w.part_s, w.counter, st));
+                                w.part_s, w.counter, u_ready, st));
     g_timer.stop(0, st);
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
                                      w.part_m, w.part_s, lse_outs, lse_offset, w.block_partials, loss_outs,
-                                     loss_index, loss_scale, st));
+                                     loss_index, loss_scale, lse_signal, st));
     return NTXENT_OK;
 }
 
@@ -215,8 +216,12 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
                      int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
                      float* loss_out, float loss_scale, cudaStream_t st) {
     return run_forward_rows_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p, w,
-                                 single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, st);
+                                 single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, no_wait(),
+                                 no_signal(), st);
 }
+
+bool to_peer_signal(const ntxent_peer_signal* in, PeerSignal* out);
+bool to_peer_wait(const ntxent_peer_wait* in, PeerWait* out);
 
 bool to_peer_list(const ntxent_peer_list* in, PeerList* out) {
     if (!in || in->count < 1 || in->count > NTXENT_MAX_PEERS || in->count > kMaxPeers) return false;
@@ -228,17 +233,40 @@ bool to_peer_list(const ntxent_peer_list* in, PeerList* out) {
     return true;
 }
 
+// NULL selects "off"; anything else must be complete.
+bool to_peer_signal(const ntxent_peer_signal* in, PeerSignal* out) {
+    *out = no_signal();
+    if (!in) return true;
+    if (!in->epoch || in->rank < 0 || in->rank >= kMaxPeers ||
+        !to_peer_list(&in->flags, &out->flags))
+        return false;
+    out->epoch = in->epoch;
+    out->rank = in->rank;
+    return true;
+}
+bool to_peer_wait(const ntxent_peer_wait* in, PeerWait* out) {
+    *out = no_wait();
+    if (!in) return true;
+    if (!in->flags || !in->epoch || in->ranks < 1 || in->ranks > kMaxPeers || in->rows_per_rank < 1)
+        return false;
+    out->flags = in->flags;
+    out->epoch = in->epoch;
+    out->ranks = in->ranks;
+    out->rows_per_rank = in->rows_per_rank;
+    return true;
+}
+
 int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                   int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float tau,
                   int mode, const Plans& p, const SplitPlan& plan, float* acc, float* ut,
-                  cudaStream_t st) {
+                  cudaStream_t st, const PeerWait& lse_ready = PeerWait{}) {
     g_timer.start(1, st);
     if (p.tc)
         NTX_TRY(tc_launch_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau,
-                              mode, p.flags, plan, acc, ut, st));
+                              mode, p.flags, plan, acc, ut, lse_ready, st));
     else
         NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
-                                tau, mode, plan, acc, st));
+                                tau, mode, plan, acc, lse_ready, st));
     g_timer.stop(1, st);
     return NTXENT_OK;
 }
@@ -381,14 +409,17 @@ int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, uns
 
 int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
                                const ntxent_peer_list* u_all_peers, int64_t row_begin,
-                               float* inv_norm_out, ntxent_stream_t stream) {
+                               float* inv_norm_out, const ntxent_peer_signal* u_signal,
+                               ntxent_stream_t stream) {
     PeerList outs{};
-    if (!z || rows < 0 || row_begin < 0 || !aligned(z, 16) || !to_peer_list(u_all_peers, &outs))
+    PeerSignal sig{};
+    if (!z || rows < 0 || row_begin < 0 || !aligned(z, 16) || !to_peer_list(u_all_peers, &outs) ||
+        !to_peer_signal(u_signal, &sig) || (u_signal && rows < 1))
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
     NTX_TRY(launch_normalize_push(z, dtype == NTXENT_BF16, rows, D, outs, row_begin,
-                                  op_is_bf16(dtype, flags), inv_norm_out, stream));
+                                  op_is_bf16(dtype, flags), inv_norm_out, sig, stream));
     return NTXENT_OK;
 }
 
@@ -397,10 +428,14 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
                                   void* workspace, size_t workspace_bytes,
                                   const ntxent_peer_list* lse_all_peers,
                                   const ntxent_peer_list* loss_parts_peers, int loss_index,
+                                  const ntxent_peer_wait* u_ready, const ntxent_peer_signal* lse_signal,
                                   ntxent_stream_t stream) {
     PeerList lse_outs{}, loss_outs{};
+    PeerWait wait{};
+    PeerSignal sig{};
     if (!u_all || !workspace || !to_peer_list(lse_all_peers, &lse_outs) ||
-        !to_peer_list(loss_parts_peers, &loss_outs) || loss_index < 0)
+        !to_peer_list(loss_parts_peers, &loss_outs) || loss_index < 0 || !to_peer_wait(u_ready, &wait) ||
+        !to_peer_signal(lse_signal, &sig) || (lse_signal && sig.flags.n != loss_outs.n))
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(u_all, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
@@ -412,7 +447,50 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     return run_forward_rows_push(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_outs, row_begin,
-                                 loss_outs, loss_index, 1.0f, stream);
+                                 loss_outs, loss_index, 1.0f, wait, sig, stream);
+}
+
+int ntxent_b200_peer_wait(const ntxent_peer_wait* ready, ntxent_stream_t stream) {
+    PeerWait wait{};
+    if (!ready || !to_peer_wait(ready, &wait)) return NTXENT_ERR_INVALID_ARGUMENT;
+    NTX_TRY(launch_peer_wait(wait, stream));
+    return NTXENT_OK;
+}
+
+int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                                 int64_t row_begin, int64_t row_count, float tau, int dtype,
+                                 unsigned flags, void* workspace, size_t workspace_bytes,
+                                 const void* z_rows, const float* inv_norm_rows, const float* grad_out,
+                                 void* dz_out, const ntxent_peer_wait* lse_ready,
+                                 ntxent_stream_t stream) {
+    PeerWait wait{};
+    if (!u_all || !lse_all || !workspace || !z_rows || !inv_norm_rows || !dz_out ||
+        !to_peer_wait(lse_ready, &wait))
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(u_all, 16) || !aligned(workspace, 256) || !aligned(z_rows, 16) || !aligned(dz_out, 16))
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags, tau);
+    const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau, kSym, p, p.bwd_rows,
+                       w.acc_rows, w.ut, stream, wait);
+    if (rc != NTXENT_OK) return rc;
+    BwdEpilogueArgs e{};
+    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit;
+    e.sk_ctas = p.bwd_rows.sk_ctas; e.sk_col_tiles = p.bwd_rows.sk_col_tiles;
+    e.u_all = u_all; e.op_bf16 = opb;
+    e.M = M; e.D = D; e.a_begin = row_begin; e.a_count = row_count;
+    e.pos_coeff = 2.f; e.pos_lo = 0; e.pos_hi = M;
+    e.scale = 1.0f / (tau * (float)M);
+    e.du_out = nullptr; e.z_rows = z_rows; e.z_bf16 = (dtype == NTXENT_BF16); e.inv_norm = inv_norm_rows;
+    e.grad_out = grad_out; e.dz_out = dz_out;
+    NTX_TRY(launch_bwd_epilogue(e, stream));
+    return NTXENT_OK;
 }
 
 int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,

@@ -31,6 +31,26 @@ inline PeerList single_peer(void* ptr) {
     return l;
 }
 
+// Cross-rank hand-off without a barrier kernel (multi-GPU push path).  Every rank owns an array
+// of per-producer flags in symmetric memory.  A producing call stores its results into all the
+// peers and then publishes its new epoch (a per-rank call counter kept in device memory, so that
+// a replayed CUDA graph needs no new arguments) to slot `rank` of every peer's array -- from the
+// one-block kernel that ends the call, i.e. after the grid that did the stores has completed.  A consuming kernel waits until the slots of the ranks whose rows it is about to
+// read have reached the consumer's own epoch (all ranks make the same sequence of calls).
+struct PeerSignal {
+    PeerList flags;         // uint32 flag array [kMaxPeers] on every rank (this rank's own included)
+    unsigned* epoch;        // local call counter; nullptr: no signalling
+    int rank;
+};
+struct PeerWait {
+    const unsigned* flags;  // this rank's flag array; nullptr: no waiting
+    const unsigned* epoch;  // local counter holding the value the slots must reach
+    int ranks;
+    int64_t rows_per_rank;  // rank r produced rows [r * rows_per_rank, (r + 1) * rows_per_rank)
+};
+inline PeerSignal no_signal() { PeerSignal s{}; return s; }
+inline PeerWait no_wait() { PeerWait w{}; return w; }
+
 struct SplitPlan {
     int row_tiles;       // tiles over the A range
     int nsplit;          // column splits (grid.y)
@@ -55,16 +75,19 @@ cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D
 // Same, storing the rows at row `row_offset` of every buffer in `outs`.
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
-                                  float* inv_norm, cudaStream_t stream);
+                                  float* inv_norm, const PeerSignal& signal, cudaStream_t stream);
 
 // SIMT (fp32 FMA) tile kernels.
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                             int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
-                            float* part_m, float* part_s, unsigned* counter, cudaStream_t stream);
+                            float* part_m, float* part_s, unsigned* counter, const PeerWait& u_ready,
+                            cudaStream_t stream);
 cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
                             int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
                             int64_t b_count, float tau, int mode, const SplitPlan& plan, float* acc,
-                            cudaStream_t stream);
+                            const PeerWait& lse_ready, cudaStream_t stream);
+// One warp that waits for every slot (for consumers that are not ours, e.g. a sum of the loss parts).
+cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream);
 
 // Forward finalize: combine the split partials into l_i, add the positive logit, reduce the loss.
 cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
@@ -78,7 +101,8 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
                                      const float* part_m, const float* part_s, const PeerList& lse_outs,
                                      int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
-                                     int loss_index, float loss_scale, cudaStream_t stream);
+                                     int loss_index, float loss_scale, const PeerSignal& signal,
+                                     cudaStream_t stream);
 
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
@@ -139,6 +163,54 @@ struct Elem<__nv_bfloat16> {
         *reinterpret_cast<uint2*>(p) = raw;
     }
 };
+
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Spin (bounded: a lost peer traps instead of hanging the GPU) until rank r's slot reaches `want`.
+__device__ __forceinline__ void peer_wait_rank(const PeerWait& w, int r, unsigned want) {
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(w.flags + r) - want) < 0) {
+        __nanosleep(40);
+        if (++spins > (1u << 27)) __trap();
+    }
+}
+// Ranks that produced rows [lo, hi): wait for those not yet seen ready (bit r of `ready_mask`).
+__device__ __forceinline__ void peer_wait_rows(const PeerWait& w, int64_t lo, int64_t hi, unsigned want,
+                                               unsigned& ready_mask) {
+    if (!w.flags || hi <= lo || ready_mask == 0xffffffffu) return;
+    const int r0 = (int)min((int64_t)w.ranks - 1, lo / w.rows_per_rank);
+    const int r1 = (int)min((int64_t)w.ranks - 1, (hi - 1) / w.rows_per_rank);
+    for (int r = r0; r <= r1; ++r)
+        if (!((ready_mask >> r) & 1u)) {
+            peer_wait_rank(w, r, want);
+            ready_mask |= 1u << r;
+        }
+}
+// Whole warp: one round trip that polls every rank's slot at once (lane r reads slot r); returns
+// the mask of ranks already published and the value to reach in `want`.  The common case -- all
+// there -- then costs a consumer CTA one L2 access instead of one per rank.
+__device__ __forceinline__ unsigned peer_poll_all_warp(const PeerWait& w, unsigned& want) {
+    want = 0u;
+    if (!w.flags) return 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    want = *w.epoch;
+    const bool ok = lane >= w.ranks || (int)(ld_acquire_sys(w.flags + lane) - want) >= 0;
+    return __ballot_sync(0xffffffffu, ok);
+}
+// Block-wide: wait for every rank (kernels without a dedicated loader warp).
+__device__ __forceinline__ void peer_wait_all_block(const PeerWait& w) {
+    if (!w.flags) return;
+    if ((int)threadIdx.x < w.ranks) peer_wait_rank(w, threadIdx.x, *w.epoch);
+    __syncthreads();
+}
+#endif
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -74,7 +74,7 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
 // launch costs less than the fence + same-address atomic of a last-CTA-done scheme here.
 __global__ void __launch_bounds__(1024)
 loss_reduce_kernel(const float* __restrict__ block_partials, int n, PeerList loss_outs, int loss_index,
-                   float loss_scale) {
+                   float loss_scale, PeerSignal signal) {
     __shared__ double red[1024];
     double acc = 0.0;
     for (int b = threadIdx.x; b < n; b += 1024) acc += (double)block_partials[b];
@@ -84,16 +84,38 @@ loss_reduce_kernel(const float* __restrict__ block_partials, int n, PeerList los
         if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0)
-        for (int i = 0; i < loss_outs.n; ++i)
-            static_cast<float*>(loss_outs.p[i])[loss_index] = (float)(red[0] * (double)loss_scale);
+    // Lane i serves peer i: the partial loss, then (multi-GPU push path) the flag.  This block runs
+    // after the finalize kernel has completed, so the signal covers every l_i stored by that
+    // kernel; each lane's release store orders its own loss store before its flag, and the peers
+    // are written in parallel rather than one NVLink round trip after the other.
+    if (threadIdx.x < 32) {
+        unsigned e = signal.epoch ? *signal.epoch + 1u : 0u;
+        __syncwarp();
+        if (threadIdx.x == 0 && signal.epoch) *signal.epoch = e;
+        if ((int)threadIdx.x < loss_outs.n) {
+            static_cast<float*>(loss_outs.p[threadIdx.x])[loss_index] = (float)(red[0] * (double)loss_scale);
+            if (signal.epoch)  // (the C-ABI checks that both lists name the same peers)
+                st_release_sys(static_cast<unsigned*>(signal.flags.p[threadIdx.x]) + signal.rank, e);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(32) peer_wait_kernel(PeerWait wait) {
+    if ((int)threadIdx.x < wait.ranks) peer_wait_rank(wait, threadIdx.x, *wait.epoch);
+}
+
+cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream) {
+    if (!wait.flags || !wait.epoch || wait.ranks < 1 || wait.ranks > 32) return cudaErrorInvalidValue;
+    peer_wait_kernel<<<1, 32, 0, stream>>>(wait);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
                                      const float* part_m, const float* part_s, const PeerList& lse_outs,
                                      int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
-                                     int loss_index, float loss_scale, cudaStream_t stream) {
+                                     int loss_index, float loss_scale, const PeerSignal& signal,
+                                     cudaStream_t stream) {
     dim3 grid((unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta)), block(256);
     if (op_bf16)
         fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
@@ -105,7 +127,8 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
             lse_outs, lse_offset, block_partials);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_outs, loss_index, loss_scale);
+    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_outs, loss_index, loss_scale,
+                                               signal);
     return cudaGetLastError();
 }
 
@@ -117,7 +140,7 @@ cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int6
     (void)counter;
     return launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, nsplit, part_m, part_s,
                                     single_peer(lse_rows), 0, block_partials, single_peer(loss_out), 0,
-                                    loss_scale, stream);
+                                    loss_scale, no_signal(), stream);
 }
 
 // -------------------------------------------------------------- bwd epilogue ---

@@ -129,7 +129,8 @@ template <int D, bool TF32, bool kOnline>
 __global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
               int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
-              float* __restrict__ part_m, float* __restrict__ part_s, unsigned* __restrict__ counter) {
+              float* __restrict__ part_m, float* __restrict__ part_s, unsigned* __restrict__ counter,
+              PeerWait u_ready) {
     using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
     extern __shared__ uint8_t smem_raw[];
@@ -167,13 +168,21 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == kFwdTmaWarp) {
+        // multi-GPU push path: a tile is loaded once the ranks that produced its rows have
+        // published them -- the CTA starts on the columns that are there instead of waiting
+        // behind a barrier for all of them
+        unsigned want;
+        unsigned ready_mask = peer_poll_all_warp(u_ready, want);
         if (lane == 0) {
+            peer_wait_rows(u_ready, a0, min(M, a0 + kTile), want, ready_mask);
             mbar_arrive_expect_tx(q_full, C::kTileBytes);
             for (int a = 0; a < C::kAtoms; ++a)
                 tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * C::kAtomCols, (int32_t)a0);
             for (int it = 0; it < n_tiles; ++it) {
                 const int st = it % NS;
                 const uint32_t ph = (it / NS) & 1;
+                const int64_t c0 = (int64_t)(jt0 + it) * kTile;
+                peer_wait_rows(u_ready, c0, min(M, c0 + kTile), want, ready_mask);
                 mbar_wait(&k_empty[st], ph ^ 1);
                 mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                 for (int a = 0; a < C::kAtoms; ++a)
@@ -437,7 +446,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
               const void* __restrict__ U_raw,
               const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int col_tiles, int64_t total_tiles,
-              float* __restrict__ acc_out, unsigned long long* __restrict__ trace) {
+              float* __restrict__ acc_out, unsigned long long* __restrict__ trace, PeerWait lse_ready) {
     using C = Cfg<D, TF32>;
     using B = BwdCfg<D, TF32>;
     constexpr int NS = B::kStages;
@@ -599,11 +608,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         // time; `cb` counts blocks across units
         if (MODE != kRow) {
             int cb = 0;
+            // multi-GPU push path: a block of l_b is read once the ranks that produced it have
+            // published it (the rows of the A range are this rank's own and need no wait)
+            unsigned want;
+            unsigned ready_mask = peer_poll_all_warp(lse_ready, want);
             while (bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u)) {
                 for (int it0 = 0; it0 < u.n; it0 += B::kCcTiles, ++cb) {
                     float* dst = colc + (cb & 1) * B::kCcTiles * kTile;
                     const int ncols = min(B::kCcTiles, u.n - it0) * kTile;
                     const int64_t c0 = b_begin + (int64_t)(u.ct0 + it0) * kTile;
+                    peer_wait_rows(lse_ready, c0, min(b_end, c0 + ncols), want, ready_mask);
                     mbar_wait(&cc_empty[cb & 1], ((cb >> 1) & 1) ^ 1);
                     // four columns per load, eight loads in flight per lane: two round trips per
                     // full block (scalar loads when the range start is not 16-byte aligned)
@@ -875,7 +889,7 @@ cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtens
 template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
-                         float* part_s, unsigned* counter, cudaStream_t stream) {
+                         float* part_s, unsigned* counter, const PeerWait& u_ready, cudaStream_t stream) {
     using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
     const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
@@ -885,7 +899,7 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
     kern<<<grid, kThreads, smem, stream>>>(tmap, M, row_begin, row_count, k_scale,
                                           (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s,
-                                          counter);
+                                          counter, u_ready);
     return cudaGetLastError();
 }
 
@@ -908,7 +922,7 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* acc,
-                         cudaStream_t stream) {
+                         const PeerWait& lse_ready, cudaStream_t stream) {
     using B = BwdCfg<D, TF32>;
     const int smem = max(B::kSmem, 120 * 1024);
     auto kern = tc_bwd_kernel<D, TF32, MODE, kTwoExp>;
@@ -917,7 +931,8 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
     const int64_t total_tiles = (int64_t)plan.row_tiles * col_tiles;
     if (plan.sk_ctas < 1 || plan.sk_ctas > total_tiles) return cudaErrorInvalidValue;
     kern<<<plan.sk_ctas, B::kThreads, smem, stream>>>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin,
-                                                     b_count, k_scale, col_tiles, total_tiles, acc, g_trace);
+                                                     b_count, k_scale, col_tiles, total_tiles, acc, g_trace,
+                                                     lse_ready);
     return cudaGetLastError();
 }
 
@@ -926,10 +941,10 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, int mode, bool two_exp, const SplitPlan& plan, int col_tiles,
-                         float* acc, cudaStream_t stream) {
+                         float* acc, const PeerWait& lse_ready, cudaStream_t stream) {
 #define NTX_BWD(MODE, TWO)                                                                               \
     launch_bwd_t<D, TF32, MODE, TWO>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, \
-                                     plan, col_tiles, acc, stream)
+                                     plan, col_tiles, acc, lse_ready, stream)
     if (mode == kRow) return NTX_BWD(kRow, false);
     if (mode == kCol) return NTX_BWD(kCol, false);
     return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
@@ -983,7 +998,8 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
-                          float* part_m, float* part_s, unsigned* counter, cudaStream_t stream) {
+                          float* part_m, float* part_s, unsigned* counter, const PeerWait& u_ready,
+                          cudaStream_t stream) {
     CUtensorMap tmap;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
@@ -992,9 +1008,9 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     const int col_tiles = (int)((M + kTile - 1) / kTile);
 #define NTX_FWD(DD, TF)                                                                                    \
     (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m,  \
-                                         part_s, counter, stream)                                          \
+                                         part_s, counter, u_ready, stream)                                 \
             : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                          part_s, counter, stream))
+                                          part_s, counter, u_ready, stream))
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_FWD(64, true);
@@ -1015,7 +1031,7 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          float* ut_scratch, cudaStream_t stream) {
+                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream) {
     CUtensorMap tmap, tmap_t;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
@@ -1035,7 +1051,7 @@ cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all,
     const int col_tiles = (int)((b_count + kTile - 1) / kTile);
 #define NTX_BWD_D(DD, TF)                                                                                   \
     launch_bwd_d<DD, TF>(tmap, tmap_t, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, \
-                         two_exp, plan, col_tiles, acc, stream)
+                         two_exp, plan, col_tiles, acc, lse_ready, stream)
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_BWD_D(64, true);

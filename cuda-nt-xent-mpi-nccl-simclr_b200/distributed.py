@@ -53,37 +53,55 @@ class CudaBackend:
 
 
 class _SymmetricBuffers:
-    """Two rotating sets of (u_all, lse_all, loss_parts) in symmetric memory: every rank maps every
-    other rank's copy, so the kernels can store their results into all of them directly
-    (ntxent_b200_normalize_push / _forward_rows_push) and the NCCL all-gather / all-reduce disappear;
-    what remains between producers and consumers is one device-side barrier.  Two sets, because a
-    fast rank may already push step t+1 while a slow one still reads step t."""
+    """Two rotating sets of (u_all, lse_all, loss_parts, flags) in symmetric memory: every rank maps
+    every other rank's copy, so the kernels store their results into all of them directly
+    (ntxent_b200_normalize_push / _forward_rows_push) and the NCCL all-gather / all-reduce
+    disappear.  Producers and consumers are ordered by per-rank flags the kernels themselves
+    publish and poll (include/ntxent_b200.h, ntxent_peer_signal / ntxent_peer_wait): no barrier
+    kernel, and a consumer starts on the rows that have arrived.  Two sets, because a fast rank
+    may already push step t+1 while a slow one still reads step t; by the time it pushes step
+    t+2 into the first set again it has waited for every peer's step-t+1 push, which those peers
+    issue after they are done with step t."""
 
-    def __init__(self, M, D, op_dtype, world, device, group):
+    def __init__(self, M, D, op_dtype, world, rank, device, group):
         import torch.distributed._symmetric_memory as symm_mem
         item = torch.empty(0, dtype=op_dtype).element_size()
         al = lambda n: (n + 255) // 256 * 256  # noqa: E731
-        u_bytes, lse_bytes, loss_bytes = al(M * D * item), al(M * 4), 256
-        set_bytes = u_bytes + lse_bytes + loss_bytes
+        u_bytes, lse_bytes, loss_bytes, sync_bytes = al(M * D * item), al(M * 4), 256, 256
+        set_bytes = u_bytes + lse_bytes + loss_bytes + sync_bytes
         self.buf = symm_mem.empty(2 * set_bytes, dtype=torch.uint8, device=device)
         self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
         bases = [int(p) for p in self.hdl.buffer_ptrs]
         if len(bases) != world:
             raise capi.NTXentError("symmetric-memory rendezvous returned an unexpected number of peers")
+        # flags and counters start at zero on every rank before anybody publishes anything
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.hdl.barrier(channel=0)
+        torch.cuda.synchronize(device)
+        local = bases[rank]
+        rows = M // world
         self.sets = []
         for k in range(2):
             o = k * set_bytes
+            o_lse, o_loss = o + u_bytes, o + u_bytes + lse_bytes
+            o_sync = o_loss + loss_bytes  # flag_u[16] | flag_lse[16] | epoch_u . epoch_lse
+            sig_u, sig_lse = capi.PeerSignal(), capi.PeerSignal()
+            sig_u.flags = capi.PeerList.of([b + o_sync for b in bases])
+            sig_u.epoch, sig_u.rank = local + o_sync + 128, rank
+            sig_lse.flags = capi.PeerList.of([b + o_sync + 64 for b in bases])
+            sig_lse.epoch, sig_lse.rank = local + o_sync + 136, rank
+            wait_u = capi.PeerWait(local + o_sync, local + o_sync + 128, world, rows)
+            wait_lse = capi.PeerWait(local + o_sync + 64, local + o_sync + 136, world, rows)
             self.sets.append(dict(
                 u_all=self.buf[o:o + M * D * item].view(op_dtype).view(M, D),
-                lse_all=self.buf[o + u_bytes:o + u_bytes + M * 4].view(torch.float32),
-                loss_parts=self.buf[o + u_bytes + lse_bytes:o + u_bytes + lse_bytes + 4 * world].view(torch.float32),
+                lse_all=self.buf[o_lse:o_lse + M * 4].view(torch.float32),
+                loss_parts=self.buf[o_loss:o_loss + 4 * world].view(torch.float32),
                 u_peers=capi.PeerList.of([b + o for b in bases]),
-                lse_peers=capi.PeerList.of([b + o + u_bytes for b in bases]),
-                loss_peers=capi.PeerList.of([b + o + u_bytes + lse_bytes for b in bases])))
+                lse_peers=capi.PeerList.of([b + o_lse for b in bases]),
+                loss_peers=capi.PeerList.of([b + o_loss for b in bases]),
+                sig_u=sig_u, sig_lse=sig_lse, wait_u=wait_u, wait_lse=wait_lse))
         self.step = 0
-
-    def barrier(self, channel: int) -> None:
-        self.hdl.barrier(channel=channel)
 
 
 def _reduce_scatter_sum(out: torch.Tensor, inp: torch.Tensor, group) -> None:
@@ -124,16 +142,18 @@ class RowPartitionedNTXent:
         op_dtype = torch.bfloat16 if (dtype == torch.bfloat16 or use_mixed_precision) else torch.float32
         if hasattr(self.backend, "operand_dtype"):  # test doubles may keep wider operands
             op_dtype = self.backend.operand_dtype(dtype)
-        if comm not in ("nccl", "symm"):
-            raise ValueError("comm must be 'nccl' (all-gather / all-reduce collectives) or 'symm' "
-                             "(results pushed into the peers' symmetric memory by the kernels)")
+        if comm not in ("nccl", "symm", "symm-barrier"):
+            raise ValueError("comm must be 'nccl' (all-gather / all-reduce collectives), 'symm' (results "
+                             "pushed into the peers' symmetric memory by the kernels, which also order "
+                             "themselves through flags) or 'symm-barrier' (the same stores, ordered by "
+                             "symmetric-memory barrier kernels)")
         self.comm = comm if self.world > 1 else "nccl"
         self.flags = flags
         self.symm = None
-        if self.comm == "symm":
+        if self.comm != "nccl":
             if backend is not None:
                 raise ValueError("comm='symm' needs the CUDA backend")
-            self.symm = _SymmetricBuffers(self.M, self.D, op_dtype, self.world, self.device, group)
+            self.symm = _SymmetricBuffers(self.M, self.D, op_dtype, self.world, self.rank, self.device, group)
         self.u_all = torch.empty(self.M, self.D, dtype=op_dtype, device=self.device)
         self.lse_all = torch.empty(self.M, dtype=torch.float32, device=self.device)
         self.du_col_local = torch.empty(self.rows, self.D, dtype=torch.float32, device=self.device)
@@ -147,7 +167,12 @@ class RowPartitionedNTXent:
         # CUDA-graph replay of the whole step (kernels and collectives): at 4-8 ranks the step is
         # ~0.1-0.2 ms of GPU work behind ~0.3 ms of host-side launches, so the host has to go
         self.use_cuda_graph = bool(use_cuda_graph)
-        self._graph = None
+        self._graphs = {}
+        self._gstep = 0
+        if self.symm is not None and lc:
+            signal = 1 if self.comm == "symm" else 0  # the one-block kernel that publishes U
+            self.launches_per_step = (lc["normalize"] + signal + lc["forward_rows"] +
+                                      (2 if sym else lc["backward_rows_contract"] + lc["finalize_dz"] + signal))
 
     # -- forward -------------------------------------------------------------------------
     def forward(self, z_local: torch.Tensor):
@@ -157,7 +182,7 @@ class RowPartitionedNTXent:
         if tuple(z_local.shape) != (self.rows, self.D):
             raise ValueError(f"rank {self.rank} expects a [{self.rows}, {self.D}] shard, got {tuple(z_local.shape)}")
         if self.symm is not None:
-            return self._forward_symm(z_local)
+            return self._forward_symm(z_local, defer_loss=False)
         u_local, inv_norm = self.backend.normalize(z_local)
         if self.world > 1:
             dist.all_gather_into_tensor(self.u_all, u_local.contiguous(), group=self.group)
@@ -180,19 +205,34 @@ class RowPartitionedNTXent:
             self.lse_all.copy_(lse_local)
         return loss, (z_local, inv_norm)
 
-    def _forward_symm(self, z_local: torch.Tensor):
-        """Forward with the collectives fused into the kernels: peer stores + two barriers."""
+    def _forward_symm(self, z_local: torch.Tensor, defer_loss: bool):
+        """Forward with the exchange inside the kernels: normalize_push publishes "my rows have
+        landed", the forward tile kernel loads a column tile once its producers have published,
+        the finalize/loss kernels publish l and the partial loss.  With defer_loss the loss parts
+        are summed after the backward kernel (which waits for the same flags); otherwise a
+        one-warp wait kernel orders the sum."""
         sy = self.symm
-        cur = sy.sets[sy.step & 1]
+        k = sy.step & 1
+        cur = sy.sets[k]
         sy.step += 1
-        inv_norm = capi.normalize_push(z_local, cur["u_peers"], self.row_begin, self.flags)
-        sy.barrier(0)  # every rank's rows have landed in this rank's u_all
         self.u_all, self.lse_all = cur["u_all"], cur["lse_all"]
+        if self.comm == "symm-barrier":
+            inv_norm = capi.normalize_push(z_local, cur["u_peers"], self.row_begin, self.flags)
+            sy.hdl.barrier(channel=0)  # every rank's rows have landed in this rank's u_all
+            capi.forward_rows_push(self.u_all, self.row_begin, self.rows, self.tau, cur["lse_peers"],
+                                   cur["loss_peers"], self.rank, self.flags, self.ws)
+            sy.hdl.barrier(channel=1)  # ... and every rank's l and partial loss
+            return cur["loss_parts"].sum(dim=0, keepdim=True), (z_local, inv_norm, k)
+        inv_norm = capi.normalize_push(z_local, cur["u_peers"], self.row_begin, self.flags,
+                                       signal=cur["sig_u"])
         capi.forward_rows_push(self.u_all, self.row_begin, self.rows, self.tau, cur["lse_peers"],
-                               cur["loss_peers"], self.rank, self.flags, self.ws)
-        sy.barrier(1)  # ... and every rank's l and partial loss
-        loss = cur["loss_parts"].sum(dim=0, keepdim=True)
-        return loss, (z_local, inv_norm)
+                               cur["loss_peers"], self.rank, self.flags, self.ws,
+                               u_ready=cur["wait_u"], lse_signal=cur["sig_lse"])
+        loss = None
+        if not defer_loss:
+            capi.peer_wait(cur["wait_lse"], self.device)
+            loss = cur["loss_parts"].sum(dim=0, keepdim=True)
+        return loss, (z_local, inv_norm, k)
 
     def _join_loss(self, loss: torch.Tensor) -> torch.Tensor:
         work, self._pending_loss = getattr(self, "_pending_loss", None), None
@@ -202,7 +242,14 @@ class RowPartitionedNTXent:
 
     # -- backward ------------------------------------------------------------------------
     def backward(self, state, grad_out: torch.Tensor | None = None) -> torch.Tensor:
-        z_local, inv_norm = state
+        z_local, inv_norm = state[0], state[1]
+        if self.symm is not None:
+            cur = self.symm.sets[state[2]]
+            self.u_all, self.lse_all = cur["u_all"], cur["lse_all"]
+            if self.mode == "symmetric":  # tile kernel waits for the peers' l, epilogue emits dz
+                return capi.backward_rows_dz(self.u_all, self.lse_all, self.row_begin, self.rows, self.tau,
+                                             z_local, inv_norm, grad_out, self.flags, self.ws,
+                                             lse_ready=cur["wait_lse"] if self.comm == "symm" else None)
         if self.mode == "symmetric":
             du_rows, _ = self.backend.backward_rows(self.u_all, self.lse_all, self.row_begin, self.rows,
                                                     self.tau, capi.BWD_SYMMETRIC, self.ws)
@@ -219,47 +266,60 @@ class RowPartitionedNTXent:
     def forward_backward(self, z_local: torch.Tensor, grad_out: torch.Tensor | None = None):
         if self.use_cuda_graph and z_local.is_cuda:
             return self._replay(z_local, grad_out)
+        return self._step(z_local, grad_out)
+
+    def _step(self, z_local, grad_out):
+        if self.comm == "symm" and self.mode == "symmetric":
+            _, state = self._forward_symm(z_local, defer_loss=True)
+            dz = self.backward(state, grad_out)
+            # the backward tile kernel has waited for every rank's l and partial loss
+            loss = self.symm.sets[state[2]]["loss_parts"].sum(dim=0, keepdim=True)
+            return loss / self.M, dz
         loss, state = self.forward(z_local)
         dz = self.backward(state, grad_out)
         return self._join_loss(loss), dz
 
     def release(self) -> None:
-        """Drop the captured graph and its static buffers.  Call this before
+        """Drop the captured graphs and their static buffers.  Call this before
         torch.distributed.destroy_process_group(): tearing a NCCL communicator down while a
         live CUDA graph still holds its kernels hangs."""
-        self._graph = None
-        self._z_static = self._g_static = self._loss_static = self._dz_static = None
+        self._graphs = {}
+        self._z_static = self._g_static = None
         if torch.cuda.is_available():
             torch.cuda.synchronize()
 
     def _replay(self, z_local, grad_out):
-        """Capture forward+backward once (static buffers), then copy-in + replay.  The returned
-        loss / dz are the graph's static outputs: consume them before the next call."""
-        if self._graph is None:
+        """Capture forward+backward once per buffer set (static inputs), then copy-in + replay.
+        The returned loss / dz are the graph's static outputs: consume them before the call
+        after next."""
+        k = (self._gstep & 1) if self.symm is not None else 0
+        self._gstep += 1
+        if not self._graphs:
             self._z_static = z_local.detach().clone()
             self._g_static = torch.ones(1, dtype=torch.float32, device=z_local.device)
             side = torch.cuda.Stream(device=z_local.device)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                for _ in range(3):  # warm-up on the side stream (NCCL communicators, lazy inits)
-                    loss, state = self.forward(self._z_static)
-                    self.backward(state, self._g_static)
-                    self._join_loss(loss)
+                for _ in range(2):  # warm-up on the side stream (communicators, lazy inits); both sets
+                    self._step(self._z_static, self._g_static)
             torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+        if k not in self._graphs:
+            if self.symm is not None:
+                self.symm.step = k  # the captured kernels are bound to buffer set k
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                loss, state = self.forward(self._z_static)
-                dz = self.backward(state, self._g_static)
-                loss = self._join_loss(loss)
-            self._graph, self._loss_static, self._dz_static = graph, loss, dz
+                loss, dz = self._step(self._z_static, self._g_static)
+            self._graphs[k] = (graph, loss, dz)
         self._z_static.copy_(z_local, non_blocking=True)
         if grad_out is None:
             self._g_static.fill_(1.0)
         else:
             self._g_static.copy_(grad_out.reshape(-1)[:1], non_blocking=True)
-        self._graph.replay()
-        return self._loss_static, self._dz_static
+        graph, loss, dz = self._graphs[k]
+        graph.replay()
+        return loss, dz
 
 
 class _DistributedNTXentFunction(torch.autograd.Function):

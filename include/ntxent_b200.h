@@ -142,31 +142,74 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
  * Instead of producing a local result and all-gathering it with NCCL, these
  * variants store the result straight into every rank's copy: `peers` lists the
  * device pointers of the SAME buffer on each rank (this rank's own included),
- * as mapped into this process.  The caller separates producer and consumers
- * with one cross-rank barrier.  No counterpart in the reference (it has no
- * communication code at all, CMakeLists.txt:13-14,41-47). */
+ * as mapped into this process.  No counterpart in the reference (it has no
+ * communication code at all, CMakeLists.txt:13-14,41-47).
+ *
+ * Producer and consumers are ordered either by a cross-rank barrier the caller
+ * puts between them (pass NULL for the signal/wait arguments), or by the
+ * kernels themselves: every rank keeps an array of per-producer flags in
+ * symmetric memory; a producing call publishes its call number (`epoch`, a
+ * device-side counter, so a replayed CUDA graph needs no new arguments) to slot
+ * `rank` of every peer's array once the grid that did the peer stores has
+ * completed (a one-block kernel at the end of the call), and a consuming
+ * kernel waits -- tile by tile, only for the ranks whose rows that tile reads --
+ * until those slots have reached the consumer's own call number.  All ranks
+ * must make the same sequence of calls.  The flag arrays and `epoch` start at
+ * zero and belong to the library afterwards; a wait that is never satisfied (a
+ * lost peer) traps after a few seconds instead of hanging the GPU. */
 #define NTXENT_MAX_PEERS 16
 typedef struct {
     void* ptr[NTXENT_MAX_PEERS];
     int count;
 } ntxent_peer_list;
+typedef struct {
+    ntxent_peer_list flags; /* uint32_t[NTXENT_MAX_PEERS] on every rank (own included) */
+    uint32_t* epoch;        /* this rank's call counter for this signal (device memory) */
+    int rank;               /* slot this rank publishes to */
+} ntxent_peer_signal;
+typedef struct {
+    const uint32_t* flags;  /* this rank's copy of the flag array */
+    const uint32_t* epoch;  /* the counter of the matching signal on this rank */
+    int ranks;
+    int64_t rows_per_rank;  /* rank r produced rows [r*rows_per_rank, (r+1)*rows_per_rank) */
+} ntxent_peer_wait;
 
 /* ntxent_b200_normalize whose rows land at row `row_begin` of every rank's
  * gathered u_all [M, D] (replaces normalise + all-gather of U). */
 int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype, unsigned flags,
                                const ntxent_peer_list* u_all_peers, int64_t row_begin,
-                               float* inv_norm_out, ntxent_stream_t stream);
+                               float* inv_norm_out, const ntxent_peer_signal* u_signal,
+                               ntxent_stream_t stream);
 
 /* ntxent_b200_forward_rows whose l_i land at element row_begin + i of every
  * rank's lse_all float[M] and whose partial loss lands at element `loss_index`
  * (the rank) of every rank's loss_parts float[ranks] (replaces the all-gather
- * of l and the all-reduce of the loss). */
+ * of l and the all-reduce of the loss).  `u_ready` (optional) makes the tile
+ * kernel wait for the peers' normalize_push; `lse_signal` (optional) publishes
+ * this call's l and partial loss. */
 int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64_t row_begin,
                                   int64_t row_count, float tau, int dtype, unsigned flags,
                                   void* workspace, size_t workspace_bytes,
                                   const ntxent_peer_list* lse_all_peers,
                                   const ntxent_peer_list* loss_parts_peers, int loss_index,
+                                  const ntxent_peer_wait* u_ready, const ntxent_peer_signal* lse_signal,
                                   ntxent_stream_t stream);
+
+/* One tiny kernel that waits for every slot of `ready` (for consumers that are
+ * not this library's kernels, e.g. the sum of loss_parts after a forward-only
+ * call). */
+int ntxent_b200_peer_wait(const ntxent_peer_wait* ready, ntxent_stream_t stream);
+
+/* Symmetric-form backward for rows [row_begin, row_begin+row_count) straight to
+ * dz (ntxent_b200_backward_rows + ntxent_b200_finalize_dz in two launches
+ * instead of three).  `lse_ready` (optional) makes the tile kernel wait for the
+ * peers' forward_rows_push, block of columns by block of columns. */
+int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                                 int64_t row_begin, int64_t row_count, float tau, int dtype,
+                                 unsigned flags, void* workspace, size_t workspace_bytes,
+                                 const void* z_rows, const float* inv_norm_rows, const float* grad_out,
+                                 void* dz_out, const ntxent_peer_wait* lse_ready,
+                                 ntxent_stream_t stream);
 
 /* Normalisation Jacobian: dz_i = g (dU_i - (dU_i . u_i) u_i) * inv_norm_i with
  * u_i = z_i * inv_norm_i.  z_rows, dz_out in `dtype`; g = *grad_out (NULL: 1). */

@@ -61,7 +61,28 @@ def _worker(rank, world, port, M, D, tau, mode, dtype_name, out_dir):
         for _ in range(3):
             loss_s, dz_s = eng_s.forward_backward(shard)
         torch.cuda.synchronize()
-        assert torch.allclose(loss_s, loss, rtol=1e-6) and torch.equal(dz_s, dz)
+        # (the symmetric form applies the normalisation Jacobian inside the backward epilogue
+        # there, so dz agrees to rounding rather than bit for bit)
+        tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+        assert torch.allclose(loss_s, loss, rtol=1e-6)
+        assert (dz_s.float() - dz.float()).abs().max() <= tol * dz.float().abs().max()
+        # forward-only + separate backward through the autograd wrapper on the same engine
+        zs = shard.clone().requires_grad_(True)
+        ls = distributed_ntxent_loss(zs, tau, engine=eng_s)
+        ls.backward()
+        torch.cuda.synchronize()
+        assert torch.allclose(ls.detach().reshape(1), loss.reshape(1), rtol=1e-6)
+        assert torch.equal(zs.grad, dz_s)
+        # and its graph replay (one graph per buffer set), bit for bit over several steps
+        eng_sg = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
+                                      comm="symm", use_cuda_graph=True)
+        same = True
+        for _ in range(5):
+            loss_sg, dz_sg = eng_sg.forward_backward(shard)
+            torch.cuda.synchronize()
+            same = same and torch.equal(loss_sg, loss_s) and torch.equal(dz_sg, dz_s)
+        eng_sg.release()
+        assert same
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), loss=loss.float().cpu().numpy(),
                  dz=dz.float().cpu().numpy(), dz_ag=zr.grad.float().cpu().numpy())
     finally:
