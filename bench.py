@@ -271,8 +271,16 @@ def run_native(args):
         launches_per_step = 6  # normalise, forward tiles, finalize, loss reduce, backward tiles, epilogue
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent
-        engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
-                                      use_cuda_graph=not args.no_graph, comm=args.comm)
+        comm_used, comm_note = args.comm, None
+        try:
+            engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
+                                          use_cuda_graph=not args.no_graph, comm=args.comm)
+        except Exception as exc:  # no peer mappings on this box: every rank fails the same rendezvous
+            if args.comm == "nccl":
+                raise
+            comm_used, comm_note = "nccl", f"{args.comm} unavailable: {type(exc).__name__}: {str(exc)[:120]}"
+            engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
+                                          use_cuda_graph=not args.no_graph, comm="nccl")
 
         def step(zin):
             return engine.forward_backward(zin)[0]
@@ -402,7 +410,7 @@ def run_native(args):
                    "rows_per_gpu": rows, "flop_model": "8*M^2*D per step (BASELINE.md section 3)",
                    "l2_flush_between_steps": flush is not None, "plan": plan,
                    "backward_mode": "symmetric" if world == 1 else args.bwd_mode,
-                   "cuda_graph": bool(graph_mode), "comm": args.comm if world > 1 else None},
+                   "cuda_graph": bool(graph_mode), "comm": (comm_used if comm_note is None else f"{comm_used} ({comm_note})") if world > 1 else None},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": z_host.numel() * z_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": launches_per_step * args.steps,

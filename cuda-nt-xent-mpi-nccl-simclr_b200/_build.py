@@ -15,6 +15,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libntxent_b200.so")
+LIB_PATH_TRACE = LIB_PATH[:-3] + "_trace.so"
 BINDING_PATH = os.path.join(PKG_DIR, "ntxent_cuda.so")
 
 KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu"]
@@ -40,18 +41,23 @@ def _stale(target: str, sources) -> bool:
     return any(os.path.getmtime(s) > t for s in sources)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
-    """nvcc -> libntxent_b200.so (all kernels + the extern "C" boundary)."""
+def build_library(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """nvcc -> libntxent_b200.so (all kernels + the extern "C" boundary).  trace=True builds the
+    variant with the pipeline time stamps compiled in (libntxent_b200_trace.so, for
+    tools/trace_bwd.py; loaded instead of the product library when NTXENT_TRACE=1)."""
     srcs = [os.path.join(CSRC, s) for s in KERNEL_SOURCES]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     deps.append(os.path.join(REPO_DIR, "include", "ntxent_b200.h"))
-    if force or _stale(LIB_PATH, deps):
+    lib_path = LIB_PATH_TRACE if trace else LIB_PATH
+    if force or _stale(lib_path, deps):
         objs = []
         procs = []
         for s in srcs:
-            o = os.path.join(CSRC, os.path.basename(s)[:-3] + ".o")
+            o = os.path.join(CSRC, os.path.basename(s)[:-3] + (".trace.o" if trace else ".o"))
             objs.append(o)
             cmd = [_nvcc(), *NVCC_FLAGS, "-I", os.path.join(REPO_DIR, "include"), "-c", s, "-o", o]
+            if trace:
+                cmd.insert(1, "-DNTXENT_TRACE=1")
             procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                                                 text=True)))
         log = []
@@ -60,13 +66,14 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
             log.append(out)
             if p.returncode != 0:
                 raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
-        link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH, *objs]  # static cudart
+        link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib_path, *objs]  # static cudart
         subprocess.run(link, check=True)
-        with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
-            f.write("\n".join(log))
+        if not trace:
+            with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
+                f.write("\n".join(log))
         if verbose:
             print("\n".join(log))
-    return LIB_PATH
+    return lib_path
 
 
 def build_binding(force: bool = False) -> str:

@@ -73,9 +73,14 @@ def lib() -> ctypes.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB_PATH
-    if not os.path.exists(path):
-        path = _build.build_library()
+    if os.environ.get("NTXENT_TRACE") == "1":  # tools/trace_bwd.py: the build with time stamps
+        path = _build.LIB_PATH_TRACE
+        if not os.path.exists(path):
+            path = _build.build_library(trace=True)
+    else:
+        path = _build.LIB_PATH
+        if not os.path.exists(path):
+            path = _build.build_library()
     L = ctypes.CDLL(path)
     vp, i64, u32, f32, sz, ci = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint, ctypes.c_float,
                                  ctypes.c_size_t, ctypes.c_int)

@@ -359,8 +359,7 @@ int ntxent_b200_profile_end(float* fwd_ms, int* fwd_launches, float* bwd_ms, int
 }
 
 int ntxent_b200_debug_set_trace(void* dev_buffer) {
-    tc_set_trace_buffer((unsigned long long*)dev_buffer);
-    return NTXENT_OK;
+    return tc_set_trace_buffer((unsigned long long*)dev_buffer) ? NTXENT_OK : NTXENT_ERR_INVALID_ARGUMENT;
 }
 
 int ntxent_b200_plan_info(int64_t M, int64_t D, int64_t row_count, int dtype, unsigned flags,

@@ -394,8 +394,14 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
 // warp 15, 3 = the other weight warps (overwriting each other), all for the CTA's first unit;
 // role 4 = unit-level events of weight warp 0 (row 63: kernel entry / set-up done / exit, with
 // %globaltimer in events 6 and 7 to calibrate the clock).
+// Compiled in only with -DNTXENT_TRACE=1 (NTXENT_TRACE=1 in the environment of the build, as
+// tools/trace_bwd.py does): even predicated off, the stamps cost issue slots in the weight loop.
 constexpr int kTraceTiles = 64, kTraceEvents = 8;
 unsigned long long* g_trace = nullptr;
+#ifndef NTXENT_TRACE
+#define NTXENT_TRACE 0
+#endif
+#if NTXENT_TRACE
 #define NTX_TRACE(role, it, ev)                                                                   \
     do {                                                                                          \
         if (trace && blockIdx.x == 0 && un == 0 && (it) < kTraceTiles && lane == 0)               \
@@ -407,6 +413,10 @@ unsigned long long* g_trace = nullptr;
         if (trace && blockIdx.x == 0 && warp == 0 && lane == 0 && (row) < kTraceTiles)            \
             trace[(4 * kTraceTiles + (row)) * kTraceEvents + (ev)] = (val);                       \
     } while (0)
+#else
+#define NTX_TRACE(role, it, ev) do { (void)trace; } while (0)
+#define NTX_TRACE_U(row, ev, val) do { (void)trace; } while (0)
+#endif
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -663,6 +673,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         const int wt = threadIdx.x;  // 0..511: the weight threads come first
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
         const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
+        (void)trole;
 
         // park k U_a of row tile `rt` in TMEM (bf16 pairs, or fp32 for tf32): column groups of the
         // row dealt round-robin to the four warps that share this lane quadrant.  Called for the
@@ -953,7 +964,11 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
 
 }  // namespace
 
-void tc_set_trace_buffer(unsigned long long* dev_ptr) { g_trace = dev_ptr; }
+bool tc_set_trace_buffer(unsigned long long* dev_ptr) {
+    if (dev_ptr && !NTXENT_TRACE) return false;  // this build has no time stamps compiled in
+    g_trace = dev_ptr;
+    return true;
+}
 
 int64_t tc_ut_cols(int64_t M) { return (M + 3) / 4 * 4; }
 

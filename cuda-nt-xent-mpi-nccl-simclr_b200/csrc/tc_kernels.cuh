@@ -28,6 +28,6 @@ int64_t tc_ut_cols(int64_t M);
 
 // Debug aid: CTA (0,0) of the backward tile kernel stamps its pipeline hand-offs into this
 // device buffer ([3 roles][64 tiles][8 events] of clock64 values); nullptr turns it off.
-void tc_set_trace_buffer(unsigned long long* dev_ptr);
+bool tc_set_trace_buffer(unsigned long long* dev_ptr);  // false: time stamps not compiled in
 
 }  // namespace ntxent_b200

@@ -257,9 +257,11 @@ int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, float tau, i
 int ntxent_b200_profile_begin(void);
 int ntxent_b200_profile_end(float* fwd_ms, int* fwd_launches, float* bwd_ms, int* bwd_launches);
 
-/* Debug aid for tools/trace_bwd.py: while a device buffer of 3*64*8 uint64 is
- * set, CTA (0,0) of the tcgen05 backward kernel stamps clock64() at its pipeline
- * hand-offs into it.  NULL switches it off (the default). */
+/* Debug aid for tools/trace_bwd.py: while a device buffer of 5*64*8 uint64 is
+ * set, CTA 0 of the tcgen05 backward kernel stamps clock64() at its pipeline
+ * hand-offs into it.  NULL switches it off (the default).  The stamps exist only
+ * in the trace build of the library (-DNTXENT_TRACE=1, libntxent_b200_trace.so);
+ * the product build refuses a non-NULL buffer with NTXENT_ERR_INVALID_ARGUMENT. */
 int ntxent_b200_debug_set_trace(void* dev_buffer);
 
 /* Which kernel family and how many column splits a call with these arguments

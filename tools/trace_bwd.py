@@ -1,7 +1,12 @@
-"""Prints the pipeline timeline of CTA (0,0) of the tcgen05 backward kernel (clock64 deltas)."""
+"""Prints the pipeline timeline of CTA 0 of the tcgen05 backward kernel (clock64 deltas).
+
+Needs the trace build of the library; build it where nvcc is cheap (not on the GPU box):
+    python -c "import ntxent_b200; from ntxent_b200 import _build; _build.build_library(trace=True)"
+"""
 import sys, os, ctypes
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
+os.environ["NTXENT_TRACE"] = "1"  # load libntxent_b200_trace.so (build it first: see above)
 import ntxent_b200
 from ntxent_b200 import capi
 M, D, tau = 32768, 128, 0.1
