@@ -728,6 +728,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             const int64_t row = a0 + row_in_tile;
             const bool row_ok = row < a_end;
             const int jt0 = u.ct0, n_tiles = u.n;
+            // column tiles that need the masked weight path, as 32-bit tile numbers: those that
+            // overlap this row tile's own rows (the diagonal) and a ragged last tile
+            const int64_t dd = a0 - b_begin;
+            const int jt_diag_lo = (int)(dd >= 0 ? dd / kTile : -((-dd + kTile - 1) / kTile));
+            const int jt_diag_hi = (int)(dd >= 0 ? (dd + kTile - 1) / kTile : -((-dd) / kTile));
+            const int jt_ragged = (b_count % kTile) ? col_tiles - 1 : -1;
             NTX_TRACE_U(un, 0, clock64());
             NTX_TRACE_U(un, 7, (unsigned long long)n_tiles);
 
@@ -743,8 +749,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             }
             for (int it = 0; it < n_tiles; ++it, ++g) {
                 const int pb = SEP ? (g & 1) : 0;
-                const int64_t j0 = b_begin + (int64_t)(jt0 + it) * kTile;
-                const bool special = (j0 < a0 + kTile && j0 + kTile > a0) || (j0 + kTile > b_end);
+                const int jt = jt0 + it;
+                const bool special = (jt >= jt_diag_lo && jt <= jt_diag_hi) || jt == jt_ragged;
+                const int64_t j0 = b_begin + (int64_t)jt * kTile;  // (used on the masked path only)
                 if (MODE != kRow && (it % B::kCcTiles) == 0)  // the block staged by the constants warp
                     mbar_wait(&cc_full[cb & 1], (cb >> 1) & 1);
                 const float* cc = colc + ((cb & 1) * B::kCcTiles + it % B::kCcTiles) * kTile + quarter * 32;
