@@ -254,10 +254,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         mbar_wait(&s_full[0], 0);
         tc_fence_after();
         tmem_ld32(lane_addr, va);
+        // 64-column half tiles that need the masked path, as 32-bit numbers: those overlapping
+        // this row tile's own rows (the diagonal) and everything from the ragged end of the range
+        const int hj_diag_lo = (int)(a0 / 64), hj_diag_hi = (int)((a0 + 63) / 64) + 1;
+        const int hj_ragged = (int)(M / 64);
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
-            const int64_t j0 = (int64_t)(jt0 + it) * kTile + half * 64;
-            const bool special = (j0 < a0 + kTile && j0 + 64 > a0) || (j0 + 64 > M);
+            const int hj = 2 * (jt0 + it) + half;
+            const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged;
+            const int64_t j0 = (int64_t)hj * 64;  // (used on the masked path only)
             const uint32_t taddr = lane_addr + buf * kTile;
             tmem_ld_wait();
             tmem_ld32(taddr + 32, vb);
