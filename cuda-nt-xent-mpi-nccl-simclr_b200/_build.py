@@ -41,23 +41,33 @@ def _stale(target: str, sources) -> bool:
     return any(os.path.getmtime(s) > t for s in sources)
 
 
-def build_library(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, trace: bool = False,
+                  variant: str | None = None, defines=()) -> str:
     """nvcc -> libntxent_b200.so (all kernels + the extern "C" boundary).  trace=True builds the
     variant with the pipeline time stamps compiled in (libntxent_b200_trace.so, for
-    tools/trace_bwd.py; loaded instead of the product library when NTXENT_TRACE=1)."""
+    tools/trace_bwd.py; loaded instead of the product library when NTXENT_TRACE=1).
+    variant="name", defines=["-DX=1"] builds libntxent_b200_name.so for A/B runs (loaded when
+    NTXENT_LIBRARY points at it)."""
+    if variant:
+        trace = False
     srcs = [os.path.join(CSRC, s) for s in KERNEL_SOURCES]
     deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     deps.append(os.path.join(REPO_DIR, "include", "ntxent_b200.h"))
     lib_path = LIB_PATH_TRACE if trace else LIB_PATH
+    if variant:
+        lib_path = LIB_PATH[:-3] + f"_{variant}.so"
     if force or _stale(lib_path, deps):
         objs = []
         procs = []
         for s in srcs:
-            o = os.path.join(CSRC, os.path.basename(s)[:-3] + (".trace.o" if trace else ".o"))
+            o = os.path.join(CSRC, os.path.basename(s)[:-3] +
+                             (f".{variant}.o" if variant else ".trace.o" if trace else ".o"))
             objs.append(o)
             cmd = [_nvcc(), *NVCC_FLAGS, "-I", os.path.join(REPO_DIR, "include"), "-c", s, "-o", o]
             if trace:
                 cmd.insert(1, "-DNTXENT_TRACE=1")
+            for d in defines:
+                cmd.insert(1, d)
             procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                                                 text=True)))
         log = []
@@ -68,7 +78,7 @@ def build_library(force: bool = False, verbose: bool = False, trace: bool = Fals
                 raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
         link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib_path, *objs]  # static cudart
         subprocess.run(link, check=True)
-        if not trace:
+        if not trace and not variant:
             with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
                 f.write("\n".join(log))
         if verbose:

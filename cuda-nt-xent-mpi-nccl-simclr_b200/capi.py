@@ -73,7 +73,9 @@ def lib() -> ctypes.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if os.environ.get("NTXENT_TRACE") == "1":  # tools/trace_bwd.py: the build with time stamps
+    if os.environ.get("NTXENT_LIBRARY"):  # A/B runs against a variant build (_build.build_library(variant=))
+        path = os.environ["NTXENT_LIBRARY"]
+    elif os.environ.get("NTXENT_TRACE") == "1":  # tools/trace_bwd.py: the build with time stamps
         path = _build.LIB_PATH_TRACE
         if not os.path.exists(path):
             path = _build.build_library(trace=True)
