@@ -392,7 +392,7 @@ def run_native(args):
                        + ("" if dt == "bf16" or args.simt else " / 2 for tf32"),
         # DRAM bytes of one launch from the committed ncu capture (same workload, 1 GPU); the
         # kernel is tensor-bound: its operands (8 MB of U) live in L2 for the whole launch
-        "traffic": ncu_dram_traffic("v2_bwd") if (world == 1 and (M, D, dt) == (32768, 128, "bf16")
+        "traffic": ncu_dram_traffic("v3_bwd") if (world == 1 and (M, D, dt) == (32768, 128, "bf16")
                                                    and not args.simt) else None,
         "flop_per_launch": bwd_flop_per_launch, "ms_per_launch": bwd_ms,
         "fwd_kernel": {"ms_per_launch": fwd_ms, "flop_per_launch": 2.0 * rows * M * D,
