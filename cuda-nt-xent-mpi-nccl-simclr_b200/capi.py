@@ -27,7 +27,7 @@ EXPORTS = [
     "ntxent_b200_finalize_dz", "ntxent_b200_profile_begin", "ntxent_b200_profile_end",
     "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
     "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push", "ntxent_b200_peer_wait",
-    "ntxent_b200_backward_rows_dz",
+    "ntxent_b200_backward_rows_dz", "ntxent_b200_backward_tau",
 ]
 
 _lib = None
@@ -96,6 +96,8 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_forward.argtypes = [vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
     L.ntxent_b200_backward.restype = ci
     L.ntxent_b200_backward.argtypes = [vp, vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
+    L.ntxent_b200_backward_tau.restype = ci
+    L.ntxent_b200_backward_tau.argtypes = [vp, vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp]
     L.ntxent_b200_forward_backward.restype = ci
     L.ntxent_b200_forward_backward.argtypes = [vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
                                                vp, vp]
@@ -239,6 +241,29 @@ def backward(z: torch.Tensor, lse: torch.Tensor, grad_out: torch.Tensor | None, 
                                          _dtype_code(z), fl, _ptr(ws), ws.numel(), _ptr(dz), _ptr(pp),
                                          _stream()))
     return dz, pp
+
+
+def backward_tau(z: torch.Tensor, lse: torch.Tensor, grad_out: torch.Tensor | None, tau: float,
+                 use_mixed_precision: bool = False, flags: int = 0, ws: torch.Tensor | None = None):
+    """-> (dz[M,D] in z's dtype, tau_grad_rows[M] fp32); d loss / d tau = grad_out * tau_grad_rows.sum()."""
+    _require_cuda(z, lse, grad_out)
+    z = z.contiguous()
+    lse = lse.contiguous().float()
+    M, D = z.shape
+    if lse.numel() != M:
+        raise NTXentError(f"backward expects the forward's row log-sum-exp of {M} entries, got a "
+                          f"tensor of shape {tuple(lse.shape)}")
+    if grad_out is not None:
+        grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        ws = workspace(M, D, z, fl) if ws is None else ws
+        dz = torch.empty_like(z)
+        rows = torch.empty(M, dtype=torch.float32, device=z.device)
+        check(lib().ntxent_b200_backward_tau(_ptr(z), _ptr(lse), _ptr(grad_out), M, D, float(tau),
+                                             _dtype_code(z), fl, _ptr(ws), ws.numel(), _ptr(dz), _ptr(rows),
+                                             _stream()))
+    return dz, rows
 
 
 def forward_backward(z: torch.Tensor, tau: float, grad_out: torch.Tensor | None = None,

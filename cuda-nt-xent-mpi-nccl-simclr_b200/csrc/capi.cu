@@ -273,7 +273,8 @@ int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t
 
 int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_bf16, const float* lse,
                         const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
-                        void* dz_out, float* pos_prob_out, cudaStream_t st) {
+                        void* dz_out, float* pos_prob_out, cudaStream_t st,
+                        float* tau_grad_rows_out = nullptr) {
     int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows,
                            w.rows.acc_rows, w.rows.ut, st);
     if (rc != NTXENT_OK) return rc;
@@ -287,6 +288,7 @@ int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_b
     e.du_out = nullptr; e.z_rows = z; e.z_bf16 = z_bf16; e.inv_norm = w.inv_norm;
     e.grad_out = grad_out; e.dz_out = dz_out;
     e.lse_all = lse; e.inv_tau = 1.0f / tau; e.pos_prob_out = pos_prob_out;
+    e.tau_grad_rows_out = tau_grad_rows_out;
     NTX_TRY(launch_bwd_epilogue(e, st));
     return NTXENT_OK;
 }
@@ -523,6 +525,23 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                pos_prob_out, stream);
+}
+
+int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_out, int64_t M,
+                             int64_t D, float tau, int dtype, unsigned flags, void* workspace,
+                             size_t workspace_bytes, void* dz_out, float* tau_grad_rows_out,
+                             ntxent_stream_t stream) {
+    if (!z || !lse || !workspace || !dz_out || !tau_grad_rows_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
+    const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
+                               nullptr, stream, tau_grad_rows_out);
 }
 
 int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M, int64_t D,

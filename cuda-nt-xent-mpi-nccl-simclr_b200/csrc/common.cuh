@@ -126,6 +126,9 @@ struct BwdEpilogueArgs {
     const float* lse_all;    // [M] (needed only with pos_prob_out)
     float inv_tau;
     float* pos_prob_out;     // [a_count] or nullptr
+    // optional per-row temperature gradient (output B only): -(dU_a . u_a) / (2 tau); its sum
+    // over all rows, times grad_out, is d loss / d tau
+    float* tau_grad_rows_out;  // [a_count] or nullptr
 };
 cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& args, cudaStream_t stream);
 

@@ -160,6 +160,7 @@ struct BwdEpiDev {
     const float* lse_all;
     float inv_tau;
     float* pos_prob_out;
+    float* tau_grad_rows_out;
 };
 
 template <typename TOp, typename TZ>
@@ -232,6 +233,9 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
         dot += du[c].x * zz.x + du[c].y * zz.y + du[c].z * zz.z + du[c].w * zz.w;
     }
     dot = warp_sum(dot);
+    // sum_a dU_a . u_a = -2 tau dL/dtau (each logit S_ab = u_a.u_b / tau appears once as row a's
+    // and once as row b's): the temperature gradient falls out of the Jacobian's dot product
+    if (p.tau_grad_rows_out && lane == 0) p.tau_grad_rows_out[r] = -0.5f * p.inv_tau * dot;
     const float gi = g * inv;
 #pragma unroll
     for (int c = 0; c < kMaxDChunks; ++c) {
@@ -255,6 +259,7 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
     p.D = (int)a.D; p.pos_coeff = a.pos_coeff; p.pos_lo = a.pos_lo; p.pos_hi = a.pos_hi;
     p.scale = a.scale; p.du_out = a.du_out; p.inv_norm = a.inv_norm; p.grad_out = a.grad_out;
     p.lse_all = a.lse_all; p.inv_tau = a.inv_tau; p.pos_prob_out = a.pos_prob_out;
+    p.tau_grad_rows_out = a.du_out ? nullptr : a.tau_grad_rows_out;
     dim3 grid((unsigned)((a.a_count + 7) / 8)), block(256);
     if (a.op_bf16) {
         if (a.z_bf16)

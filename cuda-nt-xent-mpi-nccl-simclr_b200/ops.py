@@ -64,6 +64,29 @@ class _NTXentFunction(torch.autograd.Function):
         return dz, None, None
 
 
+class _NTXentLearnableTauFunction(torch.autograd.Function):
+    """Same op with the temperature as a differentiable 0-dim tensor.  The
+    kernels take tau as a host scalar, so forward reads it back once (one host sync per step)."""
+
+    @staticmethod
+    def forward(ctx, z, tau, use_mixed_precision):
+        T = float(tau.detach())
+        if not T > 0.0:
+            raise capi.NTXentError(f"temperature must stay positive, got {T}")
+        loss, lse = capi.forward(z.detach(), T, use_mixed_precision)
+        ctx.save_for_backward(z.detach(), lse)
+        ctx.T, ctx.mp, ctx.tau_meta = T, use_mixed_precision, (tau.dtype, tau.device, tau.shape)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        z, lse = ctx.saved_tensors
+        dz, rows = capi.backward_tau(z, lse, grad_loss, ctx.T, ctx.mp)
+        dtype, device, shape = ctx.tau_meta
+        dtau = (grad_loss.reshape(-1)[:1].float() * rows.double().sum().float()).reshape(shape)
+        return dz, dtau.to(device=device, dtype=dtype), None
+
+
 class GraphedNTXent:
     """Fused forward+backward for a fixed [M, D] shape, captured once into a CUDA graph and replayed
     (SURVEY.md section 8f-2): for projection-head sized batches (2N ~ 4096) the six launches of a
@@ -96,7 +119,12 @@ class GraphedNTXent:
 
 def ntxent_loss(z: torch.Tensor, temperature: float = 0.07,
                 use_mixed_precision: bool = False) -> torch.Tensor:
-    """Scalar (0-dim) differentiable NT-Xent loss of the stacked batch z[2N, D]."""
+    """Scalar (0-dim) differentiable NT-Xent loss of the stacked batch z[2N, D].  A 0-dim tensor
+    temperature that requires grad receives d loss / d tau."""
+    if isinstance(temperature, torch.Tensor):
+        if temperature.requires_grad:
+            return _NTXentLearnableTauFunction.apply(z, temperature, use_mixed_precision).squeeze(0)
+        temperature = float(temperature)
     return forward(z, temperature, use_mixed_precision).squeeze(0)
 
 
@@ -105,9 +133,15 @@ class NTXentLoss(torch.nn.Module):
     row-partitioned across the group (see distributed.py)."""
 
     def __init__(self, temperature: float = 0.07, use_mixed_precision: bool = False,
-                 process_group=None, backward_mode: str = "symmetric"):
+                 process_group=None, backward_mode: str = "symmetric",
+                 learnable_temperature: bool = False):
         super().__init__()
-        self.temperature = float(temperature)
+        if learnable_temperature:
+            if process_group is not None:
+                raise ValueError("learnable_temperature is single-GPU only for now")
+            self.temperature = torch.nn.Parameter(torch.tensor(float(temperature)))
+        else:
+            self.temperature = float(temperature)
         self.use_mixed_precision = bool(use_mixed_precision)
         self.process_group = process_group
         self.backward_mode = backward_mode
@@ -117,4 +151,6 @@ class NTXentLoss(torch.nn.Module):
             from .distributed import distributed_ntxent_loss
             return distributed_ntxent_loss(z, self.temperature, self.use_mixed_precision,
                                            group=self.process_group, backward_mode=self.backward_mode)
+        if isinstance(self.temperature, torch.Tensor):
+            return _NTXentLearnableTauFunction.apply(z, self.temperature, self.use_mixed_precision).squeeze(0)
         return ntxent_loss(z, self.temperature, self.use_mixed_precision)

@@ -91,6 +91,18 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
                          void* workspace, size_t workspace_bytes,
                          void* dz_out, float* pos_prob_out, ntxent_stream_t stream);
 
+/* Backward that also yields the gradient of the loss with respect to the
+ * temperature (learnable tau; no counterpart in the
+ * reference, whose T is a plain double).  tau_grad_rows_out: device float[M];
+ * d loss / d tau = (*grad_out) * sum_i tau_grad_rows_out[i]  (the caller sums:
+ * M floats, in whatever order it wants to be deterministic in).  It costs
+ * nothing extra: sum_a dU_a . u_a = -2 tau dL/dtau, and that dot product is
+ * already formed for the normalisation Jacobian. */
+int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_out, int64_t M,
+                             int64_t D, float tau, int dtype, unsigned flags, void* workspace,
+                             size_t workspace_bytes, void* dz_out, float* tau_grad_rows_out,
+                             ntxent_stream_t stream);
+
 /* Forward and backward in one call (one normalisation pass); the benchmark's
  * timed unit (src/benchmark.cpp:30-39 times the forward only). */
 int ntxent_b200_forward_backward(const void* z, const float* grad_out,

@@ -136,7 +136,8 @@ def literal_reference_forward(z, T: float) -> float:
 # Independent numpy restatement (dense, fp64, small cases only).
 # --------------------------------------------------------------------------
 def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e-12):
-    """Dense numpy fp64 NT-Xent.  Returns dict(loss, lse, dz, dU, pos_prob)."""
+    """Dense numpy fp64 NT-Xent.  Returns dict(loss, lse, dz, dU, pos_prob, dtau, ...); dtau is
+    d loss / d tau = -(1/tau) sum_ij G_ij S_ij."""
     z = np.asarray(z, dtype=np.float64)
     M, D = z.shape
     assert M % 2 == 0
@@ -157,4 +158,6 @@ def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e
     G = (P - Y) / M
     dU = (G + G.T) @ u / tau
     dz = grad_out * (dU - (dU * u).sum(axis=1, keepdims=True) * u) / nrm
-    return dict(loss=loss, lse=lse, dz=dz, dU=dU, pos_prob=P[idx, pos], G=G, u=u)
+    S0 = np.where(np.isfinite(Sm), S, 0.0)  # G's diagonal is zero
+    dtau = float(-grad_out * (G * S0).sum() / tau)
+    return dict(loss=loss, lse=lse, dz=dz, dU=dU, pos_prob=P[idx, pos], G=G, u=u, dtau=dtau)

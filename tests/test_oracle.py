@@ -59,6 +59,19 @@ def test_kat5_finite_differences(oracle):
     assert np.abs(num - dz).max() < 1e-8
 
 
+def test_temperature_gradient_finite_differences(oracle):
+    """d loss / d tau of the numpy restatement against central differences, and the identity the
+    CUDA epilogue uses: sum_a dU_a . u_a = -2 tau dL/dtau."""
+    z = seeded_z(24, 10, seed=11)
+    for tau in (0.1, 0.5, 2.0):
+        r = oracle.numpy_forward_backward(z, tau)
+        h = 1e-6 * tau
+        fd = (oracle.numpy_forward_backward(z, tau + h)["loss"] -
+              oracle.numpy_forward_backward(z, tau - h)["loss"]) / (2 * h)
+        assert abs(r["dtau"] - fd) <= 1e-6 * max(1.0, abs(fd))
+        assert abs(-0.5 / tau * (r["dU"] * r["u"]).sum() - r["dtau"]) <= 1e-12 * max(1.0, abs(fd))
+
+
 def test_kat6_pair_permutation(oracle):
     z = seeded_z(24, 12, seed=6, dtype=np.float64)
     N = 12

@@ -247,6 +247,45 @@ def test_autograd_matches_torch_reference():
     assert (za.grad - zb.grad).abs().max() <= 1e-4 * zb.grad.abs().max()
 
 
+@pytest.mark.parametrize("M,D,tau,dtype,flags", [
+    (64, 32, 0.5, torch.float32, capi.FLAG_FORCE_SIMT), (512, 128, 0.2, torch.float32, 0),
+    (2048, 128, 0.5, torch.float32, 0),  # tf32 tiles
+    (1024, 128, 0.1, torch.bfloat16, 0), (640, 256, 0.07, torch.bfloat16, 0)])
+def test_temperature_gradient(oracle, M, D, tau, dtype, flags):
+    """d loss / d tau (learnable temperature) against the fp64 numpy
+    restatement; the dz that comes with it is the ordinary backward's, bit for bit."""
+    z = seeded_z(M, D, seed=17)
+    z_t = dev(z, dtype)
+    ref = oracle.numpy_forward_backward(z_t.double().cpu().numpy(), tau, grad_out=1.7)
+    loss, lse = capi.forward(z_t, tau, False, flags)
+    g = torch.tensor([1.7], device="cuda")
+    dz, rows = capi.backward_tau(z_t, lse, g, tau, False, flags)
+    dz0, _ = capi.backward(z_t, lse, g, tau, False, flags)
+    torch.cuda.synchronize()
+    assert torch.equal(dz, dz0)
+    dtau = 1.7 * float(rows.double().sum().item())
+    tol = 2e-2 if dtype == torch.bfloat16 else 2e-4
+    assert abs(dtau - ref["dtau"]) <= tol * abs(ref["dtau"]), (dtau, ref["dtau"])
+
+
+def test_learnable_temperature_module():
+    """NTXentLoss(learnable_temperature=True): tau is a Parameter and receives a gradient that
+    matches plain PyTorch autograd on the same expression (fp32)."""
+    torch.manual_seed(4)
+    z = torch.randn(256, 64, device="cuda")
+    mod = ntxent_b200.NTXentLoss(0.3, learnable_temperature=True).cuda()
+    za = z.clone().requires_grad_(True)
+    (mod(za) * 2.0).backward()
+    zb = z.clone().requires_grad_(True)
+    tb = torch.tensor(0.3, device="cuda", requires_grad=True)
+    u = torch.nn.functional.normalize(zb)
+    s = (u @ u.t() / tb).masked_fill(torch.eye(256, dtype=torch.bool, device="cuda"), float("-inf"))
+    tgt = (torch.arange(256, device="cuda") + 128) % 256
+    (torch.nn.functional.cross_entropy(s, tgt) * 2.0).backward()
+    assert (za.grad - zb.grad).abs().max() <= 1e-4 * zb.grad.abs().max()
+    assert abs(mod.temperature.grad.item() - tb.grad.item()) <= 2e-4 * abs(tb.grad.item())
+
+
 def test_fused_equals_separate_and_is_deterministic():
     z_t = dev(seeded_z(1024, 128, seed=5), torch.bfloat16)
     loss, lse = capi.forward(z_t, 0.1)
