@@ -91,3 +91,41 @@ def test_device_supported_is_false_without_a_gpu():
         pytest.skip("GPU present")
     assert capi.lib().ntxent_b200_device_supported() == 0
     assert ntxent_b200.check_tensor_core_support() is False
+
+
+def _cta_of_tile(t, total, ctas):
+    # tc_kernels.cu, bwd_cta_of_tile: CTA c owns the linear tiles [c*T/G, (c+1)*T/G)
+    return ((t + 1) * ctas - 1) // total
+
+
+@pytest.mark.parametrize("M,rows", [(32768, 32768), (32768, 16384), (32768, 4096), (8192, 8192), (2048, 2048),
+                                    (4096, 512), (1030, 1030), (256, 256), (131072, 16384)])
+def test_backward_tile_dealing_invariants(M, rows):
+    """The tcgen05 backward deals the (row tile, column tile) pairs to persistent CTAs in equal
+    contiguous shares and the epilogue re-derives, per row tile, how many partials to add.  This
+    restates the dealing (csrc/tc_kernels.cu, BwdUnit) and ties it to the library's own plan:
+    every tile is owned exactly once, shares differ by at most one tile, the slots of a row tile
+    are 0..count-1 with count = the epilogue's formula, and the largest count is the plan's split
+    number (which sizes the workspace)."""
+    plan = capi.plan_info(M, 128, rows, capi.BF16)
+    assert plan["tcgen05"]
+    row_tiles, col_tiles = -(-rows // 128), -(-M // 128)
+    total = row_tiles * col_tiles
+    ctas = min(148, total)  # device_sm_count() is 148 when there is no device
+    begins = [c * total // ctas for c in range(ctas + 1)]
+    assert begins[0] == 0 and begins[-1] == total
+    shares = [b - a for a, b in zip(begins, begins[1:])]
+    assert max(shares) - min(shares) <= 1 and min(shares) >= 1
+    for c in range(ctas):  # the closed form the kernel and the epilogue use agrees with the ranges
+        assert _cta_of_tile(begins[c], total, ctas) == c
+        assert _cta_of_tile(begins[c + 1] - 1, total, ctas) == c
+    worst = 0
+    for rt in range(row_tiles):
+        first, last = rt * col_tiles, (rt + 1) * col_tiles - 1
+        owners = list(range(_cta_of_tile(first, total, ctas), _cta_of_tile(last, total, ctas) + 1))
+        slots = [c - owners[0] for c in owners]
+        assert slots == list(range(len(owners)))
+        # epilogue_kernels.cu: ((first + col_tiles) * G - 1) / T - ((first + 1) * G - 1) / T + 1
+        assert ((first + col_tiles) * ctas - 1) // total - ((first + 1) * ctas - 1) // total + 1 == len(owners)
+        worst = max(worst, len(owners))
+    assert worst == plan["bwd_splits"]
