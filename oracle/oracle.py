@@ -48,6 +48,8 @@ def lib() -> ctypes.CDLL:
         L.ntxent_oracle_backward_f64.argtypes = [dp, dp, ctypes.c_double, i64, i64,
                                                  ctypes.c_double, dp, dp]
         L.ntxent_oracle_backward_f64.restype = ctypes.c_int
+        L.ntxent_oracle_dtau_f64.argtypes = [dp, dp, ctypes.c_double, i64, i64, ctypes.c_double, dp]
+        L.ntxent_oracle_dtau_f64.restype = ctypes.c_int
         L.ntxent_oracle_rowblock_f32.argtypes = [fp, i64, i64, ctypes.c_float, i64, i64,
                                                  fp, fp, fp, fp]
         L.ntxent_oracle_rowblock_f32.restype = ctypes.c_int
@@ -94,6 +96,18 @@ def backward(z, lse, tau: float, grad_out: float = 1.0):
     if rc != 0:
         raise ValueError(f"ntxent_oracle_backward_f64 rc={rc}")
     return dz, pp
+
+
+def dtau(z, lse, tau: float, grad_out: float = 1.0) -> float:
+    """fp64 d loss / d tau (the contract of ntxent_b200_backward_tau)."""
+    z = np.ascontiguousarray(z, dtype=np.float64)
+    lse = np.ascontiguousarray(lse, dtype=np.float64)
+    M, D = z.shape
+    out = np.zeros(1)
+    rc = lib().ntxent_oracle_dtau_f64(_dptr(z), _dptr(lse), float(grad_out), M, D, float(tau), _dptr(out))
+    if rc != 0:
+        raise ValueError(f"ntxent_oracle_dtau_f64 rc={rc}")
+    return float(out[0])
 
 
 def forward_backward(z, tau: float, grad_out: float = 1.0):

@@ -70,6 +70,10 @@ def test_temperature_gradient_finite_differences(oracle):
               oracle.numpy_forward_backward(z, tau - h)["loss"]) / (2 * h)
         assert abs(r["dtau"] - fd) <= 1e-6 * max(1.0, abs(fd))
         assert abs(-0.5 / tau * (r["dU"] * r["u"]).sum() - r["dtau"]) <= 1e-12 * max(1.0, abs(fd))
+        # the C restatement (direct sum over P_ij S_ij) agrees with the numpy one
+        _, lse, _ = oracle.forward(z, tau)
+        assert abs(oracle.dtau(z, lse, tau) - r["dtau"]) <= 1e-12 * max(1.0, abs(fd))
+        assert abs(oracle.dtau(z, lse, tau, grad_out=-2.5) + 2.5 * r["dtau"]) <= 1e-11 * max(1.0, abs(fd))
 
 
 def test_kat6_pair_permutation(oracle):
