@@ -342,6 +342,7 @@ def run_native(args):
             engine.use_cuda_graph = True
         else:
             graphed = keep
+        sync_all()  # eager and replayed steps pick their buffer set independently: never back to back
 
     # --- end to end: pinned host z -> device -> fused op -> loss back on the host -------
     z_stage = torch.empty_like(z_dev)

@@ -291,7 +291,9 @@ class RowPartitionedNTXent:
     def _replay(self, z_local, grad_out):
         """Capture forward+backward once per buffer set (static inputs), then copy-in + replay.
         The returned loss / dz are the graph's static outputs: consume them before the call
-        after next."""
+        after next.  Replayed and eager steps each alternate between the two buffer sets on
+        their own count: when switching an engine between the two modes, put a cross-rank
+        barrier in between (bench.py does) so that two consecutive steps never share a set."""
         k = (self._gstep & 1) if self.symm is not None else 0
         self._gstep += 1
         if not self._graphs:
