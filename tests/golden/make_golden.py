@@ -50,13 +50,15 @@ def main():
         if norm:
             z = F.normalize(z, dim=1)
         z = (z * scale).detach().requires_grad_(True)
-        loss, lse = ntxent_torch(z, tau)
-        (dz,) = torch.autograd.grad(loss, z)
+        tau_t = torch.tensor(tau, dtype=torch.float64, requires_grad=True)
+        loss, lse = ntxent_torch(z, tau_t)
+        dz, dtau = torch.autograd.grad(loss, (z, tau_t))
         out[name + "/z"] = z.detach().numpy()
         out[name + "/tau"] = np.float64(tau)
         out[name + "/loss"] = np.float64(loss.item())
         out[name + "/lse"] = lse.detach().numpy()
         out[name + "/dz"] = dz.numpy()
+        out[name + "/dtau"] = np.float64(dtau.item())  # d loss / d tau (learnable temperature)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ntxent_golden.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes,", len(CASES), "cases")

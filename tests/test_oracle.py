@@ -114,6 +114,10 @@ def test_golden_fixtures(oracle, golden):
         np.testing.assert_allclose(lse, c["lse"], rtol=1e-11, atol=1e-11, err_msg=name)
         scale = np.abs(c["dz"]).max()
         assert np.abs(dz - c["dz"]).max() <= 1e-9 * max(scale, 1e-300), name
+        # d loss / d tau: both restatements against autograd's
+        ref = float(c["dtau"])
+        assert oracle.dtau(c["z"], lse, tau) == pytest.approx(ref, rel=1e-9, abs=1e-12), name
+        assert oracle.numpy_forward_backward(c["z"], tau)["dtau"] == pytest.approx(ref, rel=1e-9, abs=1e-12), name
 
 
 def test_reference_test_properties_hold(oracle):
