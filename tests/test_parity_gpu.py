@@ -55,6 +55,24 @@ def test_golden_fixtures_fp32(golden, path):
         assert dz_err(dz, c["dz"]) <= DZ_TOL_F32, name
 
 
+def test_golden_fixtures_temperature_gradient(golden):
+    """d loss / d tau of the fixtures (PyTorch autograd, fp64) through ntxent_b200_backward_tau."""
+    worst = 0.0
+    for name, c in golden.items():
+        M, D = c["z"].shape
+        if D % 8:
+            continue
+        tau = float(c["tau"])
+        z_t = dev(c["z"])
+        _, lse = capi.forward(z_t, tau)
+        _, rows = capi.backward_tau(z_t, lse, None, tau)
+        got, ref = float(rows.double().sum().item()), float(c["dtau"])
+        err = abs(got - ref) / max(abs(ref), 1e-12)
+        worst = max(worst, err)
+        print(f"{name}: dtau {got:.9g} vs {ref:.9g} rel {err:.2e}")
+        assert err <= 2e-5, (name, got, ref)  # measured 5e-8 .. 5e-7 on the fp32 paths
+
+
 # ------------------------------------------------------- BASELINE.json configurations
 @pytest.mark.parametrize("path", list(PATHS))
 def test_config_c1_fp32(oracle, path):
