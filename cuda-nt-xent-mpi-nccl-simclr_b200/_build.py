@@ -86,6 +86,33 @@ def build_library(force: bool = False, verbose: bool = False, trace: bool = Fals
     return lib_path
 
 
+def write_sass_summary(path: str | None = None) -> str:
+    """cuobjdump -sass of the built kernel objects -> counts of the mnemonics that show what the
+    kernels are made of (tcgen05.mma = UTC*MMA, tcgen05.ld/st = LDTM/STTM, TMA = UTMALDG,
+    tcgen05.commit = UTCBAR, griddepcontrol = ACQBULK/..., peer flags = LD/ST .SYS), per object.
+    Written to profiles/r2_sass_summary.txt by __graft_entry__.build()."""
+    import re
+    path = path or os.path.join(REPO_DIR, "profiles", "r2_sass_summary.txt")
+    pats = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "UTCATOMSWS",
+            "MUFU.EX2", r"\bHMMA", r"\bHGMMA", r"\.SYS", "FENCE.VIEW.ASYNC", "SYNCS", "ELECT", "ACQBULK", "PREEXIT",
+            "CCTL.IVALL"]
+    cuobjdump = os.path.join(os.path.dirname(_nvcc()), "cuobjdump")
+    lines = ["# cuobjdump -sass <object> | grep -c <mnemonic>   (sm_100a cubins, built by _build.py)",
+             "# flags: " + " ".join(NVCC_FLAGS)]
+    for src in KERNEL_SOURCES:
+        obj = os.path.join(CSRC, src[:-3] + ".o")
+        if not os.path.exists(obj):
+            continue
+        sass = subprocess.run([cuobjdump, "-sass", obj], stdout=subprocess.PIPE, text=True).stdout
+        funcs = len(re.findall(r"^\s*Function :", sass, flags=re.M))
+        counts = {p: len(re.findall(p, sass)) for p in pats}
+        lines.append(f"{src[:-3]}.o: {funcs} kernels; " +
+                     ", ".join(f"{k.replace(chr(92), '')} {v}" for k, v in counts.items() if v))
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path
+
+
 def build_binding(force: bool = False) -> str:
     """g++ -> ntxent_cuda.so, the torch extension with the reference's operator surface.
 

@@ -28,6 +28,7 @@ EXPORTS = [
     "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
     "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push", "ntxent_b200_peer_wait",
     "ntxent_b200_backward_rows_dz", "ntxent_b200_backward_tau",
+    "ntxent_b200_set_peer_wait_timeout_ms",
 ]
 
 _lib = None
@@ -57,7 +58,7 @@ class PeerSignal(ctypes.Structure):
 class PeerWait(ctypes.Structure):
     """ntxent_peer_wait: the local flag array a consuming kernel polls, and the value to reach."""
     _fields_ = [("flags", ctypes.c_void_p), ("epoch", ctypes.c_void_p), ("ranks", ctypes.c_int),
-                ("rows_per_rank", ctypes.c_int64)]
+                ("rows_per_rank", ctypes.c_int64), ("status", ctypes.c_void_p)]
 
 
 def _ref(struct):
@@ -129,6 +130,8 @@ def lib() -> ctypes.CDLL:
                                                 pw, ps, vp]
     L.ntxent_b200_peer_wait.restype = ci
     L.ntxent_b200_peer_wait.argtypes = [pw, vp]
+    L.ntxent_b200_set_peer_wait_timeout_ms.restype = ci
+    L.ntxent_b200_set_peer_wait_timeout_ms.argtypes = [ctypes.c_uint64]
     L.ntxent_b200_backward_rows_dz.restype = ci
     L.ntxent_b200_backward_rows_dz.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
                                                vp, pw, vp]
@@ -412,6 +415,11 @@ def forward_rows_push(u_all: torch.Tensor, row_begin: int, row_count: int, tau: 
                                                   _op_code(u_all), flags, _ptr(ws), ws.numel(),
                                                   ctypes.byref(lse_all_peers), ctypes.byref(loss_parts_peers),
                                                   rank, _ref(u_ready), _ref(lse_signal), _stream()))
+
+
+def set_peer_wait_timeout_ms(ms: int) -> None:
+    """How long a kernel waits for a peer's flag before it marks the step void (0: for ever)."""
+    check(lib().ntxent_b200_set_peer_wait_timeout_ms(int(ms)))
 
 
 def peer_wait(ready: "PeerWait", device) -> None:

@@ -3,6 +3,7 @@
 #include "../../include/ntxent_b200.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -22,6 +23,11 @@ int device_sm_count() {
         return 148;
     }
     return sms;
+}
+
+bool pdl_enabled() {
+    static const bool on = [] { const char* v = getenv("NTXENT_NO_PDL"); return !(v && v[0] == '1'); }();
+    return on;
 }
 
 SplitPlan plan_splits(int64_t a_count, int64_t b_count, int row_tile, int col_tile, int slots,
@@ -117,7 +123,7 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
 }
 
 struct RowsWs {
-    unsigned* counter;
+    float* pos_t;  // positive logits captured by the tcgen05 forward tile kernel (base-2 units)
     float* block_partials;
     float* part_m;
     float* part_s;
@@ -136,7 +142,7 @@ RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Pla
         off += align_up(n);
         return ptr;
     };
-    w.counter = (unsigned*)take(kAlign);
+    w.pos_t = (float*)take(sizeof(float) * (size_t)row_count);
     w.block_partials = (float*)take(sizeof(float) * (size_t)((row_count + 7) / 8));
     w.part_m = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.part_s = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
@@ -164,6 +170,22 @@ DeviceWs carve_device(char* base, int64_t M, int64_t D, bool op_bf16, const Plan
     w.rows = carve_rows(base ? base + off : nullptr, M, D, M, p, false);
     w.bytes = off + w.rows.bytes;
     return w;
+}
+
+// The kernels exist for sm_100 only: say so instead of letting the first launch fail with
+// "no kernel image".  One attribute query per device, remembered.
+int check_device() {
+    static std::atomic<unsigned long long> ok_mask{0};
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return NTXENT_ERR_UNSUPPORTED_DEVICE; }
+    if (dev < 64 && ((ok_mask.load(std::memory_order_relaxed) >> dev) & 1ull)) return NTXENT_OK;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    }
+    if (major != 10) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    if (dev < 64) ok_mask.fetch_or(1ull << dev, std::memory_order_relaxed);
+    return NTXENT_OK;
 }
 
 int check_shape(int64_t M, int64_t D, float tau, int dtype) {
@@ -201,14 +223,14 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, w.counter, u_ready, st));
+                              w.part_s, w.pos_t, u_ready, st));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
-                                w.part_s, w.counter, u_ready, st));
+                                w.part_s, u_ready, st));
     g_timer.stop(0, st);
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
-                                     w.part_m, w.part_s, lse_outs, lse_offset, w.block_partials, loss_outs,
-                                     loss_index, loss_scale, lse_signal, st));
+                                     w.part_m, w.part_s, p.tc ? w.pos_t : nullptr, lse_outs, lse_offset,
+                                     w.block_partials, loss_outs, loss_index, loss_scale, lse_signal, st));
     return NTXENT_OK;
 }
 
@@ -244,6 +266,9 @@ bool to_peer_signal(const ntxent_peer_signal* in, PeerSignal* out) {
     out->rank = in->rank;
     return true;
 }
+// How long a kernel waits for a peer's flag before it gives up (ntxent_b200_set_peer_wait_timeout_ms).
+std::atomic<unsigned long long> g_peer_timeout_ns{600ull * 1000ull * 1000ull * 1000ull};
+
 bool to_peer_wait(const ntxent_peer_wait* in, PeerWait* out) {
     *out = no_wait();
     if (!in) return true;
@@ -253,6 +278,8 @@ bool to_peer_wait(const ntxent_peer_wait* in, PeerWait* out) {
     out->epoch = in->epoch;
     out->ranks = in->ranks;
     out->rows_per_rank = in->rows_per_rank;
+    out->timeout_ns = g_peer_timeout_ns.load(std::memory_order_relaxed);
+    out->status = in->status;
     return true;
 }
 
@@ -403,6 +430,7 @@ int ntxent_b200_normalize(const void* z, int64_t rows, int64_t D, int dtype, uns
     if (!z || !u_out || rows < 0 || !aligned(z, 16) || !aligned(u_out, 16)) return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, rows, D, u_out, op_is_bf16(dtype, flags),
                              inv_norm_out, stream));
     return NTXENT_OK;
@@ -419,6 +447,7 @@ int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize_push(z, dtype == NTXENT_BF16, rows, D, outs, row_begin,
                                   op_is_bf16(dtype, flags), inv_norm_out, sig, stream));
     return NTXENT_OK;
@@ -447,8 +476,14 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     return run_forward_rows_push(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_outs, row_begin,
                                  loss_outs, loss_index, 1.0f, wait, sig, stream);
+}
+
+int ntxent_b200_set_peer_wait_timeout_ms(uint64_t milliseconds) {
+    g_peer_timeout_ns.store((unsigned long long)milliseconds * 1000000ull, std::memory_order_relaxed);
+    return NTXENT_OK;
 }
 
 int ntxent_b200_peer_wait(const ntxent_peer_wait* ready, ntxent_stream_t stream) {
@@ -478,6 +513,7 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau, kSym, p, p.bwd_rows,
                        w.acc_rows, w.ut, stream, wait);
     if (rc != NTXENT_OK) return rc;
@@ -505,6 +541,7 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
     const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
                             1.0f / (float)M, stream);
@@ -522,6 +559,7 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
     const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                pos_prob_out, stream);
@@ -539,6 +577,7 @@ int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_
     const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                nullptr, stream, tau_grad_rows_out);
@@ -556,6 +595,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     const Plans p = make_plans(M, D, M, opb, flags, tau);
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     rc = run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out, 1.0f / (float)M,
                           stream);
@@ -579,6 +619,7 @@ int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t ro
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     return run_forward_rows(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_rows_out,
                             loss_partial_out, 1.0f, stream);
 }
@@ -602,6 +643,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     const bool sym = (mode == NTXENT_BWD_SYMMETRIC);
     rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau,
                        sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, w.ut, stream);
@@ -640,6 +682,7 @@ int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const floa
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_finalize_dz(du_rows, z_rows, dtype == NTXENT_BF16, inv_norm_rows, grad_out, rows,
                                D, dz_out, stream));
     return NTXENT_OK;
@@ -652,8 +695,8 @@ int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const floa
 // changes none of their code paths.
 namespace {
 
-// The scratch of the forward pass (normalised operands, 1/|z|, split partials, the loss
-// reduction's counter and per-CTA partials) for ntxent_b200_forward_static.  It is part of
+// The scratch of the forward pass (normalised operands, 1/|z|, split partials, positive logits
+// and the loss reduction's per-CTA partials) for ntxent_b200_forward_static.  It is part of
 // the library image: every GPU whose context loads this library holds these bytes until the
 // process exits, whether or not the entry point is ever called.
 static __device__ __align__(256) unsigned char g_static_scratch[NTXENT_STATIC_SCRATCH_BYTES];
@@ -661,21 +704,47 @@ static __device__ __align__(256) unsigned char g_static_scratch[NTXENT_STATIC_SC
 constexpr int kMaxStaticDevices = 64;
 std::mutex g_static_mu;
 void* g_static_ptr[kMaxStaticDevices] = {};
+void* g_static_ctx[kMaxStaticDevices] = {};  // the driver context each address was looked up in
+
+// The context that is current on this thread (nullptr when the driver call cannot be had).
+void* current_context() {
+    typedef int (*GetCurrentFn)(void**);
+    static GetCurrentFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPointByVersion("cuCtxGetCurrent", &p, 12000, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            p = nullptr;
+        }
+        return reinterpret_cast<GetCurrentFn>(p);
+    }();
+    void* ctx = nullptr;
+    if (!fn || fn(&ctx) != 0) return nullptr;
+    return ctx;
+}
 
 // In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel
-// can use, so the device address is looked up once per device, with that device current.
+// can use, so the device address is looked up once per device, with that device current.  The
+// address belongs to the context it was looked up in: after cudaDeviceReset(), or when the host
+// makes another context current on the same device, the remembered one is stale, so it is kept
+// together with its context and looked up again when that changes (and on every call when the
+// current context cannot be told).
 int static_scratch_base(char** out) {
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
     if (dev < 0 || dev >= kMaxStaticDevices) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     std::lock_guard<std::mutex> lock(g_static_mu);
-    if (!g_static_ptr[dev]) {
+    void* ctx = current_context();
+    if (!g_static_ptr[dev] || !ctx || ctx != g_static_ctx[dev]) {
         void* ptr = nullptr;
         e = cudaGetSymbolAddress((void**)&ptr, g_static_scratch);
         if (e != cudaSuccess) return (int)e;
         if (!ptr) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+        if (!ctx) ctx = current_context();  // the lookup above may have been what bound a context
         g_static_ptr[dev] = ptr;
+        g_static_ctx[dev] = ctx;
     }
     *out = (char*)g_static_ptr[dev];
     return NTXENT_OK;
@@ -701,13 +770,13 @@ extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, f
     const Plans p = make_plans(M, D, M, opb, flags, tau);
     if (forward_scratch_bytes(M, D, opb, p) > (size_t)NTXENT_STATIC_SCRATCH_BYTES)
         return NTXENT_ERR_STATIC_SCRATCH_EXCEEDED;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     char* base = nullptr;
     rc = static_scratch_base(&base);
     if (rc != NTXENT_OK) return rc;
     const DeviceWs w = carve_device(base, M, D, opb, p);
-    // Nothing in the array has to start at zero except the reduction counter, and the tile
-    // kernel launched first resets that itself; every other region is written before it is read,
-    // so whatever the previous call left behind is harmless.
+    // Nothing in the array has to start at zero: every region is written before it is read, so
+    // whatever the previous call left behind is harmless.
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
     return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
                             1.0f / (float)M, stream);

@@ -47,6 +47,13 @@ struct PeerWait {
     const unsigned* epoch;  // local counter holding the value the slots must reach
     int ranks;
     int64_t rows_per_rank;  // rank r produced rows [r * rows_per_rank, (r + 1) * rows_per_rank)
+    // A peer that stalls on its host (a checkpoint write, a debugger) must not kill this rank:
+    // the wait gives up only after `timeout_ns` of %globaltimer (0: never), then sets *status to
+    // 1 + the rank it was waiting for and carries on with whatever is in the buffer -- the host
+    // reads the word (ntxent_b200_peer_wait_status) and knows the step's results are void.
+    // Without a status word the kernel traps instead (the old behaviour, now after the timeout).
+    unsigned long long timeout_ns;
+    unsigned* status;
 };
 inline PeerSignal no_signal() { PeerSignal s{}; return s; }
 inline PeerWait no_wait() { PeerWait w{}; return w; }
@@ -80,7 +87,7 @@ cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int6
 // SIMT (fp32 FMA) tile kernels.
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                             int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
-                            float* part_m, float* part_s, unsigned* counter, const PeerWait& u_ready,
+                            float* part_m, float* part_s, const PeerWait& u_ready,
                             cudaStream_t stream);
 cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
                             int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
@@ -89,20 +96,18 @@ cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_al
 // One warp that waits for every slot (for consumers that are not ours, e.g. a sum of the loss parts).
 cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream);
 
-// Forward finalize: combine the split partials into l_i, add the positive logit, reduce the loss.
-cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
-                                int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                const float* part_m, const float* part_s, float* lse_rows,
-                                float* block_partials, unsigned* counter, float* loss_out,
-                                float loss_scale, cudaStream_t stream);
-// Same with fan-out: l_i goes to element lse_offset + i of every buffer in `lse_outs`, the
-// (scaled) loss to element loss_index of every buffer in `loss_outs`.
+// Forward finalize: combine the split partials into l_i, subtract the positive logit, reduce the
+// loss.  l_i goes to element lse_offset + i of every buffer in `lse_outs`, the (scaled) loss to
+// element loss_index of every buffer in `loss_outs` (one buffer each on a single device).
+// pos_t: the positive logits in base-2 units (k u_i.u_pos(i)) as captured by the tcgen05 forward
+// tile kernel from the same MMA that feeds the denominator, or nullptr: the kernel then forms the
+// dot product of the operand rows itself (fp32-FMA family).
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                     const float* part_m, const float* part_s, const PeerList& lse_outs,
-                                     int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
-                                     int loss_index, float loss_scale, const PeerSignal& signal,
-                                     cudaStream_t stream);
+                                     const float* part_m, const float* part_s, const float* pos_t,
+                                     const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
+                                     const PeerList& loss_outs, int loss_index, float loss_scale,
+                                     const PeerSignal& signal, cudaStream_t stream);
 
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
@@ -135,6 +140,36 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& args, cudaStream_t stream
 cudaError_t launch_finalize_dz(const float* du_rows, const void* z_rows, bool z_bf16,
                                const float* inv_norm, const float* grad_out, int64_t rows, int64_t D,
                                void* dz_out, cudaStream_t stream);
+
+// ---- launching ------------------------------------------------------------------
+// Every kernel of the library is launched with programmatic stream serialisation (PDL): its
+// CTAs may become resident while the kernel before it on the stream is still draining, run their
+// set-up (barrier init, TMEM allocation, tensor-map prefetch) and then block in pdl_wait() until
+// that kernel has completed and its stores are visible.  Each kernel calls pdl_trigger() first
+// thing -- "my dependents may be scheduled once all my CTAs are running" -- and pdl_wait() before
+// its first access to global memory that another kernel of the stream reads or writes (inputs of
+// the step included: the previous step's last kernel may still be reading what this one is about
+// to overwrite).  NTXENT_NO_PDL=1 in the environment launches the plain way (for A/B runs).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 
 // ---- element access helpers ---------------------------------------------------
 template <typename T>
@@ -176,13 +211,31 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-// Spin (bounded: a lost peer traps instead of hanging the GPU) until rank r's slot reaches `want`.
-__device__ __forceinline__ void peer_wait_rank(const PeerWait& w, int r, unsigned want) {
+__device__ __forceinline__ unsigned long long peer_globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Spin until rank r's slot reaches `want`.  The bound is wall time, not a poll count, and it is
+// the caller's (default: ten minutes, the order of a collective-library watchdog): see PeerWait.
+// Returns false when it gave up.
+__device__ __forceinline__ bool peer_wait_rank(const PeerWait& w, int r, unsigned want) {
+    if ((int)(ld_acquire_sys(w.flags + r) - want) >= 0) return true;
     unsigned spins = 0;
+    unsigned long long t0 = 0;
     while ((int)(ld_acquire_sys(w.flags + r) - want) < 0) {
         __nanosleep(40);
-        if (++spins > (1u << 27)) __trap();
+        if ((++spins & 0x3ffu) == 0 && w.timeout_ns) {  // look at the clock every ~1000 polls
+            const unsigned long long now = peer_globaltimer_ns();
+            if (!t0) t0 = now;
+            if (now - t0 > w.timeout_ns) {
+                if (!w.status) __trap();
+                atomicCAS(w.status, 0u, 1u + (unsigned)r);
+                return false;
+            }
+        }
     }
+    return true;
 }
 // Ranks that produced rows [lo, hi): wait for those not yet seen ready (bit r of `ready_mask`).
 __device__ __forceinline__ void peer_wait_rows(const PeerWait& w, int64_t lo, int64_t hi, unsigned want,
@@ -192,8 +245,8 @@ __device__ __forceinline__ void peer_wait_rows(const PeerWait& w, int64_t lo, in
     const int r1 = (int)min((int64_t)w.ranks - 1, (hi - 1) / w.rows_per_rank);
     for (int r = r0; r <= r1; ++r)
         if (!((ready_mask >> r) & 1u)) {
-            peer_wait_rank(w, r, want);
-            ready_mask |= 1u << r;
+            // after a timeout nothing is waited for any more: the step is void, let it drain
+            ready_mask = peer_wait_rank(w, r, want) ? (ready_mask | (1u << r)) : 0xffffffffu;
         }
 }
 // Whole warp: one round trip that polls every rank's slot at once (lane r reads slot r); returns

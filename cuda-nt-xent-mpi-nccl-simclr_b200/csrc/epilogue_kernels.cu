@@ -13,8 +13,10 @@ constexpr int kMaxDChunks = 8;  // D <= 1024: each lane holds 4 floats per 128-w
 
 // -------------------------------------------------------------- fwd finalize ---
 constexpr int kFinalizeRowsPerWarp = 4;                       // independent rows in flight per warp
-constexpr int kFinalizeRowsPerCta = 8 * kFinalizeRowsPerWarp;  // fewer CTAs -> fewer fence+atomic round trips
+constexpr int kFinalizeRowsPerCta = 8 * kFinalizeRowsPerWarp;
 
+// fp32-FMA family (no captured positive logits): one warp per four rows, the positive logit as
+// an fp32 dot product of the operand rows.
 template <typename T>
 __global__ void __launch_bounds__(256)
 fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
@@ -22,6 +24,8 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
                     const float* __restrict__ part_s, PeerList lse_outs, int64_t lse_offset,
                     float* __restrict__ block_partials) {
     __shared__ float warp_contrib[8];
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t r0 = (int64_t)blockIdx.x * kFinalizeRowsPerCta + warp * kFinalizeRowsPerWarp;
     float m[kFinalizeRowsPerWarp], s[kFinalizeRowsPerWarp], dot[kFinalizeRowsPerWarp];
@@ -70,12 +74,57 @@ fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin
     }
 }
 
+// tcgen05 family: the forward tile kernel has already captured the positive logit of every row
+// (pos_t, base-2 units), so all that is left is one thread per row merging nsplit coalesced
+// partials: ~M * (8 nsplit + 12) bytes, against two 16 MB sweeps over U before.
+constexpr int kFinalizeThreads = 128;
+__global__ void __launch_bounds__(kFinalizeThreads)
+fwd_finalize_rows_kernel(int64_t row_count, int nsplit, const float* __restrict__ part_m,
+                         const float* __restrict__ part_s, const float* __restrict__ pos_t,
+                         PeerList lse_outs, int64_t lse_offset, float* __restrict__ block_partials) {
+    __shared__ float warp_contrib[kFinalizeThreads / 32];
+    pdl_trigger();
+    pdl_wait();
+    const int64_t r = (int64_t)blockIdx.x * kFinalizeThreads + threadIdx.x;
+    float contrib = 0.f;
+    if (r < row_count) {
+        float m = -INFINITY, s = 0.f;
+        const float pt = pos_t[r];
+        for (int sp0 = 0; sp0 < nsplit; sp0 += 8) {  // eight partial pairs in flight per thread
+            float pm[8], ps[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const bool ok = sp0 + j < nsplit;
+                pm[j] = ok ? part_m[(int64_t)(sp0 + j) * row_count + r] : -INFINITY;
+                ps[j] = ok ? part_s[(int64_t)(sp0 + j) * row_count + r] : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) lse2_merge(m, s, pm[j], ps[j]);
+        }
+        const float l2 = m + log2f(s);
+        const float l = l2 * kLn2;
+        for (int i = 0; i < lse_outs.n; ++i) static_cast<float*>(lse_outs.p[i])[lse_offset + r] = l;
+        contrib = (l2 - pt) * kLn2;
+    }
+    contrib = warp_sum(contrib);
+    if ((threadIdx.x & 31) == 0) warp_contrib[threadIdx.x >> 5] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float bsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < kFinalizeThreads / 32; ++w) bsum += warp_contrib[w];
+        block_partials[blockIdx.x] = bsum;
+    }
+}
+
 // One CTA sums the per-CTA partials in a fixed order (run-to-run deterministic).  A separate
 // launch costs less than the fence + same-address atomic of a last-CTA-done scheme here.
 __global__ void __launch_bounds__(1024)
 loss_reduce_kernel(const float* __restrict__ block_partials, int n, PeerList loss_outs, int loss_index,
                    float loss_scale, PeerSignal signal) {
     __shared__ double red[1024];
+    pdl_trigger();
+    pdl_wait();
     double acc = 0.0;
     for (int b = threadIdx.x; b < n; b += 1024) acc += (double)block_partials[b];
     red[threadIdx.x] = acc;
@@ -101,46 +150,42 @@ loss_reduce_kernel(const float* __restrict__ block_partials, int n, PeerList los
 }
 
 __global__ void __launch_bounds__(32) peer_wait_kernel(PeerWait wait) {
+    pdl_trigger();
+    pdl_wait();
     if ((int)threadIdx.x < wait.ranks) peer_wait_rank(wait, threadIdx.x, *wait.epoch);
 }
 
 cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream) {
     if (!wait.flags || !wait.epoch || wait.ranks < 1 || wait.ranks > 32) return cudaErrorInvalidValue;
-    peer_wait_kernel<<<1, 32, 0, stream>>>(wait);
-    return cudaGetLastError();
+    return launch_kernel(peer_wait_kernel, dim3(1), dim3(32), 0, stream, wait);
 }
 
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                     const float* part_m, const float* part_s, const PeerList& lse_outs,
-                                     int64_t lse_offset, float* block_partials, const PeerList& loss_outs,
-                                     int loss_index, float loss_scale, const PeerSignal& signal,
-                                     cudaStream_t stream) {
-    dim3 grid((unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta)), block(256);
-    if (op_bf16)
-        fwd_finalize_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
-            part_s, lse_outs, lse_offset, block_partials);
-    else
-        fwd_finalize_kernel<float><<<grid, block, 0, stream>>>(
-            (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m, part_s,
-            lse_outs, lse_offset, block_partials);
-    cudaError_t e = cudaGetLastError();
+                                     const float* part_m, const float* part_s, const float* pos_t,
+                                     const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
+                                     const PeerList& loss_outs, int loss_index, float loss_scale,
+                                     const PeerSignal& signal, cudaStream_t stream) {
+    cudaError_t e;
+    unsigned blocks;
+    if (pos_t) {
+        blocks = (unsigned)((row_count + kFinalizeThreads - 1) / kFinalizeThreads);
+        e = launch_kernel(fwd_finalize_rows_kernel, dim3(blocks), dim3(kFinalizeThreads), 0, stream, row_count,
+                          nsplit, part_m, part_s, pos_t, lse_outs, lse_offset, block_partials);
+    } else {
+        blocks = (unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta);
+        if (op_bf16)
+            e = launch_kernel(fwd_finalize_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
+                              (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit,
+                              part_m, part_s, lse_outs, lse_offset, block_partials);
+        else
+            e = launch_kernel(fwd_finalize_kernel<float>, dim3(blocks), dim3(256), 0, stream,
+                              (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
+                              part_s, lse_outs, lse_offset, block_partials);
+    }
     if (e != cudaSuccess) return e;
-    loss_reduce_kernel<<<1, 1024, 0, stream>>>(block_partials, (int)grid.x, loss_outs, loss_index, loss_scale,
-                                               signal);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_fwd_finalize(const void* u_all, bool op_bf16, int64_t M, int64_t D,
-                                int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                const float* part_m, const float* part_s, float* lse_rows,
-                                float* block_partials, unsigned* counter, float* loss_out,
-                                float loss_scale, cudaStream_t stream) {
-    (void)counter;
-    return launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, nsplit, part_m, part_s,
-                                    single_peer(lse_rows), 0, block_partials, single_peer(loss_out), 0,
-                                    loss_scale, no_signal(), stream);
+    return launch_kernel(loss_reduce_kernel, dim3(1), dim3(1024), 0, stream, (const float*)block_partials,
+                         (int)blocks, loss_outs, loss_index, loss_scale, signal);
 }
 
 // -------------------------------------------------------------- bwd epilogue ---
@@ -163,91 +208,142 @@ struct BwdEpiDev {
     float* tau_grad_rows_out;
 };
 
-template <typename TOp, typename TZ>
+// A warp owns kRows rows of kChunks x 128 columns each and issues the loads of all of them
+// (partials, u_pos, z) before the first use: kRows * kChunks 16-byte requests in flight per lane
+// and per operand.  (One row per warp, as this kernel used to work, left it latency-bound at
+// 19 % of the HBM peak.)
+template <typename TOp, typename TZ, int kChunks, int kRows>
 __global__ void __launch_bounds__(256)
 bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict__ z_rows,
                     TZ* __restrict__ dz_out) {
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
-    const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (r >= p.a_count) return;
+    const int64_t r0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * kRows;
+    if (r0 >= p.a_count) return;
+    pdl_wait();
     const int D = p.D;
-    const int64_t row = p.a_begin + r;
-    const int64_t pos = (row + p.M / 2) % p.M;
-    const float pc = (pos >= p.pos_lo && pos < p.pos_hi) ? p.pos_coeff : 0.f;
-    const TOp* up = U + pos * D;
-    int nsplit = p.nsplit;
-    if (p.sk_ctas > 0) {  // CTAs whose tile ranges touch this row tile (tc_kernels.cu, BwdUnit)
-        const int64_t first = (r / 128) * p.sk_col_tiles;
-        nsplit = (int)(((first + p.sk_col_tiles) * p.sk_ctas - 1) / p.sk_total -
-                       ((first + 1) * p.sk_ctas - 1) / p.sk_total) + 1;
-    }
-    float4 du[kMaxDChunks];
+    float4 du[kRows][kChunks], zz[kRows][kChunks];
+    int64_t pos[kRows];
+    float pc[kRows], inv[kRows];
+    const bool jac = p.du_out == nullptr;
+    // loads first: z, 1/|z|, u_pos ...
 #pragma unroll
-    for (int c = 0; c < kMaxDChunks; ++c) {
-        const int k = c * 128 + lane * 4;
-        if (k >= D) break;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int sp = 0; sp < nsplit; ++sp) {
-            const float4 t =
-                *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
-            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    for (int q = 0; q < kRows; ++q) {
+        const int64_t r = min(r0 + q, p.a_count - 1);  // rows past the end redo the last row, unstored
+        const int64_t row = p.a_begin + r;
+        pos[q] = (row + p.M / 2) % p.M;
+        pc[q] = (pos[q] >= p.pos_lo && pos[q] < p.pos_hi) ? p.pos_coeff : 0.f;
+        inv[q] = jac ? p.inv_norm[r] : 0.f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            const int k = c * 128 + lane * 4;
+            zz[q][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            du[q][c] = zz[q][c];
+            if (k < D) {
+                if (jac) zz[q][c] = Elem<TZ>::ld4(z_rows + r * D + k);
+                if (pc[q] != 0.f) {
+                    const float4 u = Elem<TOp>::ld4(U + pos[q] * D + k);
+                    du[q][c] = make_float4(-pc[q] * u.x, -pc[q] * u.y, -pc[q] * u.z, -pc[q] * u.w);
+                }
+            }
         }
-        if (pc != 0.f) {
-            const float4 q = Elem<TOp>::ld4(up + k);
-            v.x -= pc * q.x; v.y -= pc * q.y; v.z -= pc * q.z; v.w -= pc * q.w;
-        }
-        v.x *= p.scale; v.y *= p.scale; v.z *= p.scale; v.w *= p.scale;
-        du[c] = v;
     }
-    if (p.pos_prob_out) {
-        const TOp* ui = U + row * D;
+    // ... then the partials of each row tile, added in slot order (deterministic)
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+        const int64_t r = min(r0 + q, p.a_count - 1);
+        int nsplit = p.nsplit;
+        if (p.sk_ctas > 0) {  // CTAs whose tile ranges touch this row tile (tc_kernels.cu, BwdUnit)
+            const int64_t first = (r / 128) * p.sk_col_tiles;
+            nsplit = (int)(((first + p.sk_col_tiles) * p.sk_ctas - 1) / p.sk_total -
+                           ((first + 1) * p.sk_ctas - 1) / p.sk_total) + 1;
+        }
+        float4 acc[kChunks];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int sp = 0; sp < nsplit; ++sp) {
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const int k = c * 128 + lane * 4;
+                if (k < D) {
+                    const float4 t =
+                        *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
+                    acc[c].x += t.x; acc[c].y += t.y; acc[c].z += t.z; acc[c].w += t.w;
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            du[q][c].x = (du[q][c].x + acc[c].x) * p.scale;
+            du[q][c].y = (du[q][c].y + acc[c].y) * p.scale;
+            du[q][c].z = (du[q][c].z + acc[c].z) * p.scale;
+            du[q][c].w = (du[q][c].w + acc[c].w) * p.scale;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+        const int64_t r = r0 + q;
+        if (r >= p.a_count) break;
+        const int64_t row = p.a_begin + r;
+        if (p.pos_prob_out) {
+            const TOp* ui = U + row * D;
+            const TOp* up = U + pos[q] * D;
+            float dot = 0.f;
+            for (int k = lane * 4; k < D; k += 128) {
+                const float4 a = Elem<TOp>::ld4(ui + k), b = Elem<TOp>::ld4(up + k);
+                dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+            }
+            dot = warp_sum(dot);
+            if (lane == 0) p.pos_prob_out[r] = expf(dot * p.inv_tau - p.lse_all[row]);
+        }
+        if (!jac) {
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const int k = c * 128 + lane * 4;
+                if (k < D) *reinterpret_cast<float4*>(p.du_out + r * D + k) = du[q][c];
+            }
+            continue;
+        }
+        // normalisation Jacobian with the exact fp32 direction u = z * inv_norm
+        const float g = p.grad_out ? *p.grad_out : 1.0f;
         float dot = 0.f;
-        for (int k = lane * 4; k < D; k += 128) {
-            const float4 a = Elem<TOp>::ld4(ui + k), b = Elem<TOp>::ld4(up + k);
-            dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            float4& u = zz[q][c];
+            u.x *= inv[q]; u.y *= inv[q]; u.z *= inv[q]; u.w *= inv[q];
+            dot += du[q][c].x * u.x + du[q][c].y * u.y + du[q][c].z * u.z + du[q][c].w * u.w;
         }
         dot = warp_sum(dot);
-        if (lane == 0) p.pos_prob_out[r] = expf(dot * p.inv_tau - p.lse_all[row]);
-    }
-    if (p.du_out) {
+        // sum_a dU_a . u_a = -2 tau dL/dtau (each logit S_ab = u_a.u_b / tau appears once as row a's
+        // and once as row b's): the temperature gradient falls out of the Jacobian's dot product
+        if (p.tau_grad_rows_out && lane == 0) p.tau_grad_rows_out[r] = -0.5f * p.inv_tau * dot;
+        const float gi = g * inv[q];
 #pragma unroll
-        for (int c = 0; c < kMaxDChunks; ++c) {
+        for (int c = 0; c < kChunks; ++c) {
             const int k = c * 128 + lane * 4;
             if (k >= D) break;
-            *reinterpret_cast<float4*>(p.du_out + r * D + k) = du[c];
+            float4 o;
+            o.x = gi * (du[q][c].x - dot * zz[q][c].x);
+            o.y = gi * (du[q][c].y - dot * zz[q][c].y);
+            o.z = gi * (du[q][c].z - dot * zz[q][c].z);
+            o.w = gi * (du[q][c].w - dot * zz[q][c].w);
+            Elem<TZ>::st4(dz_out + r * D + k, o);
         }
-        return;
     }
-    // normalisation Jacobian with the exact fp32 direction u = z * inv_norm
-    const float inv = p.inv_norm[r];
-    const float g = p.grad_out ? *p.grad_out : 1.0f;
-    float4 u[kMaxDChunks];
-    float dot = 0.f;
-#pragma unroll
-    for (int c = 0; c < kMaxDChunks; ++c) {
-        const int k = c * 128 + lane * 4;
-        if (k >= D) break;
-        float4 zz = Elem<TZ>::ld4(z_rows + r * D + k);
-        zz.x *= inv; zz.y *= inv; zz.z *= inv; zz.w *= inv;
-        u[c] = zz;
-        dot += du[c].x * zz.x + du[c].y * zz.y + du[c].z * zz.z + du[c].w * zz.w;
-    }
-    dot = warp_sum(dot);
-    // sum_a dU_a . u_a = -2 tau dL/dtau (each logit S_ab = u_a.u_b / tau appears once as row a's
-    // and once as row b's): the temperature gradient falls out of the Jacobian's dot product
-    if (p.tau_grad_rows_out && lane == 0) p.tau_grad_rows_out[r] = -0.5f * p.inv_tau * dot;
-    const float gi = g * inv;
-#pragma unroll
-    for (int c = 0; c < kMaxDChunks; ++c) {
-        const int k = c * 128 + lane * 4;
-        if (k >= D) break;
-        float4 o;
-        o.x = gi * (du[c].x - dot * u[c].x);
-        o.y = gi * (du[c].y - dot * u[c].y);
-        o.z = gi * (du[c].z - dot * u[c].z);
-        o.w = gi * (du[c].w - dot * u[c].w);
-        Elem<TZ>::st4(dz_out + r * D + k, o);
-    }
+}
+
+template <typename TOp, typename TZ>
+static cudaError_t launch_bwd_epilogue_t(const BwdEpiDev& p, const BwdEpilogueArgs& a, cudaStream_t stream) {
+    const int chunks = (p.D + 127) / 128;
+    dim3 block(256);
+#define NTX_EPI(C, R)                                                                                   \
+    launch_kernel(bwd_epilogue_kernel<TOp, TZ, C, R>, dim3((unsigned)((a.a_count + 8 * R - 1) / (8 * R))), \
+                  block, 0, stream, p, (const TOp*)a.u_all, (const TZ*)a.z_rows, (TZ*)a.dz_out)
+    if (chunks <= 1) return NTX_EPI(1, 4);
+    if (chunks <= 2) return NTX_EPI(2, 2);
+    if (chunks <= 4) return NTX_EPI(4, 1);
+    return NTX_EPI(8, 1);
+#undef NTX_EPI
 }
 
 cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
@@ -260,24 +356,11 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
     p.scale = a.scale; p.du_out = a.du_out; p.inv_norm = a.inv_norm; p.grad_out = a.grad_out;
     p.lse_all = a.lse_all; p.inv_tau = a.inv_tau; p.pos_prob_out = a.pos_prob_out;
     p.tau_grad_rows_out = a.du_out ? nullptr : a.tau_grad_rows_out;
-    dim3 grid((unsigned)((a.a_count + 7) / 8)), block(256);
-    if (a.op_bf16) {
-        if (a.z_bf16)
-            bwd_epilogue_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, stream>>>(
-                p, (const __nv_bfloat16*)a.u_all, (const __nv_bfloat16*)a.z_rows,
-                (__nv_bfloat16*)a.dz_out);
-        else
-            bwd_epilogue_kernel<__nv_bfloat16, float><<<grid, block, 0, stream>>>(
-                p, (const __nv_bfloat16*)a.u_all, (const float*)a.z_rows, (float*)a.dz_out);
-    } else {
-        if (a.z_bf16)
-            bwd_epilogue_kernel<float, __nv_bfloat16><<<grid, block, 0, stream>>>(
-                p, (const float*)a.u_all, (const __nv_bfloat16*)a.z_rows, (__nv_bfloat16*)a.dz_out);
-        else
-            bwd_epilogue_kernel<float, float><<<grid, block, 0, stream>>>(
-                p, (const float*)a.u_all, (const float*)a.z_rows, (float*)a.dz_out);
-    }
-    return cudaGetLastError();
+    if (a.op_bf16)
+        return a.z_bf16 ? launch_bwd_epilogue_t<__nv_bfloat16, __nv_bfloat16>(p, a, stream)
+                        : launch_bwd_epilogue_t<__nv_bfloat16, float>(p, a, stream);
+    return a.z_bf16 ? launch_bwd_epilogue_t<float, __nv_bfloat16>(p, a, stream)
+                    : launch_bwd_epilogue_t<float, float>(p, a, stream);
 }
 
 // --------------------------------------------------------------- finalize dz ---
@@ -286,9 +369,11 @@ __global__ void __launch_bounds__(256)
 finalize_dz_kernel(const float* __restrict__ du_rows, const TZ* __restrict__ z_rows,
                    const float* __restrict__ inv_norm, const float* __restrict__ grad_out,
                    int64_t rows, int D, TZ* __restrict__ dz_out) {
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (r >= rows) return;
+    pdl_wait();
     const float inv = inv_norm[r];
     const float g = grad_out ? *grad_out : 1.0f;
     float dot = 0.f;
@@ -317,13 +402,11 @@ cudaError_t launch_finalize_dz(const float* du_rows, const void* z_rows, bool z_
     if (rows == 0) return cudaSuccess;
     dim3 grid((unsigned)((rows + 7) / 8)), block(256);
     if (z_bf16)
-        finalize_dz_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
-            du_rows, (const __nv_bfloat16*)z_rows, inv_norm, grad_out, rows, (int)D,
-            (__nv_bfloat16*)dz_out);
-    else
-        finalize_dz_kernel<float><<<grid, block, 0, stream>>>(du_rows, (const float*)z_rows, inv_norm,
-                                                            grad_out, rows, (int)D, (float*)dz_out);
-    return cudaGetLastError();
+        return launch_kernel(finalize_dz_kernel<__nv_bfloat16>, grid, block, 0, stream, du_rows,
+                             (const __nv_bfloat16*)z_rows, inv_norm, grad_out, rows, (int)D,
+                             (__nv_bfloat16*)dz_out);
+    return launch_kernel(finalize_dz_kernel<float>, grid, block, 0, stream, du_rows, (const float*)z_rows,
+                         inv_norm, grad_out, rows, (int)D, (float*)dz_out);
 }
 
 }  // namespace ntxent_b200

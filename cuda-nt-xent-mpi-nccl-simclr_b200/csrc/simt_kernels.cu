@@ -17,39 +17,59 @@
 namespace ntxent_b200 {
 
 // ------------------------------------------------------------------ normalise ---
-// One warp per row.  u = z / max(|z|, eps), computed as (z/amax) / |z/amax| so that
-// rows scaled by 1e-5 .. 1e5 (python/test.py:64) neither underflow nor overflow.
-template <typename TIn, typename TOut>
+// u = z / max(|z|, eps), computed as (z/amax) / |z/amax| so that rows scaled by 1e-5 .. 1e5
+// (python/test.py:64) neither underflow nor overflow.  One pass: a warp keeps kRows whole rows
+// in registers (kChunks x 128 columns each), with every load issued before the first use, so
+// that each lane has kRows * kChunks 16-byte (fp32) or 8-byte (bf16) requests in flight -- the
+// one-row-per-warp, three-pass version this replaces ran at 21 % of the HBM peak.
+template <typename TIn, typename TOut, int kChunks, int kRows>
 __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ z, int64_t rows,
                                                         int D, PeerList outs, int64_t row_offset,
                                                         float* __restrict__ inv_norm) {
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= rows) return;
-    const TIn* zr = z + row * D;
-    float amax = 0.f;
-    for (int k = lane * 4; k < D; k += 128) {
-        float4 v = Elem<TIn>::ld4(zr + k);
-        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
-    }
-    amax = warp_max(amax);
-    const float sc = (amax > 0.f && amax < INFINITY) ? 1.0f / amax : 1.0f;
-    float ss = 0.f;
-    for (int k = lane * 4; k < D; k += 128) {
-        float4 v = Elem<TIn>::ld4(zr + k);
-        v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
-        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-    }
-    ss = warp_sum(ss);
-    const float nrm = sqrtf(ss) / sc;  // |z|
-    const float inv = 1.0f / fmaxf(nrm, kNormEps);
-    if (lane == 0 && inv_norm) inv_norm[row] = inv;
-    for (int k = lane * 4; k < D; k += 128) {
-        float4 v = Elem<TIn>::ld4(zr + k);
-        v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-        // one local store, or the same row pushed into every rank's gathered copy (peer stores)
-        for (int i = 0; i < outs.n; ++i)
-            Elem<TOut>::st4(static_cast<TOut*>(outs.p[i]) + (row_offset + row) * D + k, v);
+    const int64_t row0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * kRows;
+    if (row0 >= rows) return;
+    pdl_wait();  // the previous step's epilogue may still be reading the U this kernel overwrites
+    float4 v[kRows][kChunks];
+#pragma unroll
+    for (int q = 0; q < kRows; ++q)
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            const int k = c * 128 + lane * 4;
+            v[q][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row0 + q < rows && k < D) v[q][c] = Elem<TIn>::ld4(z + (row0 + q) * D + k);
+        }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q) {
+        float amax = 0.f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c)
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[q][c].x), fabsf(v[q][c].y)),
+                                     fmaxf(fabsf(v[q][c].z), fabsf(v[q][c].w))));
+        amax = warp_max(amax);
+        const float sc = (amax > 0.f && amax < INFINITY) ? 1.0f / amax : 1.0f;
+        float ss = 0.f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            const float4 t = make_float4(v[q][c].x * sc, v[q][c].y * sc, v[q][c].z * sc, v[q][c].w * sc);
+            ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+        }
+        ss = warp_sum(ss);
+        const float nrm = sqrtf(ss) / sc;  // |z|
+        const float inv = 1.0f / fmaxf(nrm, kNormEps);
+        const int64_t row = row0 + q;
+        if (row >= rows) break;
+        if (lane == 0 && inv_norm) inv_norm[row] = inv;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            const int k = c * 128 + lane * 4;
+            if (k >= D) break;
+            const float4 t = make_float4(v[q][c].x * inv, v[q][c].y * inv, v[q][c].z * inv, v[q][c].w * inv);
+            // one local store, or the same row pushed into every rank's gathered copy (peer stores)
+            for (int i = 0; i < outs.n; ++i)
+                Elem<TOut>::st4(static_cast<TOut*>(outs.p[i]) + (row_offset + row) * D + k, t);
+        }
     }
 }
 
@@ -58,6 +78,8 @@ __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ 
 // writing it to every rank's slot is all it takes -- measured far cheaper than ending each of
 // the ~2000 normalize blocks with a system-scope fence (+11 us at 16384 x 128 on two GPUs).
 __global__ void __launch_bounds__(32) peer_signal_kernel(PeerSignal s) {
+    pdl_trigger();
+    pdl_wait();  // (this is the "kernel before me has finished" the comment above relies on)
     unsigned e = 0;
     if (threadIdx.x == 0) {
         e = *s.epoch + 1u;
@@ -67,27 +89,36 @@ __global__ void __launch_bounds__(32) peer_signal_kernel(PeerSignal s) {
     if ((int)threadIdx.x < s.flags.n) st_release_sys(static_cast<unsigned*>(s.flags.p[threadIdx.x]) + s.rank, e);
 }
 
+template <typename TIn, typename TOut>
+static cudaError_t launch_normalize_t(const void* z, int64_t rows, int64_t D, const PeerList& outs,
+                                      int64_t row_offset, float* inv_norm, cudaStream_t stream) {
+    const int chunks = (int)((D + 127) / 128);
+    dim3 block(256);
+#define NTX_NORM(C, R)                                                                           \
+    launch_kernel(normalize_kernel<TIn, TOut, C, R>, dim3((unsigned)((rows + 8 * R - 1) / (8 * R))), \
+                  block, 0, stream, (const TIn*)z, rows, (int)D, outs, row_offset, inv_norm)
+    if (chunks <= 1) return NTX_NORM(1, 4);
+    if (chunks <= 2) return NTX_NORM(2, 4);
+    if (chunks <= 4) return NTX_NORM(4, 2);
+    return NTX_NORM(8, 1);
+#undef NTX_NORM
+}
+
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
                                   float* inv_norm, const PeerSignal& signal, cudaStream_t stream) {
     if (rows == 0) return signal.epoch ? cudaErrorInvalidValue : cudaSuccess;
-    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
+    cudaError_t e;
     if (z_bf16 && op_bf16)
-        normalize_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)z, rows, (int)D, outs, row_offset, inv_norm);
+        e = launch_normalize_t<__nv_bfloat16, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream);
     else if (z_bf16)
-        normalize_kernel<__nv_bfloat16, float><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)z, rows, (int)D, outs, row_offset, inv_norm);
+        e = launch_normalize_t<__nv_bfloat16, float>(z, rows, D, outs, row_offset, inv_norm, stream);
     else if (op_bf16)
-        normalize_kernel<float, __nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const float*)z, rows, (int)D, outs, row_offset, inv_norm);
+        e = launch_normalize_t<float, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream);
     else
-        normalize_kernel<float, float><<<grid, block, 0, stream>>>((const float*)z, rows, (int)D, outs,
-                                                                  row_offset, inv_norm);
-    cudaError_t e = cudaGetLastError();
+        e = launch_normalize_t<float, float>(z, rows, D, outs, row_offset, inv_norm, stream);
     if (e != cudaSuccess || !signal.epoch) return e;
-    peer_signal_kernel<<<1, 32, 0, stream>>>(signal);
-    return cudaGetLastError();
+    return launch_kernel(peer_signal_kernel, dim3(1), dim3(32), 0, stream, signal);
 }
 
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
@@ -140,10 +171,11 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
                 float scale_log2, int64_t cols_per_split, float* __restrict__ part_m,
-                float* __restrict__ part_s, unsigned* __restrict__ counter, PeerWait u_ready) {
+                float* __restrict__ part_s, PeerWait u_ready) {
     __shared__ __align__(16) float As[kTK][kTM + kPad];
     __shared__ __align__(16) float Bs[kTK][kTN + kPad];
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *counter = 0u;
+    pdl_trigger();
+    pdl_wait();
     peer_wait_all_block(u_ready);  // multi-GPU push path: every rank's rows of U have landed
     const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
     const int64_t a0 = row_begin + (int64_t)blockIdx.x * kTM;
@@ -194,20 +226,16 @@ simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, in
 
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                             int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
-                            float* part_m, float* part_s, unsigned* counter, const PeerWait& u_ready,
+                            float* part_m, float* part_s, const PeerWait& u_ready,
                             cudaStream_t stream) {
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit), block(256);
     const float scale_log2 = kLog2e / tau;
     if (op_bf16)
-        simt_fwd_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(
-            (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, scale_log2,
-            plan.cols_per_split, part_m, part_s, counter, u_ready);
-    else
-        simt_fwd_kernel<float><<<grid, block, 0, stream>>>((const float*)u_all, M, (int)D,
-                                                           row_begin, row_count, scale_log2,
-                                                           plan.cols_per_split, part_m, part_s,
-                                                           counter, u_ready);
-    return cudaGetLastError();
+        return launch_kernel(simt_fwd_kernel<__nv_bfloat16>, grid, block, 0, stream,
+                             (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, scale_log2,
+                             plan.cols_per_split, part_m, part_s, u_ready);
+    return launch_kernel(simt_fwd_kernel<float>, grid, block, 0, stream, (const float*)u_all, M, (int)D,
+                         row_begin, row_count, scale_log2, plan.cols_per_split, part_m, part_s, u_ready);
 }
 
 // --------------------------------------------------------------- backward ---
@@ -218,10 +246,12 @@ constexpr int kDC = 128;
 
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256)
-simt_bwd_kernel(const T* __restrict__ U, const float* __restrict__ lse, int64_t M, int D,
+simt_bwd_kernel(const T* __restrict__ U, const float* lse, int64_t M, int D,
                 int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                 float scale_log2, int64_t cols_per_split, float* __restrict__ acc_out,
                 PeerWait lse_ready) {
+    pdl_trigger();
+    pdl_wait();
     peer_wait_all_block(lse_ready);  // multi-GPU push path: every rank's l has landed
     __shared__ __align__(16) float As[kTK][kTM + kPad];
     __shared__ __align__(16) float Bs[kTK][kTN + kPad];
@@ -316,24 +346,15 @@ static cudaError_t launch_simt_bwd_t(const T* U, const float* lse, int64_t M, in
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit, (unsigned)((D + kDC - 1) / kDC));
     dim3 block(256);
     const float sl2 = kLog2e / tau;
+#define NTX_SIMT_BWD(MODE)                                                                            \
+    launch_kernel(simt_bwd_kernel<T, MODE>, grid, block, 0, stream, U, lse, M, (int)D, a_begin, a_count, \
+                  b_begin, b_count, sl2, plan.cols_per_split, acc, lse_ready)
     switch (mode) {
-        case kSym:
-            simt_bwd_kernel<T, kSym><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
-                                                                b_begin, b_count, sl2,
-                                                                plan.cols_per_split, acc, lse_ready);
-            break;
-        case kRow:
-            simt_bwd_kernel<T, kRow><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
-                                                                b_begin, b_count, sl2,
-                                                                plan.cols_per_split, acc, lse_ready);
-            break;
-        default:
-            simt_bwd_kernel<T, kCol><<<grid, block, 0, stream>>>(U, lse, M, (int)D, a_begin, a_count,
-                                                                b_begin, b_count, sl2,
-                                                                plan.cols_per_split, acc, lse_ready);
-            break;
+        case kSym: return NTX_SIMT_BWD(kSym);
+        case kRow: return NTX_SIMT_BWD(kRow);
+        default: return NTX_SIMT_BWD(kCol);
     }
-    return cudaGetLastError();
+#undef NTX_SIMT_BWD
 }
 
 cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,

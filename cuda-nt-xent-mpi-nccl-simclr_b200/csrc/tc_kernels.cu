@@ -84,10 +84,17 @@ __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
 // already t = log2(e)/tau * u_a.u_b: the A operand was scaled by k = log2(e)/tau when it was
 // staged, which saves one FFMA per logit.  The fixed-max form sums 2^t as is (t <= k <= 50, so
 // M terms of at most 2^50 stay far inside fp32) and reports max = 0.
+// On the masked path the chunk is also searched for the row's positive, column pos_col: its
+// logit t goes to pos_t (the tiles that can hold it are always sent down the masked path).
 template <bool kOnline>
 __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special, int64_t col0,
-                                          int64_t row, int64_t M, float k_scale, float& m_run,
-                                          float& s_run) {
+                                          int64_t row, int64_t M, int64_t pos_col, float& pos_t,
+                                          float& m_run, float& s_run) {
+    if (special) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+            if (col0 + e == pos_col) pos_t = __uint_as_float(v[e]);
+    }
     if (!kOnline) {
         float p0 = 0.f, p1 = 0.f;
         if (!special) {
@@ -129,7 +136,7 @@ template <int D, bool TF32, bool kOnline>
 __global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
               int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
-              float* __restrict__ part_m, float* __restrict__ part_s, unsigned* __restrict__ counter,
+              float* __restrict__ part_m, float* __restrict__ part_s, float* __restrict__ pos_t_out,
               PeerWait u_ready) {
     using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
@@ -147,7 +154,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *counter = 0u;
+    pdl_trigger();
 
     const int64_t a0 = row_begin + (int64_t)blockIdx.x * kTile;
     const int jt0 = blockIdx.y * tiles_per_split;
@@ -166,6 +173,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // set-up done; from here on the kernel reads what the normalise kernel wrote
 
     if (warp == kFwdTmaWarp) {
         // multi-GPU push path: a tile is loaded once the ranks that produced its rows have
@@ -174,7 +182,17 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         unsigned want;
         unsigned ready_mask = peer_poll_all_warp(u_ready, want);
         if (lane == 0) {
-            peer_wait_rows(u_ready, a0, min(M, a0 + kTile), want, ready_mask);
+            // the flags are read through the generic proxy, the rows they cover through the async
+            // proxy (TMA): a cross-proxy fence after every acquire that let new rows in
+            unsigned fenced_mask = ~ready_mask;
+            auto wait_rows = [&](int64_t lo, int64_t hi) {
+                peer_wait_rows(u_ready, lo, hi, want, ready_mask);
+                if (u_ready.flags && fenced_mask != ready_mask) {
+                    fence_proxy_async_global();
+                    fenced_mask = ready_mask;
+                }
+            };
+            wait_rows(a0, min(M, a0 + kTile));
             mbar_arrive_expect_tx(q_full, C::kTileBytes);
             for (int a = 0; a < C::kAtoms; ++a)
                 tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * C::kAtomCols, (int32_t)a0);
@@ -182,7 +200,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 const int st = it % NS;
                 const uint32_t ph = (it / NS) & 1;
                 const int64_t c0 = (int64_t)(jt0 + it) * kTile;
-                peer_wait_rows(u_ready, c0, min(M, c0 + kTile), want, ready_mask);
+                wait_rows(c0, min(M, c0 + kTile));
                 mbar_wait(&k_empty[st], ph ^ 1);
                 mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                 for (int a = 0; a < C::kAtoms; ++a)
@@ -258,15 +276,25 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         // this row tile's own rows (the diagonal) and everything from the ragged end of the range
         const int hj_diag_lo = (int)(a0 / 64), hj_diag_hi = (int)((a0 + 63) / 64) + 1;
         const int hj_ragged = (int)(M / 64);
+        // ... and those that hold the positives of this row tile, columns (a0 + N + i) mod M: one run
+        // of 128 columns, or two when it wraps around M
+        const int64_t p0 = (a0 + M / 2) % M;
+        const int hj_pos_lo = (int)(p0 / 64), hj_pos_hi = (int)((min(p0 + kTile, M) - 1) / 64);
+        const int hj_wrap_hi = p0 + kTile > M ? (int)((p0 + kTile - M - 1) / 64) : -1;
+        const int64_t pos_col = (row + M / 2) % M;
+        float pos_t = 0.f;
+        bool pos_seen = false;
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
             const int hj = 2 * (jt0 + it) + half;
-            const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged;
+            const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged ||
+                                 (hj >= hj_pos_lo && hj <= hj_pos_hi) || hj <= hj_wrap_hi;
+            pos_seen |= (pos_col >> 6) == hj;
             const int64_t j0 = (int64_t)hj * 64;  // (used on the masked path only)
             const uint32_t taddr = lane_addr + buf * kTile;
             tmem_ld_wait();
             tmem_ld32(taddr + 32, vb);
-            fwd_chunk<kOnline>(va, special, j0, row, M, k_scale, m_run, s_run);
+            fwd_chunk<kOnline>(va, special, j0, row, M, pos_col, pos_t, m_run, s_run);
             tmem_ld_wait();
             // this warp's S columns have left TMEM: hand the buffer back, then prefetch
             tc_fence_before();
@@ -277,8 +305,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 tc_fence_after();
                 tmem_ld32(lane_addr + (buf ^ 1) * kTile, va);
             }
-            fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, k_scale, m_run, s_run);
+            fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, pos_col, pos_t, m_run, s_run);
         }
+        // the positive logit, from the same MMA (same operand rounding) as the denominator
+        if (pos_seen && row < M && row < row_begin + row_count) pos_t_out[row - row_begin] = pos_t;
         // merge the two column halves of each row (upper half hands over through shared memory)
         float2* halves = reinterpret_cast<float2*>(q_tile);  // the row tile is no longer needed:
         named_bar_sync(1, kSoftmaxThreads);                  // every MMA that read it has completed
@@ -459,7 +489,7 @@ template <int D, bool TF32, int MODE, bool kTwoExp>
 __global__ void __launch_bounds__(BwdCfg<D, TF32>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_t,
               const void* __restrict__ U_raw,
-              const float* __restrict__ lse, int64_t M, int64_t a_begin, int64_t a_count,
+              const float* lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int col_tiles, int64_t total_tiles,
               float* __restrict__ acc_out, unsigned long long* __restrict__ trace, PeerWait lse_ready) {
     using C = Cfg<D, TF32>;
@@ -489,6 +519,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cc_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_trigger();
     NTX_TRACE_U(63, 0, clock64());
     NTX_TRACE_U(63, 6, globaltimer_ns());
     const int64_t a_end = a_begin + a_count, b_end = b_begin + b_count;
@@ -519,6 +550,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // set-up done; U, l and the accumulator slots belong to earlier kernels until here
     NTX_TRACE_U(63, 1, clock64());
 
     if (warp == B::kTmaWarp) {
@@ -648,13 +680,15 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                             const int c = base + j * 128 + lane * 4;
                             l[j] = make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
                             if (c < ncols) {
+                                // (peers may still be storing other blocks of l while this kernel
+                                // runs: coherent loads, never ld.global.nc)
                                 if (vec_ok && c0 + c + 3 < b_end) {
-                                    l[j] = __ldg(reinterpret_cast<const float4*>(lse + c0 + c));
+                                    l[j] = ld_f4_coherent(lse + c0 + c);
                                 } else {
-                                    if (c0 + c < b_end) l[j].x = __ldg(lse + c0 + c);
-                                    if (c0 + c + 1 < b_end) l[j].y = __ldg(lse + c0 + c + 1);
-                                    if (c0 + c + 2 < b_end) l[j].z = __ldg(lse + c0 + c + 2);
-                                    if (c0 + c + 3 < b_end) l[j].w = __ldg(lse + c0 + c + 3);
+                                    if (c0 + c < b_end) l[j].x = ld_f1_coherent(lse + c0 + c);
+                                    if (c0 + c + 1 < b_end) l[j].y = ld_f1_coherent(lse + c0 + c + 1);
+                                    if (c0 + c + 2 < b_end) l[j].z = ld_f1_coherent(lse + c0 + c + 2);
+                                    if (c0 + c + 3 < b_end) l[j].w = ld_f1_coherent(lse + c0 + c + 3);
                                 }
                             }
                         }
@@ -746,7 +780,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             float row_c = 0.f;
             if (MODE != kCol) {
                 if (row_ok) {
-                    const float l2 = lse[row] * kLog2e;
+                    const float l2 = ld_f1_coherent(lse + row) * kLog2e;  // this rank's own rows
                     row_c = (MODE == kSym && !kTwoExp) ? ex2(-l2) : l2;
                 } else {
                     row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
@@ -791,6 +825,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                     weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
                                                       b_end);
                 }
+#ifdef NTXENT_DROP_TILE
+                // Fault injection for the parity tests' own test (tools/drop_tile_proof.py): a build
+                // with this define loses the weights of ONE tile; the full-size comparison must notice.
+                if (u.rt == 100 && jt == 37) {
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) packed[e] = 0u;
+                }
+#endif
                 NTX_TRACE(trole, it, 3);
                 if (SEP) {
                     tc_fence_after();
@@ -905,25 +947,70 @@ cudaError_t make_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
+// Encoding a tensor map is ~1-2 us of host time per call and the same few (pointer, shape) pairs
+// come back every step: keep the last ones.  (A map only encodes address, shape and layout, so a
+// hit stays valid when the buffer was freed and handed out again at the same address.)
+struct TmapKey {
+    const void* base; int64_t rows, cols; int box_rows; bool tf32;
+    bool operator==(const TmapKey& o) const {
+        return base == o.base && rows == o.rows && cols == o.cols && box_rows == o.box_rows && tf32 == o.tf32;
+    }
+};
+cudaError_t cached_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols, int box_rows,
+                           CUtensorMap* out) {
+    constexpr int kSlots = 32;
+    static std::mutex mu;
+    static TmapKey keys[kSlots];
+    static CUtensorMap maps[kSlots];
+    static int used = 0, next = 0;
+    const TmapKey key{base, rows, cols, box_rows, tf32};
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (int i = 0; i < used; ++i)
+            if (keys[i] == key) { *out = maps[i]; return cudaSuccess; }
+    }
+    cudaError_t e = make_tmap_2d(base, tf32, rows, cols, box_rows, out);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    const int slot = used < kSlots ? used++ : (next++ % kSlots);
+    keys[slot] = key;
+    maps[slot] = *out;
+    return cudaSuccess;
+}
+
 cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtensorMap* out) {
-    return make_tmap_2d(u_all, tf32, M, D, kTile, out);
+    return cached_tmap_2d(u_all, tf32, M, D, kTile, out);
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per function and per device: set it the first
+// time an instantiation is launched on a device, not on every launch.
+template <typename K>
+cudaError_t set_smem_once(K kern, int smem, unsigned long long& done_mask) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev < 64 && ((done_mask >> dev) & 1ull)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && dev < 64) done_mask |= 1ull << dev;
+    return e;
 }
 
 template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
-                         float* part_s, unsigned* counter, const PeerWait& u_ready, cudaStream_t stream) {
+                         float* part_s, float* pos_t, const PeerWait& u_ready, cudaStream_t stream) {
     using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
     const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
     auto kern = tc_fwd_kernel<D, TF32, kOnline>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    static unsigned long long attr_done = 0;
+    cudaError_t e = set_smem_once(kern, smem, attr_done);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
-    kern<<<grid, kThreads, smem, stream>>>(tmap, M, row_begin, row_count, k_scale,
-                                          (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s,
-                                          counter, u_ready);
-    return cudaGetLastError();
+    return launch_kernel(kern, grid, dim3(kThreads), smem, stream, tmap, M, row_begin, row_count, k_scale,
+                         (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s, pos_t, u_ready);
 }
 
 // U [M, D] fp32 -> UT [D, Mpad] (Mpad = M rounded up to 4, pad columns zero): the K-major B operand
@@ -931,6 +1018,8 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
 __global__ void __launch_bounds__(256) transpose_f32_kernel(const float* __restrict__ U, int64_t M, int D,
                                                             int64_t Mpad, float* __restrict__ UT) {
     __shared__ float tile[32][33];
+    pdl_trigger();
+    pdl_wait();
     const int64_t r0 = (int64_t)blockIdx.x * 32;
     const int d0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
@@ -949,14 +1038,14 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
     using B = BwdCfg<D, TF32>;
     const int smem = max(B::kSmem, 120 * 1024);
     auto kern = tc_bwd_kernel<D, TF32, MODE, kTwoExp>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    static unsigned long long attr_done = 0;
+    cudaError_t e = set_smem_once(kern, smem, attr_done);
     if (e != cudaSuccess) return e;
     const int64_t total_tiles = (int64_t)plan.row_tiles * col_tiles;
     if (plan.sk_ctas < 1 || plan.sk_ctas > total_tiles) return cudaErrorInvalidValue;
-    kern<<<plan.sk_ctas, B::kThreads, smem, stream>>>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin,
-                                                     b_count, k_scale, col_tiles, total_tiles, acc, g_trace,
-                                                     lse_ready);
-    return cudaGetLastError();
+    return launch_kernel(kern, dim3((unsigned)plan.sk_ctas), dim3(B::kThreads), smem, stream, tmap, tmap_t,
+                         u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, col_tiles, total_tiles,
+                         acc, g_trace, lse_ready);
 }
 
 template <int D, bool TF32>
@@ -1025,7 +1114,7 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
-                          float* part_m, float* part_s, unsigned* counter, const PeerWait& u_ready,
+                          float* part_m, float* part_s, float* pos_t, const PeerWait& u_ready,
                           cudaStream_t stream) {
     CUtensorMap tmap;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
@@ -1035,9 +1124,9 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     const int col_tiles = (int)((M + kTile - 1) / kTile);
 #define NTX_FWD(DD, TF)                                                                                    \
     (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m,  \
-                                         part_s, counter, u_ready, stream)                                 \
+                                         part_s, pos_t, u_ready, stream)                                   \
             : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                          part_s, counter, u_ready, stream))
+                                          part_s, pos_t, u_ready, stream))
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_FWD(64, true);
@@ -1067,10 +1156,10 @@ cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all,
         if (!ut_scratch) return cudaErrorInvalidValue;
         const int64_t Mpad = tc_ut_cols(M);
         dim3 tgrid((unsigned)((Mpad + 31) / 32), (unsigned)(D / 32));
-        transpose_f32_kernel<<<tgrid, 256, 0, stream>>>((const float*)u_all, M, (int)D, Mpad, ut_scratch);
-        e = cudaGetLastError();
+        e = launch_kernel(transpose_f32_kernel, tgrid, dim3(256), 0, stream, (const float*)u_all, M, (int)D,
+                          Mpad, ut_scratch);
         if (e != cudaSuccess) return e;
-        e = make_tmap_2d(ut_scratch, true, /*rows=*/D, /*cols=*/Mpad, /*box_rows=*/D, &tmap_t);
+        e = cached_tmap_2d(ut_scratch, true, /*rows=*/D, /*cols=*/Mpad, /*box_rows=*/D, &tmap_t);
         if (e != cudaSuccess) return e;
     }
     const float k_scale = kLog2e / tau;

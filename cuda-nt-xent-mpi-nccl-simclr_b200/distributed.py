@@ -91,8 +91,10 @@ class _SymmetricBuffers:
             sig_u.epoch, sig_u.rank = local + o_sync + 128, rank
             sig_lse.flags = capi.PeerList.of([b + o_sync + 64 for b in bases])
             sig_lse.epoch, sig_lse.rank = local + o_sync + 136, rank
-            wait_u = capi.PeerWait(local + o_sync, local + o_sync + 128, world, rows)
-            wait_lse = capi.PeerWait(local + o_sync + 64, local + o_sync + 136, world, rows)
+            # (word 36 of the sync block: set by a kernel whose wait for a peer timed out)
+            wait_u = capi.PeerWait(local + o_sync, local + o_sync + 128, world, rows, local + o_sync + 144)
+            wait_lse = capi.PeerWait(local + o_sync + 64, local + o_sync + 136, world, rows,
+                                     local + o_sync + 144)
             self.sets.append(dict(
                 u_all=self.buf[o:o + M * D * item].view(op_dtype).view(M, D),
                 lse_all=self.buf[o_lse:o_lse + M * 4].view(torch.float32),
@@ -102,6 +104,17 @@ class _SymmetricBuffers:
                 loss_peers=capi.PeerList.of([b + o_loss for b in bases]),
                 sig_u=sig_u, sig_lse=sig_lse, wait_u=wait_u, wait_lse=wait_lse))
         self.step = 0
+        self._sync_words = [self.buf[k * set_bytes + u_bytes + lse_bytes + loss_bytes:(k + 1) * set_bytes]
+                            .view(torch.int32) for k in range(2)]
+
+    def timed_out_on(self):
+        """Rank a kernel of this process gave up waiting for (ntxent_b200_set_peer_wait_timeout_ms),
+        or None.  Reads device memory: synchronises."""
+        for w in self._sync_words:
+            v = int(w[36].item())
+            if v:
+                return v - 1
+        return None
 
 
 def _reduce_scatter_sum(out: torch.Tensor, inp: torch.Tensor, group) -> None:

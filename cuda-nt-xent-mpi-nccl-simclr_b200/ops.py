@@ -94,22 +94,21 @@ class GraphedNTXent:
     and returns the graph's static (loss[1], dz[M, D]); consume them before the next call."""
 
     def __init__(self, M: int, D: int, temperature: float, dtype: torch.dtype = torch.bfloat16,
-                 device="cuda", use_mixed_precision: bool = False):
+                 device="cuda", use_mixed_precision: bool = False, flags: int = 0):
         self.T, self.mp = float(temperature), bool(use_mixed_precision)
         self.z = torch.zeros(M, D, dtype=dtype, device=device)
-        flags = capi.FLAG_MIXED_PRECISION if self.mp else 0
-        self.ws = capi.workspace(M, D, self.z, flags)
+        self.ws = capi.workspace(M, D, self.z, flags | (capi.FLAG_MIXED_PRECISION if self.mp else 0))
         self.out = (torch.empty(1, dtype=torch.float32, device=device),
                     torch.empty(M, dtype=torch.float32, device=device), torch.empty_like(self.z))
         side = torch.cuda.Stream(device=device)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(2):
-                capi.forward_backward(self.z, self.T, None, self.mp, 0, self.ws, self.out)
+                capi.forward_backward(self.z, self.T, None, self.mp, flags, self.ws, self.out)
         torch.cuda.current_stream().wait_stream(side)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            capi.forward_backward(self.z, self.T, None, self.mp, 0, self.ws, self.out)
+            capi.forward_backward(self.z, self.T, None, self.mp, flags, self.ws, self.out)
 
     def __call__(self, z: torch.Tensor):
         self.z.copy_(z, non_blocking=True)

@@ -167,8 +167,17 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
  * kernel waits -- tile by tile, only for the ranks whose rows that tile reads --
  * until those slots have reached the consumer's own call number.  All ranks
  * must make the same sequence of calls.  The flag arrays and `epoch` start at
- * zero and belong to the library afterwards; a wait that is never satisfied (a
- * lost peer) traps after a few seconds instead of hanging the GPU. */
+ * zero and belong to the library afterwards.
+ *
+ * A slow peer is not an error: a rank that stalls on its host (a checkpoint
+ * write, a data-loader hiccup, a debugger) simply keeps the others waiting, as
+ * it would inside a NCCL collective.  Only after the timeout set with
+ * ntxent_b200_set_peer_wait_timeout_ms (default 600 000 ms, 0 = wait for ever)
+ * does a waiting kernel give up: it stores 1 + the rank it was waiting for in
+ * the wait's `status` word (device memory, zero-initialised by the caller) and
+ * runs to completion on whatever is in the buffers -- the context stays usable,
+ * the step's results are void, and the host finds out by reading the word.
+ * With status == NULL the kernel traps at that point instead. */
 #define NTXENT_MAX_PEERS 16
 typedef struct {
     void* ptr[NTXENT_MAX_PEERS];
@@ -184,7 +193,12 @@ typedef struct {
     const uint32_t* epoch;  /* the counter of the matching signal on this rank */
     int ranks;
     int64_t rows_per_rank;  /* rank r produced rows [r*rows_per_rank, (r+1)*rows_per_rank) */
+    uint32_t* status;       /* device word, 0 = fine; set by a wait that timed out; may be NULL */
 } ntxent_peer_wait;
+
+/* Process-wide bound on how long a kernel waits for a peer's flag (see above).
+ * Takes effect for calls made after it returns. */
+int ntxent_b200_set_peer_wait_timeout_ms(uint64_t milliseconds);
 
 /* ntxent_b200_normalize whose rows land at row `row_begin` of every rank's
  * gathered u_all [M, D] (replaces normalise + all-gather of U). */
@@ -249,9 +263,12 @@ int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const floa
  *     launched.  Every GPU that loads the library keeps the 8 MiB until exit.
  *   - The first call on each device looks up the array's device address (one
  *     cudaGetSymbolAddress with that device current); make that first call
- *     before starting any stream capture.  No call allocates or frees.
+ *     before starting any stream capture.  No call allocates or frees.  The
+ *     address is remembered together with the driver context it belongs to,
+ *     and looked up again when a call finds another context current (after
+ *     cudaDeviceReset(), or in a host that switches contexts on one device).
  *   - All calls on a device share the one array, and it keeps whatever the last
- *     call wrote.  The pass re-initialises the little it needs zeroed, so
+ *     call wrote.  The pass writes every part of it before reading it, so
  *     back-to-back calls on one stream are fine; calls that can run on the GPU
  *     at the same time (different streams, different host threads) race on it
  *     and must be serialised by the caller. */

@@ -43,6 +43,8 @@ def lib() -> ctypes.CDLL:
         fp = ctypes.POINTER(ctypes.c_float)
         i64 = ctypes.c_int64
         L.ntxent_oracle_num_threads.restype = ctypes.c_int
+        L.ntxent_oracle_set_num_threads.argtypes = [ctypes.c_int]
+        L.ntxent_oracle_set_num_threads.restype = None
         L.ntxent_oracle_forward_f64.argtypes = [dp, i64, i64, ctypes.c_double, dp, dp, dp]
         L.ntxent_oracle_forward_f64.restype = ctypes.c_int
         L.ntxent_oracle_backward_f64.argtypes = [dp, dp, ctypes.c_double, i64, i64,
@@ -69,6 +71,13 @@ def _fptr(a):
 
 def num_threads() -> int:
     return int(lib().ntxent_oracle_num_threads())
+
+
+def use_all_cores() -> int:
+    """Run the OpenMP loops on every host core, whatever OMP_NUM_THREADS the launcher exported
+    (torchrun sets it to 1 for its ranks).  Returns the thread count now in use."""
+    lib().ntxent_oracle_set_num_threads(os.cpu_count() or 1)
+    return num_threads()
 
 
 def forward(z, tau: float):

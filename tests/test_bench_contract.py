@@ -28,9 +28,18 @@ def test_reference_arm_json_line():
     assert d["value"] > 0 and d["ms_per_step"] > 0
     assert d["config"]["workload"].startswith("ntxent_fwd_bwd_M512_D128")
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "rows [0," in cb["sample"]
+    # C1 is small: the CPU arm times whole steps, and says so
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "whole step" in cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["gpu_launches"] == 0 and d["vs_baseline"] is None
+
+
+def test_reference_arm_uses_every_core_under_a_launcher():
+    """torchrun exports OMP_NUM_THREADS=1 to its ranks; the CPU arm must not inherit that."""
+    p = _run({"OMP_NUM_THREADS": "1", "RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"})
+    assert p.returncode == 0, p.stderr[-2000:]
+    d = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("{")][0])
+    assert d["cpu_baseline"]["cores"] == (os.cpu_count() or 1)
 
 
 def test_reference_arm_other_ranks_do_no_work():

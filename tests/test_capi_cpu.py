@@ -78,6 +78,19 @@ def test_argument_errors_return_codes_without_touching_the_device():
     assert L.ntxent_b200_forward_rows(one, 64, 128, 48, 32, 0.5, 0, 0, one, 1 << 30, one, one, null) == -1
 
 
+def test_compute_calls_report_an_unsupported_device():
+    """Valid arguments on a machine without an sm_100 GPU: NTXENT_ERR_UNSUPPORTED_DEVICE, not a raw
+    "no kernel image" from the first launch (and nothing is launched)."""
+    if torch.cuda.is_available() and torch.cuda.get_device_capability()[0] == 10:
+        pytest.skip("sm_100 device present")
+    L = capi.lib()
+    one, null = ctypes.c_void_p(256), ctypes.c_void_p(None)
+    assert L.ntxent_b200_forward(one, 64, 128, 0.5, 0, 0, one, 1 << 30, one, one, null) == -2
+    assert L.ntxent_b200_forward_static(one, 64, 128, 0.5, 0, 0, one, one, null) == -2
+    assert L.ntxent_b200_normalize(one, 64, 128, 0, 0, one, one, null) == -2
+    assert b"sm_100" in L.ntxent_b200_strerror(-2)
+
+
 def test_no_cpu_fallback():
     z = torch.randn(8, 16)
     with pytest.raises(capi.NTXentError, match="CUDA"):

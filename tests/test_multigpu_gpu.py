@@ -103,7 +103,7 @@ def test_row_partition_nccl(tmp_path, oracle, mode, dtype_name):
     z = torch.from_numpy(seeded_z(M, D, seed=5)).to(dtype)
     ref_loss, _, ref_dz = oracle.forward_backward(z.double().numpy(), tau)
     rows = M // world
-    tol_l, tol_g = (2e-3, 3e-2) if dtype_name == "bfloat16" else (1e-5, 1e-4)
+    tol_l, tol_g = (2e-3, 1e-2) if dtype_name == "bfloat16" else (1e-5, 1e-4)
     scale = np.abs(ref_dz).max()
     for r in range(world):
         got = np.load(tmp_path / f"rank{r}.npz")

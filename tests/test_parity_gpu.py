@@ -20,7 +20,14 @@ from ntxent_b200 import capi
 pytestmark = pytest.mark.gpu
 
 LOSS_RTOL_F32, DZ_TOL_F32 = 1e-5, 1e-4
-LOSS_RTOL_BF16, DZ_TOL_BF16 = 2e-3, 3e-2
+LOSS_RTOL_BF16 = 2e-3
+# north_star gives bf16 no dz bound; measured against the fp64 oracle it is 3e-3 .. 8e-3 down to
+# tau = 0.05 and 1.5e-2 at tau = 0.02, so: 1e-2 where SimCLR lives, 3e-2 below (stated, not derived)
+DZ_TOL_BF16, DZ_TOL_BF16_COLD = 1e-2, 3e-2
+
+
+def dz_tol_bf16(tau):
+    return DZ_TOL_BF16 if tau >= 0.05 else DZ_TOL_BF16_COLD
 
 PATHS = {"auto": 0, "simt": capi.FLAG_FORCE_SIMT}
 
@@ -129,49 +136,100 @@ def test_tf32_tiles_meet_the_fp32_tolerance(oracle, M, D, tau):
     assert dz_err(dz_c, rdz_c) <= DZ_TOL_F32
 
 
-def test_config_c4_full_size_properties(oracle):
-    """configs[3] at full size (2N=32768, D=128, bf16): properties that need no O(M^2) oracle,
-    plus an oracle check of a row sample (the fp32 row-block form, 256 rows)."""
+def _dz_from_rowblock(zq, tau, lse_rows, du_row, du_col, rows):
+    """dz rows from the oracle's fp32 row-block outputs: dU = (row term + column term)/(tau M),
+    then the normalisation Jacobian in fp64."""
+    M = zq.shape[0]
+    nrm = np.maximum(np.linalg.norm(zq[rows], axis=1, keepdims=True), 1e-12)
+    u = zq[rows] / nrm
+    du = (du_row.astype(np.float64) + du_col[rows].astype(np.float64)) / (tau * M)
+    return (du - (du * u).sum(1, keepdims=True) * u) / nrm
+
+
+def test_config_c4_full_size(oracle):
+    """configs[3] at full size (2N=32768, D=128, bf16), the headline shape.
+
+    (a) loss, every l_i and ALL of dz against the CPU oracle (its fp32/OpenMP row-block form run
+        over all M rows: the whole 8 M^2 D problem, ~8 s on the box's host cores);
+    (b) all of dz against the rounding-faithful fp32 restatement (tests/emulation.py) at 2e-4 --
+        tight enough that one dropped 128 x 128 tile of the 443-tiles-per-CTA schedule fails it
+        (shown once with a build that drops a tile: profiles/r2_drop_tile_proof.log);
+    (c) the properties that need no reference at all."""
+    from emulation import emulate_bf16_step
     M, D, tau = 32768, 128, 0.1
     z = seeded_z(M, D)
     z_t = dev(z, torch.bfloat16)
     loss, lse, dz, pp = run_gpu(z_t, tau)
-    assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0  # i.i.d. rows: loss ~ ln(M) + O(1/tau^2 D)
     zq = z_t.double().cpu().numpy()
-    # 1. the gradient is orthogonal to every row (normalisation Jacobian)
+    # (a) CPU oracle, everything
+    rlse, rloss_sum, du_row, du_col = oracle.rowblock_f32(zq.astype(np.float32), tau, 0, M)
+    assert loss == pytest.approx(rloss_sum / M, rel=LOSS_RTOL_BF16)
+    np.testing.assert_allclose(lse, rlse, rtol=0, atol=5e-3)
+    rdz = _dz_from_rowblock(zq, tau, rlse, du_row, du_col, slice(0, M))
+    err_oracle = dz_err(dz, rdz)
+    assert err_oracle <= DZ_TOL_BF16, err_oracle
+    # (b) rounding-faithful restatement, everything
+    el, else_, edz = emulate_bf16_step(z_t, tau)
+    edz = edz.double().cpu().numpy()
+    assert loss == pytest.approx(el, rel=2e-6)
+    np.testing.assert_allclose(lse, else_.cpu().numpy(), rtol=0, atol=2e-5)
+    err_emu = dz_err(dz, edz)
+    # per row tile as well: a fault confined to one tile must not hide behind the global maximum
+    tile_err = np.abs(dz - edz).reshape(M // 128, -1).max(1) / np.abs(edz).max()
+    print(f"C4 dz: vs CPU oracle {err_oracle:.2e}, vs restatement {err_emu:.2e} (worst row tile {tile_err.argmax()})")
+    assert err_emu <= 2e-4, (err_emu, int(tile_err.argmax()))
+    # (c) properties
+    assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0  # i.i.d. rows: loss ~ ln(M) + O(1/tau^2 D)
     assert np.abs((zq * dz).sum(1)).max() <= 1e-2 * np.abs(dz).max() * np.abs(zq).max()
-    # 2. scale invariance: loss(2z) = loss(z), dz(2z) = dz(z)/2 (power of two: exact in bf16)
-    loss2, _, dz2, _ = run_gpu(z_t * 2, tau)
+    loss2, _, dz2, _ = run_gpu(z_t * 2, tau)  # scale invariance (power of two: exact in bf16)
     assert loss2 == pytest.approx(loss, rel=1e-6)
     assert dz_err(dz2 * 2, dz) <= 1e-2
-    # 3. swapping the two views leaves the loss unchanged and permutes the gradient
-    zs = torch.cat([z_t[M // 2:], z_t[:M // 2]])
+    zs = torch.cat([z_t[M // 2:], z_t[:M // 2]])  # swapping the views permutes the gradient
     loss3, _, dz3, _ = run_gpu(zs, tau)
     assert loss3 == pytest.approx(loss, rel=1e-6)
     assert dz_err(np.concatenate([dz3[M // 2:], dz3[:M // 2]]), dz) <= 1e-2
-    # 4. a row sample against the oracle's fp32 row-block form
-    R = 256
-    rlse, _, _, _ = oracle.rowblock_f32(zq.astype(np.float32), tau, 0, R)
-    np.testing.assert_allclose(lse[:R], rlse, rtol=0, atol=5e-3)
-    # 5. probabilities of the positives are probabilities
     assert (pp > 0).all() and (pp < 1).all()
 
 
-def test_config_c5_full_size_properties(oracle):
+def test_config_c5_full_size(oracle):
     """configs[4] at full size on one GPU (2N=131072, D=256, bf16; the dense fp32 logits would be
-    68.7 GB and are never formed): finite, gradient orthogonal to the rows, row-sample oracle check."""
+    68.7 GB and are never formed by the library).
+
+    All of dz and every l_i against the rounding-faithful restatement (row blocks of 2048 keep its
+    logits at 1 GB); a 1024-row sample of l and dz against the CPU oracle's row-block form, with
+    the column term of those rows taken from the GPU's l after l itself was checked."""
+    from emulation import emulate_bf16_step
     M, D, tau = 131072, 256, 0.1
     z_t = dev(seeded_z(M, D, seed=9), torch.bfloat16)
     before = torch.cuda.max_memory_allocated()
     loss, lse, dz, pp = run_gpu(z_t, tau)
     assert torch.cuda.max_memory_allocated() - before < 2 * 2**30  # O(M*D) working set
     assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0 and np.isfinite(dz).all()
-    rows = slice(0, 4096)
-    zq = z_t[rows].double().cpu().numpy()
-    assert np.abs((zq * dz[rows]).sum(1)).max() <= 1e-2 * np.abs(dz).max() * np.abs(zq).max()
-    R = 64
-    rlse, _, _, _ = oracle.rowblock_f32(z_t.float().cpu().numpy(), tau, 0, R)
+    el, else_, edz = emulate_bf16_step(z_t, tau, block=2048)
+    edz = edz.double().cpu().numpy()
+    assert loss == pytest.approx(el, rel=2e-6)
+    np.testing.assert_allclose(lse, else_.cpu().numpy(), rtol=0, atol=2e-5)
+    err_emu = dz_err(dz, edz)
+    assert err_emu <= 2e-4, err_emu
+    # CPU oracle on a row sample: rows [0, R).  Their dU needs the column term sum_b P_ba u_b with
+    # P_ba = exp(S_ab - l_b) for ALL b: formed here in fp64 numpy from the oracle's own normalised
+    # rows and the GPU's l_b (checked above against the restatement and below, on the sample,
+    # against the oracle).
+    R = 1024
+    zq = z_t.double().cpu().numpy()
+    rlse, _, du_row, _ = oracle.rowblock_f32(zq.astype(np.float32), tau, 0, R)
     np.testing.assert_allclose(lse[:R], rlse, rtol=0, atol=5e-3)
+    u = zq / np.maximum(np.linalg.norm(zq, axis=1, keepdims=True), 1e-12)
+    S = (u[:R] @ u.T) / tau
+    Pcol = np.exp(S - lse[None, :])
+    Pcol[np.arange(R), np.arange(R)] = 0.0
+    Pcol[np.arange(R), (np.arange(R) + M // 2) % M] -= 1.0  # the -Y^T term of the column part
+    du = (du_row.astype(np.float64) + Pcol @ u) / (tau * M)
+    nrm = np.maximum(np.linalg.norm(zq[:R], axis=1, keepdims=True), 1e-12)
+    rdz = (du - (du * u[:R]).sum(1, keepdims=True) * u[:R]) / nrm
+    err_oracle = np.abs(dz[:R] - rdz).max() / np.abs(dz).max()
+    print(f"C5 dz: vs restatement {err_emu:.2e} (all rows), vs CPU oracle {err_oracle:.2e} ({R} rows)")
+    assert err_oracle <= DZ_TOL_BF16, err_oracle
     assert (pp > 0).all() and (pp < 1).all()
 
 
@@ -197,7 +255,7 @@ def test_small_and_ragged_shapes_bf16(oracle, M, D, tau):
     loss, lse, dz, _ = run_gpu(z_t, tau)
     rl, rlse, rdz = oracle.forward_backward(z_t.double().cpu().numpy(), tau)
     assert loss == pytest.approx(rl, rel=LOSS_RTOL_BF16, abs=1e-4)
-    assert dz_err(dz, rdz) <= DZ_TOL_BF16
+    assert dz_err(dz, rdz) <= dz_tol_bf16(tau)
 
 
 @pytest.mark.parametrize("path", list(PATHS))
@@ -346,7 +404,7 @@ def test_row_partition_emulation(oracle, R, op_dtype):
     assert loss.item() == pytest.approx(loss1.item(), rel=1e-6)
     g = torch.tensor([0.5], device="cuda")
     ref = oracle.forward_backward(z_t.double().cpu().numpy(), tau, grad_out=0.5)[2]
-    tol = DZ_TOL_F32 if op_dtype == torch.float32 else DZ_TOL_BF16
+    tol = DZ_TOL_F32 if op_dtype == torch.float32 else dz_tol_bf16(tau)
     # symmetric form: all-gather of l only
     dz_sym = torch.cat([
         capi.finalize_dz(capi.backward_rows(u_all, lse_all, r * rows, rows, tau, capi.BWD_SYMMETRIC)[0],
