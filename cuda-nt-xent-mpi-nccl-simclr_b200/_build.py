@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libntxent_b200.so")
 LIB_PATH_TRACE = LIB_PATH[:-3] + "_trace.so"
 BINDING_PATH = os.path.join(PKG_DIR, "ntxent_cuda.so")
 
-KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu"]
+KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu", "tc_fwd_sym.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v",

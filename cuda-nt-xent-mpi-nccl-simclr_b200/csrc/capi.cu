@@ -95,16 +95,26 @@ inline bool want_tc(int64_t M, int64_t D, bool op_bf16, unsigned flags, float ta
     return tc_supported(M, D, op_bf16);
 }
 
+// Internal flag (never accepted from callers): keep the whole-batch forward on the full-matrix
+// tile kernel -- for ntxent_b200_forward_static, whose built-in scratch has no room for the
+// upper-triangle kernel's column partials.
+constexpr unsigned kFlagNoSymForward = 1u << 16;
+constexpr unsigned kPublicFlags = NTXENT_FLAG_MIXED_PRECISION | NTXENT_FLAG_FORCE_SIMT | NTXENT_FLAG_ONLINE_MAX;
+
 struct Plans {
     SplitPlan fwd, bwd_rows, bwd_cols;
     bool tc;
     unsigned flags;
     size_t ut_bytes;
+    // whole-batch forward over the upper triangle (tc_fwd_sym.cu); `sym_room`: the workspace
+    // layout reserves its buffers (decided without tau), `sym`: this call uses it
+    bool sym_room, sym;
+    SymPlan symp;
 };
 
 // All split decisions in one place so that sizing and launching can never disagree.
 Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned flags, float tau) {
-    Plans p;
+    Plans p{};
     p.flags = flags;
     p.ut_bytes = 0;
     p.tc = want_tc(M, D, op_bf16, flags, tau);
@@ -114,6 +124,12 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
         p.bwd_rows = tc_plan_bwd(M, D, row_count, M, sms);
         p.bwd_cols = tc_plan_bwd(M, D, M, row_count, sms);
         p.ut_bytes = tc_bwd_scratch_bytes(M, D, op_bf16);
+        const bool env_off = [] { const char* v = getenv("NTXENT_NO_SYM_FORWARD"); return v && v[0] == '1'; }();
+        if (row_count == M && !(flags & kFlagNoSymForward) && !env_off) {
+            p.sym_room = tc_sym_supported(M, D, op_bf16, 1.0f, flags);
+            p.sym = tau >= 0.f && tc_sym_supported(M, D, op_bf16, tau, flags);
+            if (p.sym_room) p.symp = tc_sym_plan(M, D, sms);
+        }
     } else {
         p.fwd = plan_splits(row_count, M, 64, 64, sms * 4, kMaxSplit);
         p.bwd_rows = plan_splits(row_count, M, 64, 64, sms * 2, kMaxSplit);
@@ -130,6 +146,8 @@ struct RowsWs {
     float* acc_rows;
     float* acc_cols;
     float* ut;  // tf32 tile kernels: transposed copy of U
+    float* sym_part_s;  // upper-triangle forward: row-sum partials [slots][M] ...
+    float* sym_cpart;   // ... and column partials
     size_t bytes;
 };
 
@@ -149,6 +167,10 @@ RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Pla
     w.acc_rows = (float*)take(sizeof(float) * (size_t)p.bwd_rows.nsplit * row_count * D);
     if (with_cols) w.acc_cols = (float*)take(sizeof(float) * (size_t)p.bwd_cols.nsplit * M * D);
     if (p.ut_bytes) w.ut = (float*)take(p.ut_bytes);
+    if (p.sym_room) {  // (last, so that nothing in front of them moves)
+        w.sym_part_s = (float*)take(sizeof(float) * (size_t)p.symp.slots * M);
+        w.sym_cpart = (float*)take(sizeof(float) * p.symp.cpart_floats);
+    }
     w.bytes = off;
     return w;
 }
@@ -189,6 +211,7 @@ int check_device() {
 }
 
 int check_shape(int64_t M, int64_t D, float tau, int dtype) {
+    // (flags: unknown bits are ignored, as before; the internal ones are masked off at the boundary)
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (M < 2 || (M & 1) || !(tau > 0.f) || !(tau < INFINITY)) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024) return NTXENT_ERR_UNSUPPORTED_SHAPE;
@@ -240,6 +263,22 @@ int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int6
     return run_forward_rows_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p, w,
                                  single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, no_wait(),
                                  no_signal(), st);
+}
+
+// Forward of the whole batch on one device: over the upper triangle where that applies
+// (tc_fwd_sym.cu), else the row-block path with the full range.
+int run_forward_device(const void* U, bool op_bf16, int64_t M, int64_t D, float tau, const Plans& p,
+                       const RowsWs& w, float* lse_out, float* loss_out, cudaStream_t st) {
+    if (!p.sym)
+        return run_forward_rows(U, op_bf16, M, D, 0, M, tau, p, w, lse_out, loss_out, 1.0f / (float)M, st);
+    g_timer.start(0, st);
+    NTX_TRY(tc_launch_fwd_sym(U, M, D, tau, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, st));
+    g_timer.stop(0, st);
+    NTX_TRY(tc_launch_fwd_sym_finalize(M, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, lse_out, w.block_partials,
+                                       st));
+    NTX_TRY(launch_loss_reduce(w.block_partials, p.symp.T, single_peer(loss_out), 0, 1.0f / (float)M, no_signal(),
+                               st));
+    return NTXENT_OK;
 }
 
 bool to_peer_signal(const ntxent_peer_signal* in, PeerSignal* out);
@@ -543,8 +582,7 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
-    return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
-                            1.0f / (float)M, stream);
+    return run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
 }
 
 int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out, int64_t M,
@@ -597,8 +635,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
-    rc = run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out, 1.0f / (float)M,
-                          stream);
+    rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
     if (rc != NTXENT_OK) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p,
                                dz_out, pos_prob_out, stream);
@@ -767,7 +804,7 @@ extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, f
     int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
     const bool opb = op_is_bf16(dtype, flags);
-    const Plans p = make_plans(M, D, M, opb, flags, tau);
+    const Plans p = make_plans(M, D, M, opb, flags | kFlagNoSymForward, tau);
     if (forward_scratch_bytes(M, D, opb, p) > (size_t)NTXENT_STATIC_SCRATCH_BYTES)
         return NTXENT_ERR_STATIC_SCRATCH_EXCEEDED;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;

@@ -109,6 +109,11 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
                                      const PeerList& loss_outs, int loss_index, float loss_scale,
                                      const PeerSignal& signal, cudaStream_t stream);
 
+// The loss: n per-CTA partials summed by one CTA in a fixed order, scaled, stored to element
+// loss_index of every buffer in `loss_outs` (and, multi-GPU push path, published with `signal`).
+cudaError_t launch_loss_reduce(const float* block_partials, int n, const PeerList& loss_outs, int loss_index,
+                               float loss_scale, const PeerSignal& signal, cudaStream_t stream);
+
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
     int nsplit;

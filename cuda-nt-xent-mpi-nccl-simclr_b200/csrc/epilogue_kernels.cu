@@ -184,8 +184,13 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
                               part_s, lse_outs, lse_offset, block_partials);
     }
     if (e != cudaSuccess) return e;
-    return launch_kernel(loss_reduce_kernel, dim3(1), dim3(1024), 0, stream, (const float*)block_partials,
-                         (int)blocks, loss_outs, loss_index, loss_scale, signal);
+    return launch_loss_reduce(block_partials, (int)blocks, loss_outs, loss_index, loss_scale, signal, stream);
+}
+
+cudaError_t launch_loss_reduce(const float* block_partials, int n, const PeerList& loss_outs, int loss_index,
+                               float loss_scale, const PeerSignal& signal, cudaStream_t stream) {
+    return launch_kernel(loss_reduce_kernel, dim3(1), dim3(1024), 0, stream, block_partials, n, loss_outs,
+                         loss_index, loss_scale, signal);
 }
 
 // -------------------------------------------------------------- bwd epilogue ---

@@ -1,0 +1,450 @@
+// tc_fwd_sym.cu -- the forward tile pass over the UPPER TRIANGLE of the logit matrix.
+//
+// With the fixed-max form (every row uses the same offset, so nothing is rescaled)
+// E_ab = 2^(k u_a.u_b) is symmetric: a tile (i, j), i < j, yields the row sums of tile i's rows
+// AND, summed down its columns, the row sums of tile j's rows.  The kernel therefore visits
+// T (T + 1) / 2 tiles instead of T^2: half the tensor-core work and half the exponentials of
+// tc_fwd_kernel (tc_kernels.cu), which stays for everything this one does not cover (running-max
+// logsumexp for cold temperatures, row blocks of a partitioned batch, small problems).
+//
+// Work items: row tile i owns the tiles (i, i .. T-1); they are cut into chunks of at most L
+// tiles, one CTA per chunk, long rows first.  Per chunk a CTA keeps the row sums of its 128 rows
+// in registers (as tc_fwd_kernel does) and emits, per tile, the column sums of each 32-row
+// quadrant:  cpart[(i, j)][quadrant][column]  -- a fixed slot per contribution, so the finalize
+// kernel adds them in a fixed order (deterministic, no atomics).
+//
+// The S tile is read out of TMEM with the 16x256b shape instead of 32x32b: a thread then holds
+// 4 rows x 8 columns of every 32 x 32 block rather than one row x 32 columns, so the column sums
+// need three shuffle levels (over the 8 lanes that share the columns) instead of five, and the
+// row sums stay per-thread until the end of the chunk.
+//
+// Replaces, like tc_fwd_kernel, the reference's cublasSgemm + row_max/softmax kernels
+// (src/ntxent_kernel.cu:8-103,162-199); the reference forms the full [2B,2B] matrix.
+#include <algorithm>
+
+#include "tc_kernels.cuh"
+#include "tc_tile.cuh"
+
+namespace ntxent_b200 {
+using namespace ptx;
+using namespace tc;
+
+namespace {
+
+constexpr int kSymThreads = 320;  // warps 0..7 softmax, warp 8 TMA, warp 9 MMA
+constexpr int kSymTmaWarp = 8, kSymMmaWarp = 9;
+constexpr int kSymSoftmaxThreads = 256;
+
+// 16 TMEM lanes x 32 columns -> 16 registers: thread t holds rows t/4 (regs 4n, 4n+1) and
+// t/4 + 8 (regs 4n+2, 4n+3) of the 16, columns 8n + 2 (t%4) + {0, 1}, n = 0..3.
+__device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+          "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+// One 32-row x 32-column block (this warp's lane quadrant, columns col..col+31) into v[0..31]:
+// v[16 h + 4 n + q]  =  row 16 h + 8 (q >> 1) + lane / 4,  column 8 n + 2 (lane % 4) + (q & 1).
+__device__ __forceinline__ void ld_block(uint32_t quad_addr, uint32_t col, uint32_t (&v)[32]) {
+    tmem_ld_16x256b_x4(quad_addr + col, &v[0]);
+    tmem_ld_16x256b_x4(quad_addr + (16u << 16) + col, &v[16]);
+}
+
+// Sum of c[idx] over the 8 lanes that share lane % 4, for idx = 4 b4 + 2 b3 + b2 (the lane's own
+// bits 4, 3, 2): a transposing butterfly, 7 shuffles for 8 values.
+__device__ __forceinline__ float colsum_butterfly(const float (&c)[8], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    float k4[4], k2[2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float send = b4 ? c[k] : c[4 + k], keep = b4 ? c[4 + k] : c[k];
+        k4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float send = b3 ? k4[k] : k4[2 + k], keep = b3 ? k4[2 + k] : k4[k];
+        k2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    const float send = b2 ? k2[0] : k2[1], keep = b2 ? k2[1] : k2[0];
+    return keep + __shfl_xor_sync(0xffffffffu, send, 4);
+}
+
+// Work items.  Rows i in [T - m L, T - (m-1) L) have between (m-1) L + 1 and m L tiles, i.e. m
+// chunks; items are numbered by descending m (ascending i), chunks of a row consecutively.
+struct SymItem {
+    int i, j0, n, slot;
+};
+__host__ __device__ inline int sym_item_count(int T, int L) {
+    int total = 0;
+    for (int m = (T + L - 1) / L; m >= 1; --m) {
+        const int lo = max(T - m * L, 0), hi = T - (m - 1) * L;
+        total += (hi - lo) * m;
+    }
+    return total;
+}
+__device__ __forceinline__ SymItem sym_item(int w, int T, int L) {
+    SymItem it{0, 0, 0, 0};
+    for (int m = (T + L - 1) / L; m >= 1; --m) {
+        const int lo = max(T - m * L, 0), hi = T - (m - 1) * L;
+        const int ctas = (hi - lo) * m;
+        if (w < ctas) {
+            it.i = lo + w / m;
+            it.slot = w % m;
+            it.j0 = it.i + it.slot * L;
+            it.n = min(L, T - it.j0);
+            return it;
+        }
+        w -= ctas;
+    }
+    return it;
+}
+
+template <int D, bool TF32>
+__global__ void __launch_bounds__(kSymThreads, Cfg<D, TF32>::kFwdCtasPerSm)
+tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_scale, int T, int L,
+                  float* __restrict__ part_s, float* __restrict__ cpart, float* __restrict__ pos_t_out) {
+    using C = Cfg<D, TF32>;
+    constexpr int NS = C::kFwdStages;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = align1024(smem_raw);
+    uint8_t* q_tile = smem;
+    uint8_t* k_tiles = smem + C::kTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (1 + NS) * C::kTileBytes);
+    uint64_t* q_full = bars;
+    uint64_t* k_full = bars + 1;
+    uint64_t* k_empty = k_full + NS;
+    uint64_t* s_full = k_empty + NS;
+    uint64_t* s_empty = s_full + 2;
+    uint64_t* q_ready = s_empty + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_trigger();
+    const SymItem item = sym_item((int)blockIdx.x, T, L);
+    const int64_t a0 = (int64_t)item.i * kTile;
+    const int n_tiles = item.n;
+
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmap);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_empty[b], 8); }
+        mbar_init(q_ready, 8);
+        fence_mbar_init();
+    }
+    if (warp == kSymMmaWarp) tmem_alloc<256>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // set-up done; from here on the kernel reads what the normalise kernel wrote
+
+    if (warp == kSymTmaWarp) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, C::kTileBytes);
+            for (int a = 0; a < C::kAtoms; ++a)
+                tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * C::kAtomCols, (int32_t)a0);
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it % NS;
+                mbar_wait(&k_empty[st], ((it / NS) & 1) ^ 1);
+                mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
+                for (int a = 0; a < C::kAtoms; ++a)
+                    tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
+                                a * C::kAtomCols, (item.j0 + it) * kTile);
+            }
+        }
+        __syncwarp();
+    } else if (warp == kSymMmaWarp) {
+        // the whole warp walks the loop (uniform control flow); one elected lane issues
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = idesc_op<TF32>(kTile, kTile, false);
+        const uint32_t q_addr = smem_u32(q_tile);
+        mbar_wait(q_ready, 0);
+        for (int it = 0; it < n_tiles; ++it) {
+            const int st = it % NS, buf = it & 1;
+            mbar_wait(&k_full[st], (it / NS) & 1);
+            mbar_wait(&s_empty[buf], ((it >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
+            if (leader) {
+#pragma unroll
+                for (int kk = 0; kk < C::kKSteps; ++kk)
+                    mma_ss_f16<TF32>(tmem_base + buf * kTile, desc_kmajor(q_addr, kk), desc_kmajor(k_addr, kk),
+                                     idesc, kk > 0);
+                tc_commit(&k_empty[st]);
+                tc_commit(&s_full[buf]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // eight softmax warps: warp w owns TMEM lanes 32 (w%4) .. +31 and the 64 columns
+        // [64 h, 64 h + 64) of every S tile, h = w/4, as two 32 x 32 blocks
+        const int quad = warp & 3;
+        const int half = warp >> 2;
+        const uint32_t quad_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + half * 64;
+        // this thread's four rows (tile-relative): rbase + {0, 8, 16, 24}; its columns within a
+        // 32-column block: 8 n + cbase + {0, 1}
+        const int rbase = quad * 32 + (lane >> 2);
+        const int cbase = 2 * (lane & 3);
+        float rs[4] = {0.f, 0.f, 0.f, 0.f};
+        // scale the row tile by k = log2(e)/tau where TMA put it (elementwise, so the swizzle is
+        // irrelevant), then publish it to the tensor core's (async-proxy) view of shared memory
+        {
+            mbar_wait(q_full, 0);
+            uint4* q4 = reinterpret_cast<uint4*>(q_tile);
+            for (int i = threadIdx.x; i < C::kTileBytes / 16; i += kSymSoftmaxThreads) {
+                uint4 w = q4[i];
+                uint32_t* p = reinterpret_cast<uint32_t*>(&w);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (TF32) {
+                        p[j] = to_tf32(__uint_as_float(p[j]) * k_scale);
+                    } else {
+                        const float lo = __uint_as_float(p[j] << 16) * k_scale;
+                        const float hi = __uint_as_float(p[j] & 0xffff0000u) * k_scale;
+                        p[j] = pack_bf16(lo, hi);
+                    }
+                }
+                q4[i] = w;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        // 64-column half tiles that take the masked path, as 32-bit numbers: the diagonal tile, the
+        // ragged end of the range, and the half tiles that hold the positives of this row tile
+        // (columns (a0 + N + r) mod M: one run of 128 columns, or two when it wraps around M)
+        const int hj_ragged = (int)(M / 64);
+        const int p0 = (int)((a0 + M / 2) % M);
+        const int hj_pos_lo = p0 / 64, hj_pos_hi = (min(p0 + kTile, (int)M) - 1) / 64;
+        const int hj_wrap_hi = p0 + kTile > (int)M ? (p0 + kTile - (int)M - 1) / 64 : -1;
+        // column partials of tile (i, j): cpart[(j (j-1)/2 + i) * 512 + quad * 128 + column]
+        const int col_of_lane = 8 * (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)) + cbase + ((lane >> 2) & 1);
+
+        // (all row / column numbers fit 32 bits: M <= 2^24)
+        const int M32 = (int)M, N32 = (int)(M / 2), row0 = (int)a0 + rbase;
+        int pos4[4];  // the positives of this thread's four rows
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const int p = row0 + 8 * g + N32;
+            pos4[g] = p >= M32 ? p - M32 : p;
+        }
+
+        auto block = [&](const uint32_t (&v)[32], int jt, int blk, bool special) {
+            const bool diag = jt == item.i;
+            float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (!special) {
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const float e = ex2_mix<kFwdPoly>(__uint_as_float(v[r]), r);
+                    rs[2 * (r >> 4) + ((r >> 1) & 1)] += e;
+                    cs[2 * ((r >> 2) & 3) + (r & 1)] += e;
+                }
+            } else {
+                const int c0 = jt * kTile + half * 64 + blk * 32 + cbase;
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const int g = 2 * (r >> 4) + ((r >> 1) & 1);
+                    const int row = row0 + 8 * g;
+                    const int col = c0 + 8 * ((r >> 2) & 3) + (r & 1);
+                    const float t = __uint_as_float(v[r]);
+                    const bool ok = col < M32 && col != row && row < M32;
+                    const float e = ok ? ex2(t) : 0.f;
+                    rs[g] += e;
+                    cs[2 * ((r >> 2) & 3) + (r & 1)] += e;
+                    // the positive logit, from the same MMA as the denominator; off the diagonal tile
+                    // the element (row, col) is also the positive logit of row `col`
+                    if (ok && col == pos4[g]) {
+                        pos_t_out[row] = t;
+                        if (!diag) pos_t_out[col] = t;
+                    }
+                }
+            }
+            if (!diag) {
+                const float s = colsum_butterfly(cs, lane);
+                const int64_t pair = (int64_t)jt * (jt - 1) / 2 + item.i;
+                cpart[pair * 512 + quad * 128 + half * 64 + blk * 32 + col_of_lane] = s;
+            }
+        };
+
+        // two 32-column blocks per tile, double-buffered in registers: the load of the next block
+        // (or of the next tile's first block) is in flight while the current one is exponentiated
+        uint32_t va[32], vb[32];
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        ld_block(quad_addr, 0, va);
+        for (int it = 0; it < n_tiles; ++it) {
+            const int buf = it & 1;
+            const int jt = item.j0 + it;
+            const int hj = 2 * jt + half;
+            const bool special = jt == item.i || hj >= hj_ragged || (hj >= hj_pos_lo && hj <= hj_pos_hi) ||
+                                 hj <= hj_wrap_hi;
+            tmem_ld_wait();
+            ld_block(quad_addr, buf * kTile + 32, vb);
+            block(va, jt, 0, special);
+            tmem_ld_wait();
+            // this warp's S columns have left TMEM: hand the buffer back, then prefetch
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[buf]);
+            if (it + 1 < n_tiles) {
+                mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
+                tc_fence_after();
+                ld_block(quad_addr, (buf ^ 1) * kTile, va);
+            }
+            block(vb, jt, 1, special);
+        }
+        // row sums: over the four lanes that share the rows, then the two column halves through
+        // shared memory (the row tile is no longer needed: every MMA that read it has completed)
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            rs[g] += __shfl_xor_sync(0xffffffffu, rs[g], 1);
+            rs[g] += __shfl_xor_sync(0xffffffffu, rs[g], 2);
+        }
+        float* halves = reinterpret_cast<float*>(q_tile);
+        named_bar_sync(1, kSymSoftmaxThreads);
+        if (half == 1 && (lane & 3) == 0) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) halves[rbase + 8 * g] = rs[g];
+        }
+        named_bar_sync(1, kSymSoftmaxThreads);
+        if (half == 0 && (lane & 3) == 0) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int64_t row = a0 + rbase + 8 * g;
+                if (row < M) part_s[(int64_t)item.slot * M + row] = rs[g] + halves[rbase + 8 * g];
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kSymMmaWarp) tmem_dealloc<256>(tmem_base);
+}
+
+// ---------------------------------------------------------------- finalize ---
+// One thread per row: its row-sum partials (one per chunk of its row tile) plus the column
+// partials of every tile above it in its column block, added in a fixed order.
+constexpr int kSymFinThreads = 128;
+__global__ void __launch_bounds__(kSymFinThreads)
+fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_s,
+                        const float* __restrict__ cpart, const float* __restrict__ pos_t,
+                        float* __restrict__ lse_out, float* __restrict__ block_partials) {
+    __shared__ float warp_contrib[kSymFinThreads / 32];
+    pdl_trigger();
+    pdl_wait();
+    const int j = blockIdx.x;  // row tile == column tile of these rows
+    const int c = threadIdx.x;
+    const int64_t r = (int64_t)j * kTile + c;
+    float contrib = 0.f;
+    if (r < M) {
+        const int nslots = (T - j + L - 1) / L;
+        float s = 0.f;
+        for (int sl = 0; sl < nslots; ++sl) s += part_s[(int64_t)sl * M + r];
+        const float* cp = cpart + (int64_t)j * (j - 1) / 2 * 512 + c;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};  // four chains: the loads of four tiles (16 values) in flight
+        int i = 0;
+        for (; i + 4 <= j; i += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float* q = cp + (int64_t)(i + u) * 512;
+                s4[u] += (q[0] + q[128]) + (q[256] + q[384]);
+            }
+        }
+        for (; i < j; ++i) {
+            const float* q = cp + (int64_t)i * 512;
+            s4[0] += (q[0] + q[128]) + (q[256] + q[384]);
+        }
+        s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        const float l2 = log2f(s);
+        lse_out[r] = l2 * kLn2;
+        contrib = (l2 - pos_t[r]) * kLn2;
+    }
+    contrib = warp_sum(contrib);
+    if ((threadIdx.x & 31) == 0) warp_contrib[threadIdx.x >> 5] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float bsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < kSymFinThreads / 32; ++w) bsum += warp_contrib[w];
+        block_partials[blockIdx.x] = bsum;
+    }
+}
+
+// chunk length: long enough to amortise a CTA's prologue (~1.5 tiles), short enough that the
+// last CTAs to finish do not leave the other SMs idle for long
+int pick_chunk(int T, int slots) {
+    int best = 1;
+    double best_cost = 1e300;
+    for (int L : {4, 6, 8, 12, 16, 20, 24, 32, 48, 64}) {
+        if (L > T && L != 4) continue;
+        const int items = sym_item_count(T, L);
+        const double work = (double)T * (T + 1) / 2 + 1.5 * items;
+        const double cost = work / std::min(slots, items) + 0.5 * (std::min(L, T) + 1.5);
+        if (cost < best_cost) { best_cost = cost; best = L; }
+    }
+    return best;
+}
+
+template <int D, bool TF32>
+cudaError_t launch_sym_t(const CUtensorMap& tmap, int64_t M, float k_scale, const SymPlan& sp, float* part_s,
+                         float* cpart, float* pos_t, cudaStream_t stream) {
+    using C = Cfg<D, TF32>;
+    const int smem = C::kFwdCtasPerSm == 2 ? std::max(C::kFwdSmem, 80 * 1024) : std::max(C::kFwdSmem, 120 * 1024);
+    auto kern = tc_fwd_sym_kernel<D, TF32>;
+    static unsigned long long attr_done = 0;
+    cudaError_t e = set_smem_once(kern, smem, attr_done);
+    if (e != cudaSuccess) return e;
+    return launch_kernel(kern, dim3((unsigned)sp.items), dim3(kSymThreads), smem, stream, tmap, M, k_scale, sp.T,
+                         sp.L, part_s, cpart, pos_t);
+}
+
+}  // namespace
+
+bool tc_sym_supported(int64_t M, int64_t D, bool op_bf16, float tau, unsigned flags) {
+    if (!op_bf16 || (flags & 4u) || tau < 0.f) return false;  // (tau < 0: not known yet)
+    if (kLog2e / tau > kFixedMaxLimit) return false;           // needs the fixed-max form
+    if (!(D == 64 || D == 128 || D == 192 || D == 256)) return false;
+    return M >= kSymMinRows;
+}
+
+SymPlan tc_sym_plan(int64_t M, int64_t D, int num_sms) {
+    SymPlan p{};
+    p.T = (int)((M + kTile - 1) / kTile);
+    const int tile_bytes = (int)(D * 2 * kTile);
+    const int stages = tile_bytes <= 16 * 1024 ? 3 : 2;
+    const int per_sm = ((1 + stages) * tile_bytes + 2048 <= 112 * 1024) ? 2 : 1;
+    p.L = pick_chunk(p.T, num_sms * per_sm);
+    p.items = sym_item_count(p.T, p.L);
+    p.slots = (p.T + p.L - 1) / p.L;
+    p.cpart_floats = (size_t)p.T * (p.T - 1) / 2 * 512;
+    return p;
+}
+
+cudaError_t tc_launch_fwd_sym(const void* u_all, int64_t M, int64_t D, float tau, const SymPlan& sp,
+                              float* part_s, float* cpart, float* pos_t, cudaStream_t stream) {
+    CUtensorMap tmap;
+    cudaError_t e = cached_tmap_2d(u_all, false, M, D, kTile, &tmap);
+    if (e != cudaSuccess) return e;
+    const float k_scale = kLog2e / tau;
+    switch (D) {
+        case 64: e = launch_sym_t<64, false>(tmap, M, k_scale, sp, part_s, cpart, pos_t, stream); break;
+        case 128: e = launch_sym_t<128, false>(tmap, M, k_scale, sp, part_s, cpart, pos_t, stream); break;
+        case 192: e = launch_sym_t<192, false>(tmap, M, k_scale, sp, part_s, cpart, pos_t, stream); break;
+        case 256: e = launch_sym_t<256, false>(tmap, M, k_scale, sp, part_s, cpart, pos_t, stream); break;
+        default: return cudaErrorNotSupported;
+    }
+    return e;
+}
+
+cudaError_t tc_launch_fwd_sym_finalize(int64_t M, const SymPlan& sp, const float* part_s, const float* cpart,
+                                       const float* pos_t, float* lse_out, float* block_partials,
+                                       cudaStream_t stream) {
+    return launch_kernel(fwd_sym_finalize_kernel, dim3((unsigned)sp.T), dim3(kSymFinThreads), 0, stream, M, sp.T,
+                         sp.L, part_s, cpart, pos_t, lse_out, block_partials);
+}
+
+}  // namespace ntxent_b200

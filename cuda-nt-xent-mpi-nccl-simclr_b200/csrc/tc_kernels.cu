@@ -20,65 +20,20 @@
 #include <mutex>
 
 #include "tc_ptx.cuh"
+#include "tc_tile.cuh"
 
 namespace ntxent_b200 {
 using namespace ptx;
+using namespace tc;
 
 namespace {
 
-constexpr int kTile = 128;                  // rows per row tile = columns per column tile
-constexpr int kAtomBytes = kTile * 128;     // one 128B-swizzle atom: [128 rows x 64 bf16]
 constexpr int kThreads = 320;               // warps 0..7 softmax, warp 8 TMA, warp 9 MMA
 // The issuing warps carry the highest warp ids: the scheduler favours higher ids among ready
 // warps, and a starved MMA issuer (a dozen scalar instructions per tcgen05.mma) stalls everything.
 constexpr int kFwdTmaWarp = 8, kFwdMmaWarp = 9;
 constexpr int kSoftmaxThreads = 256;        // two warps per TMEM lane quadrant, 64 columns each
-constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)/tau <= this
 constexpr int64_t kTf32MinRows = 1024;      // fp32 operands take the tf32 tiles from this many rows on
-// of every 8 exponentials in the fixed-max paths, this many are evaluated by ex2_poly
-#ifndef NTX_FWD_POLY
-#define NTX_FWD_POLY 3
-#endif
-#ifndef NTX_BWD_POLY
-#define NTX_BWD_POLY 0
-#endif
-constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
-
-// TF32 = false: bf16 operands, .kind::f16 (K = 16 per MMA).  TF32 = true: fp32 operands read as
-// tf32, .kind::tf32 (K = 8 per MMA).  Either way one MMA consumes 32 bytes of every operand row
-// and a 128-byte swizzle row holds four such slices, so the descriptor arithmetic is shared.
-template <int D, bool TF32 = false>
-struct Cfg {
-    static_assert(D % 64 == 0 && D >= 64 && D <= (TF32 ? 128 : 256),
-                  "tcgen05 tiles cover D in {64,128,192,256} (bf16) or {64,128} (tf32)");
-    static constexpr int kElemBytes = TF32 ? 4 : 2;
-    static constexpr int kAtoms = D * kElemBytes / 128;
-    static constexpr int kAtomCols = 128 / kElemBytes;  // elements per 128-byte swizzle row
-    static constexpr int kTileBytes = kAtoms * kAtomBytes;
-    static constexpr int kKSteps = D * kElemBytes / 32;  // MMAs per S tile
-    static constexpr int kKPerMma = 32 / kElemBytes;
-    // forward: two CTAs per SM when the tiles allow it
-    static constexpr int kFwdStages = (kTileBytes <= 16 * 1024) ? 3 : 2;
-    static constexpr int kFwdSmem = (1 + kFwdStages) * kTileBytes + 2048;
-    static constexpr int kFwdCtasPerSm = (kFwdSmem <= 112 * 1024) ? 2 : 1;
-};
-
-// K-major operand (rows = M or N index, 128 B of K per row, 8-row groups 1024 B apart).
-__device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {
-    // kstep counts 32-byte K slices: 4 per swizzle atom
-    const uint32_t addr = tile_addr + (kstep >> 2) * kAtomBytes + (kstep & 3) * 32;
-    return smem_desc_sw128(addr, 16, 1024);
-}
-// MN-major view of the same tile (K index = tile row): 16 (bf16) or 8 (tf32) K rows per MMA; the
-// next 128 bytes of N live one atom (16 KB) further: LBO = atom stride, SBO = 8-row group stride.
-template <bool TF32 = false>
-__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep) {
-    return smem_desc_sw128(tile_addr + kstep * (TF32 ? 1024 : 2048), kAtomBytes, 1024);
-}
-
-__device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
-    return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
-}
 
 // One 32-column chunk of an S row folded into the running base-2 (max, sum).  The values are
 // already t = log2(e)/tau * u_a.u_b: the A operand was scaled by k = log2(e)/tau when it was
@@ -276,20 +231,21 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         // this row tile's own rows (the diagonal) and everything from the ragged end of the range
         const int hj_diag_lo = (int)(a0 / 64), hj_diag_hi = (int)((a0 + 63) / 64) + 1;
         const int hj_ragged = (int)(M / 64);
-        // ... and those that hold the positives of this row tile, columns (a0 + N + i) mod M: one run
-        // of 128 columns, or two when it wraps around M
-        const int64_t p0 = (a0 + M / 2) % M;
-        const int hj_pos_lo = (int)(p0 / 64), hj_pos_hi = (int)((min(p0 + kTile, M) - 1) / 64);
-        const int hj_wrap_hi = p0 + kTile > M ? (int)((p0 + kTile - M - 1) / 64) : -1;
+        // ... and the one or two that hold the positives of THIS WARP's 32 rows (columns
+        // (row + N) mod M: a run of 32, which can straddle a half-tile boundary or wrap around M)
+        const int64_t wrow0 = a0 + quad * 32;
+        const int hj_pos_a = (int)(((wrow0 + M / 2) % M) / 64);
+        const int hj_pos_b = (int)(((min(wrow0 + 31, M - 1) + M / 2) % M) / 64);
         const int64_t pos_col = (row + M / 2) % M;
+        // whether this warp's column range holds the row's positive at all (decided once, here)
+        const int pos_hj = (int)(pos_col >> 6);
+        const bool pos_seen = (pos_hj & 1) == half && (pos_hj >> 1) >= jt0 && (pos_hj >> 1) < jt0 + n_tiles;
         float pos_t = 0.f;
-        bool pos_seen = false;
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
             const int hj = 2 * (jt0 + it) + half;
             const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged ||
-                                 (hj >= hj_pos_lo && hj <= hj_pos_hi) || hj <= hj_wrap_hi;
-            pos_seen |= (pos_col >> 6) == hj;
+                                 hj == hj_pos_a || hj == hj_pos_b;
             const int64_t j0 = (int64_t)hj * 64;  // (used on the masked path only)
             const uint32_t taddr = lane_addr + buf * kTile;
             tmem_ld_wait();
@@ -947,54 +903,8 @@ cudaError_t make_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-// Encoding a tensor map is ~1-2 us of host time per call and the same few (pointer, shape) pairs
-// come back every step: keep the last ones.  (A map only encodes address, shape and layout, so a
-// hit stays valid when the buffer was freed and handed out again at the same address.)
-struct TmapKey {
-    const void* base; int64_t rows, cols; int box_rows; bool tf32;
-    bool operator==(const TmapKey& o) const {
-        return base == o.base && rows == o.rows && cols == o.cols && box_rows == o.box_rows && tf32 == o.tf32;
-    }
-};
-cudaError_t cached_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols, int box_rows,
-                           CUtensorMap* out) {
-    constexpr int kSlots = 32;
-    static std::mutex mu;
-    static TmapKey keys[kSlots];
-    static CUtensorMap maps[kSlots];
-    static int used = 0, next = 0;
-    const TmapKey key{base, rows, cols, box_rows, tf32};
-    {
-        std::lock_guard<std::mutex> lock(mu);
-        for (int i = 0; i < used; ++i)
-            if (keys[i] == key) { *out = maps[i]; return cudaSuccess; }
-    }
-    cudaError_t e = make_tmap_2d(base, tf32, rows, cols, box_rows, out);
-    if (e != cudaSuccess) return e;
-    std::lock_guard<std::mutex> lock(mu);
-    const int slot = used < kSlots ? used++ : (next++ % kSlots);
-    keys[slot] = key;
-    maps[slot] = *out;
-    return cudaSuccess;
-}
-
 cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtensorMap* out) {
     return cached_tmap_2d(u_all, tf32, M, D, kTile, out);
-}
-
-// cudaFuncAttributeMaxDynamicSharedMemorySize is per function and per device: set it the first
-// time an instantiation is launched on a device, not on every launch.
-template <typename K>
-cudaError_t set_smem_once(K kern, int smem, unsigned long long& done_mask) {
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    static std::mutex mu;
-    std::lock_guard<std::mutex> lock(mu);
-    if (dev < 64 && ((done_mask >> dev) & 1ull)) return cudaSuccess;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e == cudaSuccess && dev < 64) done_mask |= 1ull << dev;
-    return e;
 }
 
 template <int D, bool TF32, bool kOnline>
@@ -1064,6 +974,50 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
 }
 
 }  // namespace
+
+// Encoding a tensor map is ~1-2 us of host time per call and the same few (pointer, shape) pairs
+// come back every step: keep the last ones.  (A map only encodes address, shape and layout, so a
+// hit stays valid when the buffer was freed and handed out again at the same address.)
+struct TmapKey {
+    const void* base; int64_t rows, cols; int box_rows; bool tf32;
+    bool operator==(const TmapKey& o) const {
+        return base == o.base && rows == o.rows && cols == o.cols && box_rows == o.box_rows && tf32 == o.tf32;
+    }
+};
+cudaError_t tc::cached_tmap_2d(const void* base, bool tf32, int64_t rows, int64_t cols, int box_rows,
+                           CUtensorMap* out) {
+    constexpr int kSlots = 32;
+    static std::mutex mu;
+    static TmapKey keys[kSlots];
+    static CUtensorMap maps[kSlots];
+    static int used = 0, next = 0;
+    const TmapKey key{base, rows, cols, box_rows, tf32};
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (int i = 0; i < used; ++i)
+            if (keys[i] == key) { *out = maps[i]; return cudaSuccess; }
+    }
+    cudaError_t e = make_tmap_2d(base, tf32, rows, cols, box_rows, out);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    const int slot = used < kSlots ? used++ : (next++ % kSlots);
+    keys[slot] = key;
+    maps[slot] = *out;
+    return cudaSuccess;
+}
+
+
+cudaError_t tc::set_smem_once_impl(const void* kern, int smem, unsigned long long& done_mask) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev < 64 && ((done_mask >> dev) & 1ull)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && dev < 64) done_mask |= 1ull << dev;
+    return e;
+}
 
 bool tc_set_trace_buffer(unsigned long long* dev_ptr) {
     if (dev_ptr && !NTXENT_TRACE) return false;  // this build has no time stamps compiled in

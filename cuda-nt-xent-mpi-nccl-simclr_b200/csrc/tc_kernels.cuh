@@ -21,6 +21,26 @@ cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
                           float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream);
 
+// ---- forward over the upper triangle (tc_fwd_sym.cu): whole-batch calls on one device, bf16
+// operands, fixed-max regime (log2(e)/tau <= 50), M >= kSymMinRows.
+constexpr int64_t kSymMinRows = 4096;
+struct SymPlan {
+    int T;      // row tiles = column tiles
+    int L;      // tiles per chunk (one CTA per chunk)
+    int items;  // CTAs
+    int slots;  // row-sum partials per row (chunks of the longest row)
+    size_t cpart_floats;  // column partials: T (T-1)/2 tile pairs x 4 quadrants x 128 columns
+};
+bool tc_sym_supported(int64_t M, int64_t D, bool op_bf16, float tau, unsigned flags);
+SymPlan tc_sym_plan(int64_t M, int64_t D, int num_sms);
+// part_s [slots][M], cpart [cpart_floats], pos_t [M] (positive logits, base-2 units)
+cudaError_t tc_launch_fwd_sym(const void* u_all, int64_t M, int64_t D, float tau, const SymPlan& sp,
+                              float* part_s, float* cpart, float* pos_t, cudaStream_t stream);
+// -> lse_out [M], block_partials [T] (per-row-tile sums of l_i - S_i,pos(i))
+cudaError_t tc_launch_fwd_sym_finalize(int64_t M, const SymPlan& sp, const float* part_s, const float* cpart,
+                                       const float* pos_t, float* lse_out, float* block_partials,
+                                       cudaStream_t stream);
+
 // Scratch the tf32 backward needs for its transposed copy of U ([D, M rounded up to 4] fp32);
 // zero for bf16 operands.
 size_t tc_bwd_scratch_bytes(int64_t M, int64_t D, bool op_bf16);

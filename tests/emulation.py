@@ -17,9 +17,15 @@ from ntxent_b200 import capi
 
 
 @torch.no_grad()
-def emulate_bf16_step(z_t: torch.Tensor, tau: float, grad_out: float = 1.0, block: int = 4096):
+def emulate_bf16_step(z_t: torch.Tensor, tau: float, grad_out: float = 1.0, block: int = 4096,
+                      sym_forward=None):
     """-> (loss float, lse[M] fp64 cpu-able tensor, dz[M, D] fp32) for bf16-operand configurations
-    in the fixed-max regime (log2(e)/tau <= 50)."""
+    in the fixed-max regime (log2(e)/tau <= 50).
+
+    sym_forward: the whole-batch forward of M >= 4096 rows runs over the upper triangle of tiles
+    (csrc/tc_fwd_sym.cu): a logit of the lower triangle is taken from its mirror tile, where the
+    re-rounded k*U operand is the OTHER row -- (k u_a)~ . u_b and (k u_b)~ . u_a differ in the last
+    bf16 bit of the operand.  None: decide as the library does."""
     prev = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = False
     try:
@@ -30,13 +36,20 @@ def emulate_bf16_step(z_t: torch.Tensor, tau: float, grad_out: float = 1.0, bloc
         ub, inv_norm = capi.normalize(z_t, flags)       # the device's own bf16 U and 1/|z|
         uf = ub.float()
         ka = (uf * k).bfloat16().float()                # the A operand: k*U_a, rounded again
+        if sym_forward is None:
+            sym_forward = M >= 4096 and block % 128 == 0
         idx = torch.arange(M, device=z_t.device)
         pos = (idx + N) % M
+        tile = idx // 128
         l2 = torch.empty(M, dtype=torch.float32, device=z_t.device)
         pos_t = torch.empty(M, dtype=torch.float32, device=z_t.device)
         for r0 in range(0, M, block):
             r1 = min(M, r0 + block)
             t = ka[r0:r1] @ uf.t()
+            if sym_forward:  # lower-triangle tiles: the mirror tile's value, u_a . (k u_b)~
+                lower = tile[r0:r1, None] > tile[None, :]
+                t = torch.where(lower, uf[r0:r1] @ ka.t(), t)
+                del lower
             pos_t[r0:r1] = t[idx[: r1 - r0], pos[r0:r1]]
             t[idx[: r1 - r0], idx[r0:r1]] = float("-inf")
             l2[r0:r1] = torch.log2(torch.exp2(t).double().sum(dim=1)).float()

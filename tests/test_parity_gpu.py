@@ -168,14 +168,19 @@ def test_config_c4_full_size(oracle):
     rdz = _dz_from_rowblock(zq, tau, rlse, du_row, du_col, slice(0, M))
     err_oracle = dz_err(dz, rdz)
     assert err_oracle <= DZ_TOL_BF16, err_oracle
-    # (b) rounding-faithful restatement, everything
-    el, else_, edz = emulate_bf16_step(z_t, tau)
+    # (b) rounding-faithful restatement, everything.  The same bf16 values stored as fp32 with
+    # use_mixed_precision: the same kernels on the same bf16 operands, but dz comes back in fp32 --
+    # a bf16 dz is quantised to 2^-9 of each entry, which would bury a 3e-4 tile.
+    z_f = z_t.float()
+    loss_f, lse_f, dz_f, _ = run_gpu(z_f, tau, mp=True)
+    assert loss_f == loss and dz_err(dz, dz_f) <= 2.0 ** -8  # bf16 storage only rounds the output
+    el, else_, edz = emulate_bf16_step(z_f, tau)
     edz = edz.double().cpu().numpy()
-    assert loss == pytest.approx(el, rel=2e-6)
-    np.testing.assert_allclose(lse, else_.cpu().numpy(), rtol=0, atol=2e-5)
-    err_emu = dz_err(dz, edz)
+    assert loss_f == pytest.approx(el, rel=2e-6)
+    np.testing.assert_allclose(lse_f, else_.cpu().numpy(), rtol=0, atol=2e-5)
+    err_emu = dz_err(dz_f, edz)
     # per row tile as well: a fault confined to one tile must not hide behind the global maximum
-    tile_err = np.abs(dz - edz).reshape(M // 128, -1).max(1) / np.abs(edz).max()
+    tile_err = np.abs(dz_f - edz).reshape(M // 128, -1).max(1) / np.abs(edz).max()
     print(f"C4 dz: vs CPU oracle {err_oracle:.2e}, vs restatement {err_emu:.2e} (worst row tile {tile_err.argmax()})")
     assert err_emu <= 2e-4, (err_emu, int(tile_err.argmax()))
     # (c) properties
@@ -205,11 +210,15 @@ def test_config_c5_full_size(oracle):
     loss, lse, dz, pp = run_gpu(z_t, tau)
     assert torch.cuda.max_memory_allocated() - before < 2 * 2**30  # O(M*D) working set
     assert math.isfinite(loss) and abs(loss - math.log(M)) < 1.0 and np.isfinite(dz).all()
-    el, else_, edz = emulate_bf16_step(z_t, tau, block=2048)
+    z_f = z_t.float()  # same bf16 values, fp32 storage: dz comes back unquantised (see the C4 test)
+    loss_f, lse_f, dz_f, _ = run_gpu(z_f, tau, mp=True)
+    assert loss_f == loss
+    el, else_, edz = emulate_bf16_step(z_f, tau, block=2048)
     edz = edz.double().cpu().numpy()
-    assert loss == pytest.approx(el, rel=2e-6)
-    np.testing.assert_allclose(lse, else_.cpu().numpy(), rtol=0, atol=2e-5)
-    err_emu = dz_err(dz, edz)
+    assert loss_f == pytest.approx(el, rel=2e-6)
+    np.testing.assert_allclose(lse_f, else_.cpu().numpy(), rtol=0, atol=2e-5)
+    err_emu = dz_err(dz_f, edz)
+    del dz_f, edz
     assert err_emu <= 2e-4, err_emu
     # CPU oracle on a row sample: rows [0, R).  Their dU needs the column term sum_b P_ba u_b with
     # P_ba = exp(S_ab - l_b) for ALL b: formed here in fp64 numpy from the oracle's own normalised

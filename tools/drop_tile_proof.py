@@ -22,8 +22,9 @@ from ntxent_b200 import capi
 from conftest import seeded_z
 from emulation import emulate_bf16_step
 M, D, tau = 32768, 128, 0.1
-z = torch.from_numpy(seeded_z(M, D)).cuda().to(torch.bfloat16)
-loss, lse, dz = capi.forward_backward(z, tau)
+# bf16 values stored as fp32 + use_mixed_precision: the bf16 kernels, with dz returned unquantised
+z = torch.from_numpy(seeded_z(M, D)).cuda().to(torch.bfloat16).float()
+loss, lse, dz = capi.forward_backward(z, tau, None, True)
 el, _, edz = emulate_bf16_step(z, tau)
 d = (dz.float() - edz).abs()
 err = (d.max() / edz.abs().max()).item()
