@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libntxent_b200.so")
 LIB_PATH_TRACE = LIB_PATH[:-3] + "_trace.so"
 BINDING_PATH = os.path.join(PKG_DIR, "ntxent_cuda.so")
 
-KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu", "tc_fwd_sym.cu"]
+KERNEL_SOURCES = ["capi.cu", "simt_kernels.cu", "epilogue_kernels.cu", "tc_kernels.cu", "tc_fwd_sym.cu", "comm.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v",
@@ -76,7 +76,8 @@ def build_library(force: bool = False, verbose: bool = False, trace: bool = Fals
             log.append(out)
             if p.returncode != 0:
                 raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
-        link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib_path, *objs]  # static cudart
+        # static cudart; libdl for the late-bound NCCL (comm.cu)
+        link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib_path, *objs, "-ldl"]
         subprocess.run(link, check=True)
         if not trace and not variant:
             with open(os.path.join(CSRC, "ptxas.log"), "w") as f:

@@ -28,8 +28,12 @@ EXPORTS = [
     "ntxent_b200_plan_info", "ntxent_b200_forward_static", "ntxent_b200_debug_set_trace",
     "ntxent_b200_normalize_push", "ntxent_b200_forward_rows_push", "ntxent_b200_peer_wait",
     "ntxent_b200_backward_rows_dz", "ntxent_b200_backward_tau",
-    "ntxent_b200_set_peer_wait_timeout_ms",
+    "ntxent_b200_set_peer_wait_timeout_ms", "ntxent_b200_backward_rows_part",
+    "ntxent_b200_comm_init_all", "ntxent_b200_comm_unique_id", "ntxent_b200_comm_init_rank",
+    "ntxent_b200_comm_destroy", "ntxent_b200_comm_info", "ntxent_b200_comm_status",
+    "ntxent_b200_dist_forward_backward",
 ]
+EXCHANGE_PUSH, EXCHANGE_NCCL = 0, 1
 
 _lib = None
 MAX_PEERS = 16
@@ -135,6 +139,23 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_backward_rows_dz.restype = ci
     L.ntxent_b200_backward_rows_dz.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
                                                vp, pw, vp]
+    L.ntxent_b200_backward_rows_part.restype = ci
+    L.ntxent_b200_backward_rows_part.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, ci, u32, vp, sz, vp, vp]
+    vpp, i64p = ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int64)
+    L.ntxent_b200_comm_init_all.restype = ci
+    L.ntxent_b200_comm_init_all.argtypes = [ci, ip, i64, i64, ci, u32, vpp]
+    L.ntxent_b200_comm_unique_id.restype = ci
+    L.ntxent_b200_comm_unique_id.argtypes = [vp]
+    L.ntxent_b200_comm_init_rank.restype = ci
+    L.ntxent_b200_comm_init_rank.argtypes = [vp, ci, ci, i64, i64, ci, u32, vpp]
+    L.ntxent_b200_comm_destroy.restype = ci
+    L.ntxent_b200_comm_destroy.argtypes = [vp]
+    L.ntxent_b200_comm_info.restype = ci
+    L.ntxent_b200_comm_info.argtypes = [vp, ip, ip, i64p, ip]
+    L.ntxent_b200_comm_status.restype = ci
+    L.ntxent_b200_comm_status.argtypes = [vp]
+    L.ntxent_b200_dist_forward_backward.restype = ci
+    L.ntxent_b200_dist_forward_backward.argtypes = [vp, vp, vp, f32, ci, ci, vp, vp, vp]
     L.ntxent_b200_debug_set_trace.restype = ci
     L.ntxent_b200_debug_set_trace.argtypes = [vp]
     L.ntxent_b200_forward_static.restype = ci
@@ -446,3 +467,71 @@ def backward_rows_dz(u_all: torch.Tensor, lse_all: torch.Tensor, row_begin: int,
                                                  _ptr(z_rows), _ptr(inv_norm), _ptr(grad_out), _ptr(dz),
                                                  _ref(lse_ready), _stream()))
     return dz
+
+
+# ---- communicator (include/ntxent_b200.h, "Communicator") ----------------------------------
+def comm_unique_id() -> bytes:
+    """128 opaque bytes made by rank 0; hand them to every rank (e.g. a torch.distributed broadcast)."""
+    buf = ctypes.create_string_buffer(128)
+    check(lib().ntxent_b200_comm_unique_id(buf))
+    return buf.raw
+
+
+class Communicator:
+    """One rank's handle on ntxent_b200_comm_*: owns the peer-mapped buffers, the row workspace and
+    (when NCCL could be loaded) a NCCL communicator.  `forward_backward(z_rows)` is the whole
+    row-partitioned step as one C-ABI call."""
+
+    def __init__(self, handle, device, dtype):
+        self.handle, self.device, self.dtype = handle, torch.device(device), dtype
+        rank, nranks, has = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        rows = ctypes.c_int64()
+        check(lib().ntxent_b200_comm_info(handle, ctypes.byref(rank), ctypes.byref(nranks), ctypes.byref(rows),
+                                          ctypes.byref(has)))
+        self.rank, self.nranks, self.rows, self.has_nccl = rank.value, nranks.value, rows.value, bool(has.value)
+
+    @classmethod
+    def init_rank(cls, unique_id: bytes, nranks: int, rank: int, M: int, D: int, dtype: torch.dtype, device,
+                  flags: int = 0):
+        h = ctypes.c_void_p()
+        code = BF16 if dtype == torch.bfloat16 else F32
+        with torch.cuda.device(device):
+            check(lib().ntxent_b200_comm_init_rank(ctypes.c_char_p(unique_id), nranks, rank, M, D, code, flags,
+                                                   ctypes.byref(h)))
+        return cls(h, device, dtype)
+
+    @classmethod
+    def init_all(cls, devices, M: int, D: int, dtype: torch.dtype, flags: int = 0):
+        """Single process: one communicator per device index in `devices`."""
+        n = len(devices)
+        devs = (ctypes.c_int * n)(*[int(d) for d in devices])
+        hs = (ctypes.c_void_p * n)()
+        code = BF16 if dtype == torch.bfloat16 else F32
+        check(lib().ntxent_b200_comm_init_all(n, devs, M, D, code, flags, hs))
+        return [cls(ctypes.c_void_p(hs[i]), torch.device("cuda", int(devices[i])), dtype) for i in range(n)]
+
+    def forward_backward(self, z_rows: torch.Tensor, tau: float, grad_out: torch.Tensor | None = None,
+                         exchange: int = EXCHANGE_PUSH, bwd_mode: int = BWD_SYMMETRIC, out=None):
+        """-> (loss[1] global mean, dz_rows).  `out` may carry preallocated (loss, dz)."""
+        _require_cuda(z_rows, grad_out)
+        z_rows = z_rows.contiguous()
+        if grad_out is not None:
+            grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+        with torch.cuda.device(self.device):
+            if out is None:
+                loss = torch.empty(1, dtype=torch.float32, device=self.device)
+                dz = torch.empty_like(z_rows)
+            else:
+                loss, dz = out
+            check(lib().ntxent_b200_dist_forward_backward(self.handle, _ptr(z_rows), _ptr(grad_out), float(tau),
+                                                          exchange, bwd_mode, _ptr(loss), _ptr(dz), _stream()))
+        return loss, dz
+
+    def status(self) -> int:
+        """0, or 1 + the rank a kernel of this rank gave up waiting for.  Synchronises."""
+        return int(lib().ntxent_b200_comm_status(self.handle))
+
+    def destroy(self) -> None:
+        if self.handle is not None:
+            check(lib().ntxent_b200_comm_destroy(self.handle))
+            self.handle = None

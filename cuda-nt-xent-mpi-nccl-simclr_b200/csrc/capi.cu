@@ -252,7 +252,11 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                 w.part_s, u_ready, st));
     g_timer.stop(0, st);
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
+#ifdef NTX_FWD_NOPOS
+                                     w.part_m, w.part_s, nullptr, lse_outs, lse_offset,
+#else
                                      w.part_m, w.part_s, p.tc ? w.pos_t : nullptr, lse_outs, lse_offset,
+#endif
                                      w.block_partials, loss_outs, loss_index, loss_scale, lse_signal, st));
     return NTXENT_OK;
 }
@@ -337,6 +341,44 @@ int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t
     return NTXENT_OK;
 }
 
+// Row block I = [row_begin, row_begin + row_count) against all columns: the symmetric dU of the
+// block (sym) or the row term G_{I,:} U of the contract form -> du_rows_out [row_count, D].
+int run_bwd_row_term(const void* u_all, bool opb, const float* lse_all, int64_t M, int64_t D, int64_t row_begin,
+                     int64_t row_count, float tau, bool sym, const Plans& p, const RowsWs& w, float* du_rows_out,
+                     cudaStream_t stream) {
+    int rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau, sym ? kSym : kRow, p,
+                           p.bwd_rows, w.acc_rows, w.ut, stream);
+    if (rc != NTXENT_OK) return rc;
+    BwdEpilogueArgs e{};
+    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit;
+    e.sk_ctas = p.bwd_rows.sk_ctas; e.sk_col_tiles = p.bwd_rows.sk_col_tiles;
+    e.u_all = u_all; e.op_bf16 = opb;
+    e.M = M; e.D = D; e.a_begin = row_begin; e.a_count = row_count;
+    e.pos_coeff = sym ? 2.f : 1.f; e.pos_lo = 0; e.pos_hi = M;
+    e.scale = 1.0f / (tau * (float)M);
+    e.du_out = du_rows_out;
+    NTX_TRY(launch_bwd_epilogue(e, stream));
+    return NTXENT_OK;
+}
+// All rows against the columns of block I: the column term G_{I,:}^T U_I -> du_cols_out [M, D].
+int run_bwd_col_term(const void* u_all, bool opb, const float* lse_all, int64_t M, int64_t D, int64_t row_begin,
+                     int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* du_cols_out,
+                     cudaStream_t stream) {
+    int rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p, p.bwd_cols,
+                           w.acc_cols, w.ut, stream);
+    if (rc != NTXENT_OK) return rc;
+    BwdEpilogueArgs c{};
+    c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit;
+    c.sk_ctas = p.bwd_cols.sk_ctas; c.sk_col_tiles = p.bwd_cols.sk_col_tiles;
+    c.u_all = u_all; c.op_bf16 = opb;
+    c.M = M; c.D = D; c.a_begin = 0; c.a_count = M;
+    c.pos_coeff = 1.f; c.pos_lo = row_begin; c.pos_hi = row_begin + row_count;
+    c.scale = 1.0f / (tau * (float)M);
+    c.du_out = du_cols_out;
+    NTX_TRY(launch_bwd_epilogue(c, stream));
+    return NTXENT_OK;
+}
+
 int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_bf16, const float* lse,
                         const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
                         void* dz_out, float* pos_prob_out, cudaStream_t st,
@@ -392,6 +434,11 @@ const char* ntxent_b200_strerror(int code) {
         case NTXENT_ERR_STATIC_SCRATCH_EXCEEDED:
             return "problem needs more scratch than the built-in NTXENT_STATIC_SCRATCH_BYTES array "
                    "of ntxent_b200_forward_static; use ntxent_b200_forward with a caller workspace";
+        case NTXENT_ERR_COLLECTIVE:
+            return "collective library: libnccl.so.2 could not be loaded, the communicator was made without "
+                   "it, or a NCCL call failed (NTXENT_DEBUG=1 names the call)";
+        case NTXENT_ERR_NO_PEER_ACCESS:
+            return "the devices of the communicator cannot map each other's memory (no peer access / CUDA IPC)";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
@@ -682,33 +729,29 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     const bool sym = (mode == NTXENT_BWD_SYMMETRIC);
-    rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau,
-                       sym ? kSym : kRow, p, p.bwd_rows, w.acc_rows, w.ut, stream);
+    rc = run_bwd_row_term(u_all, opb, lse_all, M, D, row_begin, row_count, tau, sym, p, w, du_rows_out, stream);
+    if (rc != NTXENT_OK || sym) return rc;
+    return run_bwd_col_term(u_all, opb, lse_all, M, D, row_begin, row_count, tau, p, w, du_cols_out, stream);
+}
+
+int ntxent_b200_backward_rows_part(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                                   int64_t row_begin, int64_t row_count, float tau, int part,
+                                   int dtype, unsigned flags, void* workspace, size_t workspace_bytes,
+                                   float* out, ntxent_stream_t stream) {
+    if (!u_all || !lse_all || !workspace || !out || (part != 0 && part != 1)) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(u_all, 16) || !aligned(workspace, 256) || !aligned(out, 16)) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
     if (rc != NTXENT_OK) return rc;
-    BwdEpilogueArgs e{};
-    e.acc = w.acc_rows; e.nsplit = p.bwd_rows.nsplit;
-    e.sk_ctas = p.bwd_rows.sk_ctas; e.sk_col_tiles = p.bwd_rows.sk_col_tiles;
-    e.u_all = u_all; e.op_bf16 = opb;
-    e.M = M; e.D = D; e.a_begin = row_begin; e.a_count = row_count;
-    e.pos_coeff = sym ? 2.f : 1.f; e.pos_lo = 0; e.pos_hi = M;
-    e.scale = 1.0f / (tau * (float)M);
-    e.du_out = du_rows_out;
-    NTX_TRY(launch_bwd_epilogue(e, stream));
-    if (!sym) {
-        rc = run_bwd_tiles(u_all, opb, lse_all, M, D, 0, M, row_begin, row_count, tau, kCol, p,
-                           p.bwd_cols, w.acc_cols, w.ut, stream);
-        if (rc != NTXENT_OK) return rc;
-        BwdEpilogueArgs c{};
-        c.acc = w.acc_cols; c.nsplit = p.bwd_cols.nsplit;
-        c.sk_ctas = p.bwd_cols.sk_ctas; c.sk_col_tiles = p.bwd_cols.sk_col_tiles;
-        c.u_all = u_all; c.op_bf16 = opb;
-        c.M = M; c.D = D; c.a_begin = 0; c.a_count = M;
-        c.pos_coeff = 1.f; c.pos_lo = row_begin; c.pos_hi = row_begin + row_count;
-        c.scale = e.scale;
-        c.du_out = du_cols_out;
-        NTX_TRY(launch_bwd_epilogue(c, stream));
-    }
-    return NTXENT_OK;
+    if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, row_count, opb, flags, tau);
+    const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    if (part == 0)
+        return run_bwd_row_term(u_all, opb, lse_all, M, D, row_begin, row_count, tau, false, p, w, out, stream);
+    return run_bwd_col_term(u_all, opb, lse_all, M, D, row_begin, row_count, tau, p, w, out, stream);
 }
 
 int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,

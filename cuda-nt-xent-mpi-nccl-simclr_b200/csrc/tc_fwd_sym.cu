@@ -47,6 +47,14 @@ __device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t* r) 
         : "r"(taddr)
         : "memory");
 }
+// 16 TMEM lanes x 16 columns -> 8 registers, same arrangement with n = 0..1.
+__device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(taddr)
+        : "memory");
+}
 // One 32-row x 32-column block (this warp's lane quadrant, columns col..col+31) into v[0..31]:
 // v[16 h + 4 n + q]  =  row 16 h + 8 (q >> 1) + lane / 4,  column 8 n + 2 (lane % 4) + (q & 1).
 __device__ __forceinline__ void ld_block(uint32_t quad_addr, uint32_t col, uint32_t (&v)[32]) {
@@ -190,7 +198,8 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
         // 32-column block: 8 n + cbase + {0, 1}
         const int rbase = quad * 32 + (lane >> 2);
         const int cbase = 2 * (lane & 3);
-        float rs[4] = {0.f, 0.f, 0.f, 0.f};
+        // row sums, as packed pairs (even column, odd column) of the thread's four rows
+        f32x2 rs2[4] = {0ull, 0ull, 0ull, 0ull};
         // scale the row tile by k = log2(e)/tau where TMA put it (elementwise, so the swizzle is
         // irrelevant), then publish it to the tensor core's (async-proxy) view of shared memory
         {
@@ -223,8 +232,6 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
         const int hj_pos_lo = p0 / 64, hj_pos_hi = (min(p0 + kTile, (int)M) - 1) / 64;
         const int hj_wrap_hi = p0 + kTile > (int)M ? (p0 + kTile - (int)M - 1) / 64 : -1;
         // column partials of tile (i, j): cpart[(j (j-1)/2 + i) * 512 + quad * 128 + column]
-        const int col_of_lane = 8 * (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)) + cbase + ((lane >> 2) & 1);
-
         // (all row / column numbers fit 32 bits: M <= 2^24)
         const int M32 = (int)M, N32 = (int)(M / 2), row0 = (int)a0 + rbase;
         int pos4[4];  // the positives of this thread's four rows
@@ -233,29 +240,43 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
             const int p = row0 + 8 * g + N32;
             pos4[g] = p >= M32 ? p - M32 : p;
         }
+        const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+        // where this lane's finished column sum of a pair of 16-column blocks goes (see `store2`)
+        const int col_of_lane = (b2 ? 16 : 0) + (b4 ? 8 : 0) + cbase + (b3 ? 1 : 0);
 
-        auto block = [&](const uint32_t (&v)[32], int jt, int blk, bool special) {
-            const bool diag = jt == item.i;
-            float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        // One 32-row x 16-column block: exponentials, row sums (packed, into rs2), and the column
+        // sums reduced over bits 4 and 3 of the lane number -- returned: the partial sum (still to be
+        // added over bit 2) of column 8 b4 + cbase + b3 of the block.
+        auto block = [&](const uint32_t (&v)[16], int jt, int blk, bool special) -> float {
+            float cs[4];
             if (!special) {
+                // registers r, r+1 are one row's two neighbouring columns: one packed add each into
+                // the row pair and the column pair
+                f32x2 cs2[2] = {0ull, 0ull};
 #pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const float e = ex2_mix<kFwdPoly>(__uint_as_float(v[r]), r);
-                    rs[2 * (r >> 4) + ((r >> 1) & 1)] += e;
-                    cs[2 * ((r >> 2) & 3) + (r & 1)] += e;
+                for (int r = 0; r < 16; r += 2) {
+                    const f32x2 e = ex2_pair<kFwdPolyPairs>(v[r], v[r + 1], r >> 1);
+                    const int g = 2 * (r >> 3) + ((r >> 1) & 1);
+                    rs2[g] = add2(rs2[g], e);
+                    cs2[(r >> 2) & 1] = add2(cs2[(r >> 2) & 1], e);
                 }
+                unpack2(cs2[0], cs[0], cs[1]);
+                unpack2(cs2[1], cs[2], cs[3]);
             } else {
-                const int c0 = jt * kTile + half * 64 + blk * 32 + cbase;
+                const bool diag = jt == item.i;
+                const int c0 = jt * kTile + half * 64 + blk * 16 + cbase;
+                float rs[4] = {0.f, 0.f, 0.f, 0.f};
+                cs[0] = cs[1] = cs[2] = cs[3] = 0.f;
 #pragma unroll
-                for (int r = 0; r < 32; ++r) {
-                    const int g = 2 * (r >> 4) + ((r >> 1) & 1);
+                for (int r = 0; r < 16; ++r) {
+                    const int g = 2 * (r >> 3) + ((r >> 1) & 1);
                     const int row = row0 + 8 * g;
-                    const int col = c0 + 8 * ((r >> 2) & 3) + (r & 1);
+                    const int col = c0 + 8 * ((r >> 2) & 1) + (r & 1);
                     const float t = __uint_as_float(v[r]);
                     const bool ok = col < M32 && col != row && row < M32;
                     const float e = ok ? ex2(t) : 0.f;
                     rs[g] += e;
-                    cs[2 * ((r >> 2) & 3) + (r & 1)] += e;
+                    cs[2 * ((r >> 2) & 1) + (r & 1)] += e;
                     // the positive logit, from the same MMA as the denominator; off the diagonal tile
                     // the element (row, col) is also the positive logit of row `col`
                     if (ok && col == pos4[g]) {
@@ -263,29 +284,58 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
                         if (!diag) pos_t_out[col] = t;
                     }
                 }
+#pragma unroll
+                for (int g = 0; g < 4; ++g) rs2[g] = add2(rs2[g], pack2(rs[g], 0.f));
             }
-            if (!diag) {
-                const float s = colsum_butterfly(cs, lane);
-                const int64_t pair = (int64_t)jt * (jt - 1) / 2 + item.i;
-                cpart[pair * 512 + quad * 128 + half * 64 + blk * 32 + col_of_lane] = s;
+            // cs[2 n + b] = this thread's sum (4 rows) of column 8 n + cbase + b: transpose-reduce over
+            // lane bit 4 (which n) and lane bit 3 (which b)
+            float k2[2];
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const float send = b4 ? cs[k] : cs[2 + k], keep = b4 ? cs[2 + k] : cs[k];
+                k2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
             }
+            const float send = b3 ? k2[0] : k2[1], keep = b3 ? k2[1] : k2[0];
+            return keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        };
+        // Two neighbouring blocks finish together: the last level (lane bit 2) hands block A's
+        // column to the lanes with b2 = 0 and block B's to those with b2 = 1 -- one shuffle, and the
+        // warp stores 32 finished column sums (one 128-byte line) of its quadrant.
+        auto store2 = [&](float pa, float pb, int jt, int pairno) {
+            if (jt == item.i) return;  // diagonal tile: its column sums are its row sums
+            const float send = b2 ? pa : pb, keep = b2 ? pb : pa;
+            const float s = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            const int64_t pr = (int64_t)jt * (jt - 1) / 2 + item.i;
+            cpart[pr * 512 + quad * 128 + half * 64 + pairno * 32 + col_of_lane] = s;
+        };
+        auto ld_blk = [&](uint32_t col, uint32_t (&v)[16]) {
+            tmem_ld_16x256b_x2(quad_addr + col, &v[0]);
+            tmem_ld_16x256b_x2(quad_addr + (16u << 16) + col, &v[8]);
         };
 
-        // two 32-column blocks per tile, double-buffered in registers: the load of the next block
+        // four 16-column blocks per tile, double-buffered in registers: the load of the next block
         // (or of the next tile's first block) is in flight while the current one is exponentiated
-        uint32_t va[32], vb[32];
+        uint32_t va[16], vb[16];
         mbar_wait(&s_full[0], 0);
         tc_fence_after();
-        ld_block(quad_addr, 0, va);
+        ld_blk(0, va);
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
             const int jt = item.j0 + it;
             const int hj = 2 * jt + half;
             const bool special = jt == item.i || hj >= hj_ragged || (hj >= hj_pos_lo && hj <= hj_pos_hi) ||
                                  hj <= hj_wrap_hi;
+            const uint32_t tcol = buf * kTile;
             tmem_ld_wait();
-            ld_block(quad_addr, buf * kTile + 32, vb);
-            block(va, jt, 0, special);
+            ld_blk(tcol + 16, vb);
+            float pa = block(va, jt, 0, special);
+            tmem_ld_wait();
+            ld_blk(tcol + 32, va);
+            float pb = block(vb, jt, 1, special);
+            store2(pa, pb, jt, 0);
+            tmem_ld_wait();
+            ld_blk(tcol + 48, vb);
+            pa = block(va, jt, 2, special);
             tmem_ld_wait();
             // this warp's S columns have left TMEM: hand the buffer back, then prefetch
             tc_fence_before();
@@ -294,14 +344,19 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
             if (it + 1 < n_tiles) {
                 mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
                 tc_fence_after();
-                ld_block(quad_addr, (buf ^ 1) * kTile, va);
+                ld_blk((buf ^ 1) * kTile, va);
             }
-            block(vb, jt, 1, special);
+            pb = block(vb, jt, 3, special);
+            store2(pa, pb, jt, 1);
         }
         // row sums: over the four lanes that share the rows, then the two column halves through
         // shared memory (the row tile is no longer needed: every MMA that read it has completed)
+        float rs[4];
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
+            float lo, hi;
+            unpack2(rs2[g], lo, hi);
+            rs[g] = lo + hi;
             rs[g] += __shfl_xor_sync(0xffffffffu, rs[g], 1);
             rs[g] += __shfl_xor_sync(0xffffffffu, rs[g], 2);
         }
@@ -326,52 +381,56 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
 }
 
 // ---------------------------------------------------------------- finalize ---
-// One thread per row: its row-sum partials (one per chunk of its row tile) plus the column
-// partials of every tile above it in its column block, added in a fixed order.
-constexpr int kSymFinThreads = 128;
+// One CTA per row tile j, four threads per row: thread (g, c) adds the column partials of the
+// tiles (i, j), i = g, g + 4, ... (eight loads in flight), the four are combined through shared
+// memory in a fixed order, and thread (0, c) adds the row-sum partials (one per chunk of the row
+// tile).  Fixed order throughout: run-to-run deterministic.
+constexpr int kSymFinThreads = 512;
 __global__ void __launch_bounds__(kSymFinThreads)
 fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_s,
                         const float* __restrict__ cpart, const float* __restrict__ pos_t,
                         float* __restrict__ lse_out, float* __restrict__ block_partials) {
-    __shared__ float warp_contrib[kSymFinThreads / 32];
+    __shared__ float part[3][kTile];
+    __shared__ float warp_contrib[kTile / 32];
     pdl_trigger();
     pdl_wait();
     const int j = blockIdx.x;  // row tile == column tile of these rows
-    const int c = threadIdx.x;
+    const int c = threadIdx.x & (kTile - 1), g = threadIdx.x >> 7;
     const int64_t r = (int64_t)j * kTile + c;
-    float contrib = 0.f;
-    if (r < M) {
-        const int nslots = (T - j + L - 1) / L;
-        float s = 0.f;
-        for (int sl = 0; sl < nslots; ++sl) s += part_s[(int64_t)sl * M + r];
-        const float* cp = cpart + (int64_t)j * (j - 1) / 2 * 512 + c;
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};  // four chains: the loads of four tiles (16 values) in flight
-        int i = 0;
-        for (; i + 4 <= j; i += 4) {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const float* q = cp + (int64_t)(i + u) * 512;
-                s4[u] += (q[0] + q[128]) + (q[256] + q[384]);
-            }
-        }
-        for (; i < j; ++i) {
-            const float* q = cp + (int64_t)i * 512;
-            s4[0] += (q[0] + q[128]) + (q[256] + q[384]);
-        }
-        s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
-        const float l2 = log2f(s);
-        lse_out[r] = l2 * kLn2;
-        contrib = (l2 - pos_t[r]) * kLn2;
+    const float* cp = cpart + (int64_t)j * (j - 1) / 2 * 512 + c;
+    float s2[2] = {0.f, 0.f};
+    int i = g;
+    for (; i + 4 < j; i += 8) {
+        const float* q0 = cp + (int64_t)i * 512;
+        const float* q1 = q0 + 4 * 512;
+        const float a0 = q0[0], a1 = q0[128], a2 = q0[256], a3 = q0[384];
+        const float b0 = q1[0], b1 = q1[128], b2 = q1[256], b3 = q1[384];
+        s2[0] += (a0 + a1) + (a2 + a3);
+        s2[1] += (b0 + b1) + (b2 + b3);
     }
-    contrib = warp_sum(contrib);
-    if ((threadIdx.x & 31) == 0) warp_contrib[threadIdx.x >> 5] = contrib;
+    if (i < j) {
+        const float* q0 = cp + (int64_t)i * 512;
+        s2[0] += (q0[0] + q0[128]) + (q0[256] + q0[384]);
+    }
+    float s = s2[0] + s2[1];
+    if (g > 0) part[g - 1][c] = s;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        float bsum = 0.f;
-#pragma unroll
-        for (int w = 0; w < kSymFinThreads / 32; ++w) bsum += warp_contrib[w];
-        block_partials[blockIdx.x] = bsum;
+    float contrib = 0.f;
+    if (g == 0) {
+        if (r < M) {
+            s = (s + part[0][c]) + (part[1][c] + part[2][c]);
+            const int nslots = (T - j + L - 1) / L;
+            for (int sl = 0; sl < nslots; ++sl) s += part_s[(int64_t)sl * M + r];
+            const float l2 = log2f(s);
+            lse_out[r] = l2 * kLn2;
+            contrib = (l2 - pos_t[r]) * kLn2;
+        }
+        contrib = warp_sum(contrib);
+        if ((threadIdx.x & 31) == 0) warp_contrib[threadIdx.x >> 5] = contrib;
     }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        block_partials[blockIdx.x] = (warp_contrib[0] + warp_contrib[1]) + (warp_contrib[2] + warp_contrib[3]);
 }
 
 // chunk length: long enough to amortise a CTA's prologue (~1.5 tiles), short enough that the

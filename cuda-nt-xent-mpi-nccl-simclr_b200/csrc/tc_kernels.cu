@@ -53,11 +53,17 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
     if (!kOnline) {
         float p0 = 0.f, p1 = 0.f;
         if (!special) {
+            // packed pairs: one FADD2 per two logits, half of the pairs through the polynomial
+            f32x2 a0 = 0ull, a1 = 0ull;
 #pragma unroll
-            for (int e = 0; e < 32; e += 2) {
-                p0 += ex2_mix<kFwdPoly>(__uint_as_float(v[e]), e);
-                p1 += ex2_mix<kFwdPoly>(__uint_as_float(v[e + 1]), e + 1);
+            for (int e = 0; e < 32; e += 4) {
+                a0 = add2(a0, ex2_pair<kFwdPolyPairs>(v[e], v[e + 1], e >> 1));
+                a1 = add2(a1, ex2_pair<kFwdPolyPairs>(v[e + 2], v[e + 3], (e >> 1) + 1));
             }
+            float lo, hi;
+            unpack2(add2(a0, a1), lo, hi);
+            p0 = lo;
+            p1 = hi;
         } else {
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
@@ -234,12 +240,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         // ... and the one or two that hold the positives of THIS WARP's 32 rows (columns
         // (row + N) mod M: a run of 32, which can straddle a half-tile boundary or wrap around M)
         const int64_t wrow0 = a0 + quad * 32;
+#ifdef NTX_FWD_NOPOS
+        const int hj_pos_a = -1, hj_pos_b = -1;
+#else
         const int hj_pos_a = (int)(((wrow0 + M / 2) % M) / 64);
         const int hj_pos_b = (int)(((min(wrow0 + 31, M - 1) + M / 2) % M) / 64);
+#endif
         const int64_t pos_col = (row + M / 2) % M;
         // whether this warp's column range holds the row's positive at all (decided once, here)
         const int pos_hj = (int)(pos_col >> 6);
+#ifdef NTX_FWD_NOPOS  // A/B build: no capture here, the finalize kernel forms the dot products
+        const bool pos_seen = false;
+#else
         const bool pos_seen = (pos_hj & 1) == half && (pos_hj >> 1) >= jt0 && (pos_hj >> 1) < jt0 + n_tiles;
+#endif
         float pos_t = 0.f;
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;

@@ -222,6 +222,60 @@ __device__ __forceinline__ float ex2_poly(float t) {
     p = fmaf(p, r, 0.99992812f);
     return __int_as_float(__float_as_int(p) + (__float_as_int(tf) << 23));
 }
+// ---- packed fp32 pairs (sm_100: add/sub/mul/fma.f32x2 -> FADD2 / FMUL2 / FFMA2) ----------------
+// The softmax loops are limited by instruction issue, not by the FMA pipe: one packed instruction
+// does the work of two.  A pair lives in a 64-bit register (low word = first element).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+// ex2_poly for a pair: six packed instructions and two integer ones instead of sixteen.
+__device__ __forceinline__ f32x2 ex2_poly2(f32x2 t) {
+    const f32x2 magic = pack2(12582912.0f, 12582912.0f);
+    const f32x2 tf = add2(t, magic);
+    const f32x2 r = sub2(t, sub2(tf, magic));
+    f32x2 p = fma2(pack2(0.055171460f, 0.055171460f), r, pack2(0.24261086f, 0.24261086f));
+    p = fma2(p, r, pack2(0.69326097f, 0.69326097f));
+    p = fma2(p, r, pack2(0.99992812f, 0.99992812f));
+    float p0, p1, f0, f1;
+    unpack2(p, p0, p1);
+    unpack2(tf, f0, f1);
+    return pack2(__int_as_float(__float_as_int(p0) + (__float_as_int(f0) << 23)),
+                 __int_as_float(__float_as_int(p1) + (__float_as_int(f1) << 23)));
+}
+// 2^t for the pair `pr` of a chunk: kPolyPairs of every 4 consecutive pairs take the polynomial,
+// the others the MUFU.
+template <int kPolyPairs>
+__device__ __forceinline__ f32x2 ex2_pair(uint32_t t0, uint32_t t1, int pr) {
+    if ((pr & 3) < kPolyPairs) return ex2_poly2(pack2(__uint_as_float(t0), __uint_as_float(t1)));
+    return pack2(ex2(__uint_as_float(t0)), ex2(__uint_as_float(t1)));
+}
+
 // ex2 for element e of a chunk: kPoly of every 8 consecutive elements take the polynomial.
 template <int kPoly>
 __device__ __forceinline__ float ex2_mix(float t, int e) {

@@ -20,6 +20,12 @@ constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)
 #define NTX_BWD_POLY 0
 #endif
 constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
+// the packed (f32x2) forward loops: of every 4 consecutive PAIRS of exponentials, this many take
+// the polynomial (2 = half of them: MUFU and issue slots then cost about the same per tile)
+#ifndef NTX_FWD_POLY_PAIRS
+#define NTX_FWD_POLY_PAIRS 2
+#endif
+constexpr int kFwdPolyPairs = NTX_FWD_POLY_PAIRS;
 
 // TF32 = false: bf16 operands, .kind::f16 (K = 16 per MMA).  TF32 = true: fp32 operands read as
 // tf32, .kind::tf32 (K = 8 per MMA).  Either way one MMA consumes 32 bytes of every operand row

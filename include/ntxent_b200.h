@@ -49,6 +49,8 @@ enum { NTXENT_F32 = 0, NTXENT_BF16 = 1 };
 #define NTXENT_ERR_WORKSPACE_TOO_SMALL (-3)
 #define NTXENT_ERR_UNSUPPORTED_SHAPE (-4)
 #define NTXENT_ERR_STATIC_SCRATCH_EXCEEDED (-5)
+#define NTXENT_ERR_COLLECTIVE (-6)      /* NCCL missing, or a NCCL call failed (NTXENT_DEBUG=1 names it) */
+#define NTXENT_ERR_NO_PEER_ACCESS (-7)  /* the devices of a communicator cannot map each other's memory */
 
 /* Backward formulations of the row-partitioned path. */
 enum {
@@ -242,6 +244,76 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
 int ntxent_b200_finalize_dz(const float* du_rows, const void* z_rows, const float* inv_norm_rows,
                             const float* grad_out, int64_t rows, int64_t D, int dtype,
                             void* dz_out, ntxent_stream_t stream);
+
+/* One term of the CONTRACT-form backward at a time, so that a caller can put a
+ * collective between them (the column term goes into a reduce-scatter that can
+ * run while the row term is being computed): part 0 -> out float[row_count, D],
+ * the row term G_{I,:} U; part 1 -> out float[M, D], the column term
+ * G_{I,:}^T U_I of every global row.  Same arithmetic as
+ * ntxent_b200_backward_rows(mode = NTXENT_BWD_CONTRACT). */
+int ntxent_b200_backward_rows_part(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                                   int64_t row_begin, int64_t row_count, float tau, int part,
+                                   int dtype, unsigned flags, void* workspace, size_t workspace_bytes,
+                                   float* out, ntxent_stream_t stream);
+
+/* ---- Communicator: the row-partitioned step as ONE call per rank --------------
+ * The reference names NCCL and MPI as build options (CMakeLists.txt:13-14,41-47,
+ * 115-121: ENABLE_NCCL / ENABLE_MPI) and never calls either; north_star asks for
+ * "the MPI/NCCL communicator setup".  A communicator is created for a fixed
+ * problem (global M, D, dtype, flags) and owns everything a rank needs between
+ * its inputs and outputs: the gathered-operand buffers (two rotating sets, mapped
+ * on every peer -- cudaMalloc + peer access inside one process, CUDA IPC handles
+ * across processes), the flag arrays and call counters of the push path, the row
+ * workspace, and -- when libnccl.so.2 can be loaded -- a NCCL communicator for
+ * the collective-based exchanges.  Creation and destruction allocate and
+ * synchronise; ntxent_b200_dist_forward_backward does neither.
+ *
+ *   ntxent_b200_comm_init_all   single process, one communicator per listed
+ *                               device (drive each from its own host thread, or
+ *                               from one thread, a device at a time: the calls
+ *                               only enqueue work).
+ *   ntxent_b200_comm_unique_id + ntxent_b200_comm_init_rank
+ *                               one process per rank: rank 0 creates the 128-byte
+ *                               id, the caller hands it to every rank by its own
+ *                               means (MPI_Bcast, a torch.distributed broadcast, a
+ *                               file), every rank calls init_rank with its device
+ *                               current.  Needs NCCL (the bootstrap runs over it).
+ * MPI itself is not used anywhere: it would only carry the 128 bytes. */
+typedef struct ntxent_comm ntxent_comm_t;
+
+enum {
+    NTXENT_EXCHANGE_PUSH = 0, /* kernels store into the peers' buffers, ordered by flags
+                                 (the fused form; no collective launches)                  */
+    NTXENT_EXCHANGE_NCCL = 1  /* ncclAllGather of U (+ of l, or ncclReduceScatter of the
+                                 column term in CONTRACT mode, overlapped with the row pass
+                                 on a second stream): north_star's formulation             */
+};
+
+int ntxent_b200_comm_init_all(int ndev, const int* devices, int64_t M, int64_t D, int dtype,
+                              unsigned flags, ntxent_comm_t** comms_out);
+int ntxent_b200_comm_unique_id(void* id128_out);
+int ntxent_b200_comm_init_rank(const void* id128, int nranks, int rank, int64_t M, int64_t D,
+                               int dtype, unsigned flags, ntxent_comm_t** comm_out);
+int ntxent_b200_comm_destroy(ntxent_comm_t* comm);
+/* rank, number of ranks, rows per rank, and whether the NCCL exchanges are available */
+int ntxent_b200_comm_info(const ntxent_comm_t* comm, int* rank, int* nranks, int64_t* rows_per_rank,
+                          int* has_nccl);
+
+/* Fused forward+backward of the GLOBAL loss from this rank's shard.
+ * z_rows: device [M/nranks, D] in the communicator's dtype (rows rank*M/nranks ..).
+ * grad_out: device float[1] or NULL (= 1).  loss_out: device float[1], the global
+ * mean loss (identical on every rank).  dz_rows_out: device [M/nranks, D].
+ * exchange / bwd_mode: NTXENT_EXCHANGE_* / NTXENT_BWD_* (PUSH runs the SYMMETRIC
+ * form).  Every rank must make the same sequence of calls.  Asynchronous on
+ * `stream`; capturable into a CUDA graph once per buffer set (two consecutive
+ * calls).  After a peer-wait timeout (see ntxent_b200_set_peer_wait_timeout_ms)
+ * the results are void and ntxent_b200_comm_status returns the rank that was
+ * waited for. */
+int ntxent_b200_dist_forward_backward(ntxent_comm_t* comm, const void* z_rows, const float* grad_out,
+                                      float tau, int exchange, int bwd_mode, float* loss_out,
+                                      void* dz_rows_out, ntxent_stream_t stream);
+/* 0: fine; r + 1: a kernel of this rank gave up waiting for rank r.  Synchronises. */
+int ntxent_b200_comm_status(ntxent_comm_t* comm);
 
 /* Forward pass for callers that are not allowed to allocate device memory.
  *

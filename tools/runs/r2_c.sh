@@ -1,0 +1,27 @@
+#!/bin/bash
+# GPU run C (1 x B200): packed-f32x2 forward loops: tests, then bench A/B lines.
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/r2_c_tests.log 2>&1; echo "tests rc=$?"
+tail -25 gpurun_out/r2_c_tests.log
+B="--no-cpu-baseline --no-sustained"
+P=cuda-nt-xent-mpi-nccl-simclr_b200
+run() { # name, env...
+  name=$1; shift
+  env "$@" timeout 300 python bench.py $B > gpurun_out/r2_c_bench_$name.json 2>> gpurun_out/r2_c_bench.err
+  python - "$name" <<'PY'
+import json,sys
+n=sys.argv[1]
+try:
+    d=json.load(open(f"gpurun_out/r2_c_bench_{n}.json")); r=d["roofline"]
+    print(f"{n:14s} step {d['ms_per_step']:.4f} fwd {r['fwd_kernel']['ms_per_launch']:.4f} bwd {r['ms_per_launch']:.4f} side {r['side_kernels_ms']:.4f} e2e {d['e2e']['ms_per_step']:.4f}")
+except Exception as e:
+    print(n, "FAILED", e)
+PY
+}
+run sym A=1
+run nosym NTXENT_NO_SYM_FORWARD=1
+run sym_p1 NTXENT_LIBRARY=$PWD/$P/libntxent_b200_p1.so
+run sym_p3 NTXENT_LIBRARY=$PWD/$P/libntxent_b200_p3.so
+run nosym_p1 NTXENT_NO_SYM_FORWARD=1 NTXENT_LIBRARY=$PWD/$P/libntxent_b200_p1.so
+run nosym_nopos NTXENT_NO_SYM_FORWARD=1 NTXENT_LIBRARY=$PWD/$P/libntxent_b200_nopos.so
+tail -5 gpurun_out/r2_c_bench.err
