@@ -39,17 +39,9 @@ constexpr int64_t kTf32MinRows = 1024;      // fp32 operands take the tf32 tiles
 // already t = log2(e)/tau * u_a.u_b: the A operand was scaled by k = log2(e)/tau when it was
 // staged, which saves one FFMA per logit.  The fixed-max form sums 2^t as is (t <= k <= 50, so
 // M terms of at most 2^50 stay far inside fp32) and reports max = 0.
-// On the masked path the chunk is also searched for the row's positive, column pos_col: its
-// logit t goes to pos_t (the tiles that can hold it are always sent down the masked path).
 template <bool kOnline>
 __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special, int64_t col0,
-                                          int64_t row, int64_t M, int64_t pos_col, float& pos_t,
-                                          float& m_run, float& s_run) {
-    if (special) {
-#pragma unroll
-        for (int e = 0; e < 32; ++e)
-            if (col0 + e == pos_col) pos_t = __uint_as_float(v[e]);
-    }
+                                          int64_t row, int64_t M, float& m_run, float& s_run) {
     if (!kOnline) {
         float p0 = 0.f, p1 = 0.f;
         if (!special) {
@@ -254,17 +246,26 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 #else
         const bool pos_seen = (pos_hj & 1) == half && (pos_hj >> 1) >= jt0 && (pos_hj >> 1) < jt0 + n_tiles;
 #endif
+        const int pos_col32 = (int)pos_col;
         float pos_t = 0.f;
         for (int it = 0; it < n_tiles; ++it) {
             const int buf = it & 1;
             const int hj = 2 * (jt0 + it) + half;
-            const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged ||
-                                 hj == hj_pos_a || hj == hj_pos_b;
+            const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged;
+            // the half tile(s) that hold this warp's positives: pick the logit out of the registers
+            // (a rare branch of its own: it must not sit in the exponential loops)
+            const bool has_pos = hj == hj_pos_a || hj == hj_pos_b;
+            const int pos_d = pos_col32 - hj * 64;  // 0..63 when the positive is in here
             const int64_t j0 = (int64_t)hj * 64;  // (used on the masked path only)
             const uint32_t taddr = lane_addr + buf * kTile;
             tmem_ld_wait();
             tmem_ld32(taddr + 32, vb);
-            fwd_chunk<kOnline>(va, special, j0, row, M, pos_col, pos_t, m_run, s_run);
+            fwd_chunk<kOnline>(va, special, j0, row, M, m_run, s_run);
+            if (has_pos) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e)
+                    if (pos_d == e) pos_t = __uint_as_float(va[e]);
+            }
             tmem_ld_wait();
             // this warp's S columns have left TMEM: hand the buffer back, then prefetch
             tc_fence_before();
@@ -275,7 +276,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 tc_fence_after();
                 tmem_ld32(lane_addr + (buf ^ 1) * kTile, va);
             }
-            fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, pos_col, pos_t, m_run, s_run);
+            fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, m_run, s_run);
+            if (has_pos) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e)
+                    if (pos_d == 32 + e) pos_t = __uint_as_float(vb[e]);
+            }
         }
         // the positive logit, from the same MMA (same operand rounding) as the denominator
         if (pos_seen && row < M && row < row_begin + row_count) pos_t_out[row - row_begin] = pos_t;

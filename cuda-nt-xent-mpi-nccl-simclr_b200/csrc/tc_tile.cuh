@@ -21,9 +21,10 @@ constexpr float kFixedMaxLimit = 50.0f;     // fixed-max logsumexp while log2(e)
 #endif
 constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
 // the packed (f32x2) forward loops: of every 4 consecutive PAIRS of exponentials, this many take
-// the polynomial (2 = half of them: MUFU and issue slots then cost about the same per tile)
+// the polynomial.  Measured at 2N = 32768 x 128 (profiles/r2_fwd_poly_sweep.txt): 1 of 4 is the
+// fastest in both forward kernels.
 #ifndef NTX_FWD_POLY_PAIRS
-#define NTX_FWD_POLY_PAIRS 2
+#define NTX_FWD_POLY_PAIRS 1
 #endif
 constexpr int kFwdPolyPairs = NTX_FWD_POLY_PAIRS;
 
