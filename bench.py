@@ -63,8 +63,12 @@ def parse_args():
     ap.add_argument("--simt", action="store_true", help="force the fp32-FMA tile kernels")
     ap.add_argument("--bwd-mode", default="symmetric", choices=["symmetric", "contract"],
                     help="multi-GPU backward formulation")
-    ap.add_argument("--comm", default="symm", choices=["symm", "symm-barrier", "nccl"],
-                    help="multi-GPU exchange: kernels push into the peers' symmetric memory, or NCCL collectives")
+    ap.add_argument("--comm", default="push", choices=["push", "nccl", "torch"],
+                    help="multi-GPU exchange: 'push' = the C-ABI communicator, kernels store into the peers' "
+                         "buffers (flag-ordered, no collective); 'nccl' = the same communicator issuing NCCL "
+                         "collectives (all-gather U + all-gather l, or with --bwd-mode contract the "
+                         "reduce-scatter overlapped with the row pass); 'torch' = torch.distributed "
+                         "collectives around the C-ABI building blocks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-flush", action="store_true")
@@ -334,15 +338,18 @@ def run_native(args):
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent
         comm_used, comm_note = args.comm, None
+        if comm_used == "push" and args.bwd_mode == "contract":
+            comm_used = "nccl"  # the contract form is the NCCL exchange's
         try:
             engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
-                                          use_cuda_graph=graph_mode, comm=args.comm)
-        except Exception as exc:  # no peer mappings on this box: every rank fails the same rendezvous
-            if args.comm == "nccl":
+                                          use_cuda_graph=graph_mode, comm=comm_used)
+        except Exception as exc:  # no peer mappings on this box: every rank fails the same way
+            if comm_used == "torch":
                 raise
-            comm_used, comm_note = "nccl", f"{args.comm} unavailable: {type(exc).__name__}: {str(exc)[:120]}"
+            comm_note = f"{comm_used} unavailable: {type(exc).__name__}: {str(exc)[:120]}"
+            comm_used = "torch"
             engine = RowPartitionedNTXent(M, D, tau, tdtype, dev, backward_mode=args.bwd_mode, flags=flags,
-                                          use_cuda_graph=graph_mode, comm="nccl")
+                                          use_cuda_graph=graph_mode, comm="torch")
 
         def step(zin):
             return engine.forward_backward(zin)
@@ -497,7 +504,7 @@ def run_native(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         parity = {"dz_vs_1gpu_maxrel": float(t[0].item()), "loss_vs_1gpu_rel": float(t[1].item()),
                   "rows": M, "norm": "max over ranks of max|dz_shard - dz_1gpu| / max|dz_1gpu|",
-                  "timed_out_on_rank": engine.symm.timed_out_on() if engine.symm is not None else None}
+                  "timed_out_on_rank": engine.timed_out_on()}
         del zf, dz1
     lse_last = None
     if world == 1:

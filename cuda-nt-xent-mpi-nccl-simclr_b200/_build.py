@@ -170,7 +170,8 @@ def build_cpp_tools(force: bool = False):
         (os.path.join(REPO_DIR, "tests", "cpp", "test_ntxent_ops"),
          [os.path.join(REPO_DIR, "tests", "cpp", "test_ntxent_ops.cpp")],
          [os.path.join(REPO_DIR, "tests", "cpp", "mini_test.hpp")]),
-        (os.path.join(PKG_DIR, "ntxent_benchmark"), [os.path.join(CSRC, "benchmark.cpp")], []),
+        (os.path.join(PKG_DIR, "ntxent_benchmark"),
+         [os.path.join(CSRC, "benchmark.cpp"), os.path.join(CSRC, "dist_benchmark.cpp")], []),
     ]
     built = []
     for exe, srcs, extra_deps in targets:
@@ -187,7 +188,24 @@ def build_cpp_tools(force: bool = False):
             if r.returncode != 0:
                 raise RuntimeError(f"build of {exe} failed:\n" + r.stdout[-4000:])
         built.append(exe)
+    built.append(build_dist_benchmark(force))
     return built
+
+
+def build_dist_benchmark(force: bool = False) -> str:
+    """g++ -> ntxent_dist_benchmark: the multi-GPU C++ benchmark on the C-ABI alone (no torch)."""
+    build_library()
+    exe = os.path.join(PKG_DIR, "ntxent_dist_benchmark")
+    src = os.path.join(CSRC, "dist_benchmark.cpp")
+    if force or _stale(exe, [src, LIB_PATH, os.path.join(REPO_DIR, "include", "ntxent_b200.h")]):
+        cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-pthread", "-DNTXENT_DIST_BENCH_MAIN", "-I",
+               os.path.join(REPO_DIR, "include"), "-isystem", "/usr/local/cuda/include", src, "-o", exe,
+               "-L", PKG_DIR, "-lntxent_b200", "-L", "/usr/local/cuda/lib64", "-lcudart",
+               f"-Wl,-rpath,{PKG_DIR}", "-Wl,-rpath,$ORIGIN"]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("build of ntxent_dist_benchmark failed:\n" + r.stdout[-4000:])
+    return exe
 
 
 if __name__ == "__main__":

@@ -7,6 +7,9 @@
 // bf16 inputs and a JSON report.
 //
 //   ntxent_benchmark [--runs N] [--json FILE] [--quick]
+//   ntxent_benchmark --gpus N [--M ..] [--D ..] [--exchange push|nccl] [--bwd symmetric|contract] ...
+//       the row-partitioned step on N GPUs of this box through the C-ABI communicator
+//       (dist_benchmark.cpp; one process, one host thread per GPU)
 #include <ATen/cuda/CUDAContext.h>
 #include <cuda_runtime.h>
 #include <torch/torch.h>
@@ -96,7 +99,11 @@ void print_row(const Row& r) {
 
 }  // namespace
 
+int ntxent_dist_benchmark_main(int argc, char** argv);  // dist_benchmark.cpp
+
 int main(int argc, char** argv) {
+    for (int i = 1; i < argc; ++i)
+        if (!std::strcmp(argv[i], "--gpus")) return ntxent_dist_benchmark_main(argc, argv);
     int runs = 100;
     bool quick = false;
     std::string json_path;

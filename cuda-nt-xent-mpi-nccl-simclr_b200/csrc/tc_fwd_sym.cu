@@ -35,19 +35,8 @@ constexpr int kSymThreads = 320;  // warps 0..7 softmax, warp 8 TMA, warp 9 MMA
 constexpr int kSymTmaWarp = 8, kSymMmaWarp = 9;
 constexpr int kSymSoftmaxThreads = 256;
 
-// 16 TMEM lanes x 32 columns -> 16 registers: thread t holds rows t/4 (regs 4n, 4n+1) and
-// t/4 + 8 (regs 4n+2, 4n+3) of the 16, columns 8n + 2 (t%4) + {0, 1}, n = 0..3.
-__device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t* r) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x4.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
-          "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-}
-// 16 TMEM lanes x 16 columns -> 8 registers, same arrangement with n = 0..1.
+// 16 TMEM lanes x 16 columns -> 8 registers: thread t holds rows t/4 (regs 4n, 4n+1) and t/4 + 8
+// (regs 4n+2, 4n+3) of the 16, columns 8n + 2 (t%4) + {0, 1}, n = 0..1.
 __device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -55,32 +44,6 @@ __device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t* r) 
         : "r"(taddr)
         : "memory");
 }
-// One 32-row x 32-column block (this warp's lane quadrant, columns col..col+31) into v[0..31]:
-// v[16 h + 4 n + q]  =  row 16 h + 8 (q >> 1) + lane / 4,  column 8 n + 2 (lane % 4) + (q & 1).
-__device__ __forceinline__ void ld_block(uint32_t quad_addr, uint32_t col, uint32_t (&v)[32]) {
-    tmem_ld_16x256b_x4(quad_addr + col, &v[0]);
-    tmem_ld_16x256b_x4(quad_addr + (16u << 16) + col, &v[16]);
-}
-
-// Sum of c[idx] over the 8 lanes that share lane % 4, for idx = 4 b4 + 2 b3 + b2 (the lane's own
-// bits 4, 3, 2): a transposing butterfly, 7 shuffles for 8 values.
-__device__ __forceinline__ float colsum_butterfly(const float (&c)[8], int lane) {
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-    float k4[4], k2[2];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float send = b4 ? c[k] : c[4 + k], keep = b4 ? c[4 + k] : c[k];
-        k4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const float send = b3 ? k4[k] : k4[2 + k], keep = b3 ? k4[2 + k] : k4[k];
-        k2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-    const float send = b2 ? k2[0] : k2[1], keep = b2 ? k2[1] : k2[0];
-    return keep + __shfl_xor_sync(0xffffffffu, send, 4);
-}
-
 // Work items.  Rows i in [T - m L, T - (m-1) L) have between (m-1) L + 1 and m L tiles, i.e. m
 // chunks; items are numbered by descending m (ascending i), chunks of a row consecutively.
 struct SymItem {
@@ -240,114 +203,148 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
             const int p = row0 + 8 * g + N32;
             pos4[g] = p >= M32 ? p - M32 : p;
         }
-        const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-        // where this lane's finished column sum of a pair of 16-column blocks goes (see `store2`)
-        const int col_of_lane = (b2 ? 16 : 0) + (b4 ? 8 : 0) + cbase + (b3 ? 1 : 0);
-
-        // One 32-row x 16-column block: exponentials, row sums (packed, into rs2), and the column
-        // sums reduced over bits 4 and 3 of the lane number -- returned: the partial sum (still to be
-        // added over bit 2) of column 8 b4 + cbase + b3 of the block.
-        auto block = [&](const uint32_t (&v)[16], int jt, int blk, bool special) -> float {
-            float cs[4];
-            if (!special) {
-                // registers r, r+1 are one row's two neighbouring columns: one packed add each into
-                // the row pair and the column pair
-                f32x2 cs2[2] = {0ull, 0ull};
-#pragma unroll
-                for (int r = 0; r < 16; r += 2) {
-                    const f32x2 e = ex2_pair<kFwdPolyPairs>(v[r], v[r + 1], r >> 1);
-                    const int g = 2 * (r >> 3) + ((r >> 1) & 1);
-                    rs2[g] = add2(rs2[g], e);
-                    cs2[(r >> 2) & 1] = add2(cs2[(r >> 2) & 1], e);
-                }
-                unpack2(cs2[0], cs[0], cs[1]);
-                unpack2(cs2[1], cs[2], cs[3]);
-            } else {
-                const bool diag = jt == item.i;
-                const int c0 = jt * kTile + half * 64 + blk * 16 + cbase;
-                float rs[4] = {0.f, 0.f, 0.f, 0.f};
-                cs[0] = cs[1] = cs[2] = cs[3] = 0.f;
-#pragma unroll
-                for (int r = 0; r < 16; ++r) {
-                    const int g = 2 * (r >> 3) + ((r >> 1) & 1);
-                    const int row = row0 + 8 * g;
-                    const int col = c0 + 8 * ((r >> 2) & 1) + (r & 1);
-                    const float t = __uint_as_float(v[r]);
-                    const bool ok = col < M32 && col != row && row < M32;
-                    const float e = ok ? ex2(t) : 0.f;
-                    rs[g] += e;
-                    cs[2 * ((r >> 2) & 1) + (r & 1)] += e;
-                    // the positive logit, from the same MMA as the denominator; off the diagonal tile
-                    // the element (row, col) is also the positive logit of row `col`
-                    if (ok && col == pos4[g]) {
-                        pos_t_out[row] = t;
-                        if (!diag) pos_t_out[col] = t;
-                    }
-                }
-#pragma unroll
-                for (int g = 0; g < 4; ++g) rs2[g] = add2(rs2[g], pack2(rs[g], 0.f));
-            }
-            // cs[2 n + b] = this thread's sum (4 rows) of column 8 n + cbase + b: transpose-reduce over
-            // lane bit 4 (which n) and lane bit 3 (which b)
-            float k2[2];
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const float send = b4 ? cs[k] : cs[2 + k], keep = b4 ? cs[2 + k] : cs[k];
-                k2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-            }
-            const float send = b3 ? k2[0] : k2[1], keep = b3 ? k2[1] : k2[0];
-            return keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        // The column sums are transposed while they are reduced: at each of three levels a lane
+        // keeps one half of its values and hands the other half to its partner (lane ^ 16, 8, 4).
+        // Which half is a bit of the lane number; as all-ones / all-zeros words the choice is one
+        // LOP3 per value (a & m | b & ~m) with three registers held across the loop -- as predicates
+        // the compiler rebuilt them from the lane number in every block (seen in the ncu source view).
+        const uint32_t m4 = (lane & 16) ? 0xffffffffu : 0u, m3 = (lane & 8) ? 0xffffffffu : 0u,
+                       m2 = (lane & 4) ? 0xffffffffu : 0u;
+        auto pick = [](uint32_t m, float a, float b) {  // m ? a : b
+            return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
         };
-        // Two neighbouring blocks finish together: the last level (lane bit 2) hands block A's
-        // column to the lanes with b2 = 0 and block B's to those with b2 = 1 -- one shuffle, and the
-        // warp stores 32 finished column sums (one 128-byte line) of its quadrant.
-        auto store2 = [&](float pa, float pb, int jt, int pairno) {
-            if (jt == item.i) return;  // diagonal tile: its column sums are its row sums
-            const float send = b2 ? pa : pb, keep = b2 ? pb : pa;
-            const float s = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-            const int64_t pr = (int64_t)jt * (jt - 1) / 2 + item.i;
-            cpart[pr * 512 + quad * 128 + half * 64 + pairno * 32 + col_of_lane] = s;
+        // cs[2 n + b] = this thread's sum (4 rows) of column 8 n + cbase + b of a 16-column block ->
+        // the sum over lane bits 4 and 3 of column 8 b4 + cbase + b3 (bit 2 still to be added)
+        auto reduce43 = [&](const float (&cs)[4]) -> float {
+            const float k0 = pick(m4, cs[2], cs[0]) + __shfl_xor_sync(0xffffffffu, pick(m4, cs[0], cs[2]), 16);
+            const float k1 = pick(m4, cs[3], cs[1]) + __shfl_xor_sync(0xffffffffu, pick(m4, cs[1], cs[3]), 16);
+            return pick(m3, k1, k0) + __shfl_xor_sync(0xffffffffu, pick(m3, k0, k1), 8);
+        };
+        // Two neighbouring blocks finish together: the last level (lane bit 2) hands block A's column
+        // to the lanes with b2 = 0 and block B's to those with b2 = 1 -- one shuffle, and the warp
+        // stores 32 finished column sums (one 128-byte line) of its quadrant.
+        auto finish2 = [&](float pa, float pb) -> float {
+            return pick(m2, pb, pa) + __shfl_xor_sync(0xffffffffu, pick(m2, pa, pb), 4);
+        };
+        // this lane's slot in the 512 column partials of a tile pair: quadrant, column half, and
+        // column 16 b2 + 8 b4 + cbase + b3 of the 32 that a pair of blocks covers
+        const int col_of_lane = ((lane & 4) ? 16 : 0) + ((lane & 16) ? 8 : 0) + cbase + ((lane & 8) ? 1 : 0);
+        // cpart[(j (j-1)/2 + i) * 512 + ...] for the tile j of this iteration: kept as a pointer and
+        // advanced by j * 512 from one tile to the next (pair(j+1) - pair(j) = j)
+        float* cp = cpart + ((int64_t)item.j0 * (item.j0 - 1) / 2 + item.i) * 512 + quad * 128 + half * 64 +
+                    col_of_lane;
+
+        // One 32-row x 16-column block on the plain path: exponentials, row sums (packed, into rs2)
+        // and column sums of the thread's four rows.
+        auto block_fast = [&](const uint32_t (&v)[16]) -> float {
+            // registers r, r+1 are one row's two neighbouring columns: one packed add each into
+            // the row pair and the column pair
+            f32x2 cs2[2] = {0ull, 0ull};
+#pragma unroll
+            for (int r = 0; r < 16; r += 2) {
+                const f32x2 e = ex2_pair<kFwdPolyPairs>(v[r], v[r + 1], r >> 1);
+                const int g = 2 * (r >> 3) + ((r >> 1) & 1);
+                rs2[g] = add2(rs2[g], e);
+                cs2[(r >> 2) & 1] = add2(cs2[(r >> 2) & 1], e);
+            }
+            float cs[4];
+            unpack2(cs2[0], cs[0], cs[1]);
+            unpack2(cs2[1], cs[2], cs[3]);
+            return reduce43(cs);
+        };
+        // The same on the masked path (diagonal tile, ragged edge, the tiles with the positives).
+        auto block_slow = [&](const uint32_t (&v)[16], int jt, int blk) -> float {
+            const bool diag = jt == item.i;
+            const int c0 = jt * kTile + half * 64 + blk * 16 + cbase;
+            float rs[4] = {0.f, 0.f, 0.f, 0.f}, cs[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const int g = 2 * (r >> 3) + ((r >> 1) & 1);
+                const int row = row0 + 8 * g;
+                const int col = c0 + 8 * ((r >> 2) & 1) + (r & 1);
+                const float t = __uint_as_float(v[r]);
+                const bool ok = col < M32 && col != row && row < M32;
+                const float e = ok ? ex2(t) : 0.f;
+                rs[g] += e;
+                cs[2 * ((r >> 2) & 1) + (r & 1)] += e;
+                // the positive logit, from the same MMA as the denominator; off the diagonal tile
+                // the element (row, col) is also the positive logit of row `col`
+                if (ok && col == pos4[g]) {
+                    pos_t_out[row] = t;
+                    if (!diag) pos_t_out[col] = t;
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < 4; ++g) rs2[g] = add2(rs2[g], pack2(rs[g], 0.f));
+            return reduce43(cs);
         };
         auto ld_blk = [&](uint32_t col, uint32_t (&v)[16]) {
             tmem_ld_16x256b_x2(quad_addr + col, &v[0]);
             tmem_ld_16x256b_x2(quad_addr + (16u << 16) + col, &v[8]);
         };
-
-        // four 16-column blocks per tile, double-buffered in registers: the load of the next block
-        // (or of the next tile's first block) is in flight while the current one is exponentiated
-        uint32_t va[16], vb[16];
-        mbar_wait(&s_full[0], 0);
-        tc_fence_after();
-        ld_blk(0, va);
-        for (int it = 0; it < n_tiles; ++it) {
+        // the S buffer has been read out by this warp: hand it back and fetch the first block of the
+        // next tile
+        auto release_and_prefetch = [&](int it, uint32_t (&v)[16]) {
             const int buf = it & 1;
-            const int jt = item.j0 + it;
-            const int hj = 2 * jt + half;
-            const bool special = jt == item.i || hj >= hj_ragged || (hj >= hj_pos_lo && hj <= hj_pos_hi) ||
-                                 hj <= hj_wrap_hi;
-            const uint32_t tcol = buf * kTile;
-            tmem_ld_wait();
-            ld_blk(tcol + 16, vb);
-            float pa = block(va, jt, 0, special);
-            tmem_ld_wait();
-            ld_blk(tcol + 32, va);
-            float pb = block(vb, jt, 1, special);
-            store2(pa, pb, jt, 0);
-            tmem_ld_wait();
-            ld_blk(tcol + 48, vb);
-            pa = block(va, jt, 2, special);
-            tmem_ld_wait();
-            // this warp's S columns have left TMEM: hand the buffer back, then prefetch
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[buf]);
             if (it + 1 < n_tiles) {
                 mbar_wait(&s_full[buf ^ 1], ((it + 1) >> 1) & 1);
                 tc_fence_after();
-                ld_blk((buf ^ 1) * kTile, va);
+                ld_blk((buf ^ 1) * kTile, v);
             }
-            pb = block(vb, jt, 3, special);
-            store2(pa, pb, jt, 1);
+        };
+
+        // four 16-column blocks per tile, double-buffered in registers: the load of the next block
+        // (or of the next tile's first block) is in flight while the current one is exponentiated.
+        // ONE branch per tile separates the plain path from the masked one.
+        uint32_t va[16], vb[16];
+        mbar_wait(&s_full[0], 0);
+        tc_fence_after();
+        ld_blk(0, va);
+        for (int it = 0; it < n_tiles; ++it) {
+            const int jt = item.j0 + it;
+            const int hj = 2 * jt + half;
+            const bool special = jt == item.i || hj >= hj_ragged || (hj >= hj_pos_lo && hj <= hj_pos_hi) ||
+                                 hj <= hj_wrap_hi;
+            const uint32_t tcol = (it & 1) * kTile;
+            if (!special) {
+                tmem_ld_wait();
+                ld_blk(tcol + 16, vb);
+                float pa = block_fast(va);
+                tmem_ld_wait();
+                ld_blk(tcol + 32, va);
+                float pb = block_fast(vb);
+                cp[0] = finish2(pa, pb);
+                tmem_ld_wait();
+                ld_blk(tcol + 48, vb);
+                pa = block_fast(va);
+                tmem_ld_wait();
+                release_and_prefetch(it, va);
+                pb = block_fast(vb);
+                cp[32] = finish2(pa, pb);
+            } else {
+                // (rare: no double buffering, the blocks one after the other)
+                float pa = 0.f;
+                tmem_ld_wait();
+#pragma unroll 1
+                for (int blk = 0; blk < 4; ++blk) {
+                    if (blk > 0) {
+                        ld_blk(tcol + 16 * blk, va);
+                        tmem_ld_wait();
+                    }
+                    const float pv = block_slow(va, jt, blk);
+                    if (blk & 1) {
+                        const float sum = finish2(pa, pv);
+                        if (jt != item.i) cp[(blk >> 1) * 32] = sum;  // (a diagonal tile's column sums are its row sums)
+                    } else {
+                        pa = pv;
+                    }
+                }
+                release_and_prefetch(it, va);
+            }
+            cp += (int64_t)jt * 512;
         }
         // row sums: over the four lanes that share the rows, then the two column halves through
         // shared memory (the row tile is no longer needed: every MMA that read it has completed)

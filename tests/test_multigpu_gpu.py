@@ -38,51 +38,56 @@ def _worker(rank, world, port, M, D, tau, mode, dtype_name, out_dir):
         z = torch.from_numpy(seeded_z(M, D, seed=5)).to(dtype)
         rows = M // world
         shard = z[rank * rows:(rank + 1) * rows].cuda()
-        eng = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode)
+        dev = torch.device("cuda", rank)
+        # the Python-level orchestration over torch.distributed collectives (the baseline) ...
+        eng = RowPartitionedNTXent(M, D, tau, dtype, dev, backward_mode=mode, comm="torch")
         loss, dz = eng.forward_backward(shard)
         zr = shard.clone().requires_grad_(True)
         l2 = distributed_ntxent_loss(zr, tau, engine=eng)
         l2.backward()
         torch.cuda.synchronize()
-        # the CUDA-graph replay of the same step must reproduce the eager result bit for bit
-        eng_g = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
-                                     use_cuda_graph=True)
+        # ... whose CUDA-graph replay must reproduce the eager result bit for bit
+        eng_g = RowPartitionedNTXent(M, D, tau, dtype, dev, backward_mode=mode, comm="torch", use_cuda_graph=True)
         for _ in range(2):
             loss_g, dz_g = eng_g.forward_backward(shard)
         torch.cuda.synchronize()
         same = torch.equal(loss_g, loss) and torch.equal(dz_g, dz)
         eng_g.release()
         assert same
-        # peer-memory exchange (kernels store into every rank's symmetric buffers, no NCCL
-        # all-gather / all-reduce): same numbers as the NCCL path, over several steps so that
-        # both rotating buffer sets are used
-        eng_s = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
-                                     comm="symm")
-        for _ in range(3):
-            loss_s, dz_s = eng_s.forward_backward(shard)
-        torch.cuda.synchronize()
-        # (the symmetric form applies the normalisation Jacobian inside the backward epilogue
-        # there, so dz agrees to rounding rather than bit for bit)
+        # the C-ABI communicator: kernels push into the peers' buffers (symmetric form), or NCCL
+        # collectives with the reduce-scatter overlapped (contract form): same numbers as the baseline,
+        # over several steps so that both rotating buffer sets are used
         tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
-        assert torch.allclose(loss_s, loss, rtol=1e-6)
-        assert (dz_s.float() - dz.float()).abs().max() <= tol * dz.float().abs().max()
-        # forward-only + separate backward through the autograd wrapper on the same engine
-        zs = shard.clone().requires_grad_(True)
-        ls = distributed_ntxent_loss(zs, tau, engine=eng_s)
-        ls.backward()
-        torch.cuda.synchronize()
-        assert torch.allclose(ls.detach().reshape(1), loss.reshape(1), rtol=1e-6)
-        assert torch.equal(zs.grad, dz_s)
-        # and its graph replay (one graph per buffer set), bit for bit over several steps
-        eng_sg = RowPartitionedNTXent(M, D, tau, dtype, torch.device("cuda", rank), backward_mode=mode,
-                                      comm="symm", use_cuda_graph=True)
-        same = True
-        for _ in range(5):
-            loss_sg, dz_sg = eng_sg.forward_backward(shard)
+        for comm in (["push", "nccl"] if mode == "symmetric" else ["nccl"]):
+            eng_c = RowPartitionedNTXent(M, D, tau, dtype, dev, backward_mode=mode, comm=comm)
+            for _ in range(3):
+                loss_c, dz_c = eng_c.forward_backward(shard)
             torch.cuda.synchronize()
-            same = same and torch.equal(loss_sg, loss_s) and torch.equal(dz_sg, dz_s)
-        eng_sg.release()
-        assert same
+            loss_c, dz_c = loss_c.clone(), dz_c.clone()
+            assert torch.allclose(loss_c, loss, rtol=1e-6), comm
+            assert (dz_c.float() - dz.float()).abs().max() <= tol * dz.float().abs().max(), comm
+            # through the autograd wrapper on the same engine
+            zs = shard.clone().requires_grad_(True)
+            ls = distributed_ntxent_loss(zs, tau, engine=eng_c)
+            (ls * 2.0).backward()
+            torch.cuda.synchronize()
+            assert torch.allclose(ls.detach().reshape(1), loss.reshape(1), rtol=1e-6), comm
+            assert torch.equal(zs.grad, (dz_c.float() * 2.0).to(dz_c.dtype)), comm
+            # and its graph replay (one graph per buffer set), bit for bit over several steps,
+            # switching between eager and replayed steps on one engine
+            eng_c.use_cuda_graph = True
+            same = True
+            for _ in range(5):
+                loss_g, dz_g = eng_c.forward_backward(shard)
+                torch.cuda.synchronize()
+                same = same and torch.equal(loss_g, loss_c) and torch.equal(dz_g, dz_c)
+            eng_c.use_cuda_graph = False
+            loss_e, dz_e = eng_c.forward_backward(shard)  # an odd number of replays, then eager again
+            torch.cuda.synchronize()
+            same = same and torch.equal(loss_e, loss_c) and torch.equal(dz_e, dz_c)
+            assert eng_c.timed_out_on() is None
+            eng_c.release()
+            assert same, comm
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), loss=loss.float().cpu().numpy(),
                  dz=dz.float().cpu().numpy(), dz_ag=zr.grad.float().cpu().numpy())
     finally:
