@@ -110,8 +110,22 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     pdl_trigger();
 
     const int64_t a0 = row_begin + (int64_t)blockIdx.x * kTile;
-    const int jt0 = blockIdx.y * tiles_per_split;
-    const int n_tiles = min(tiles_per_split, col_tiles - jt0);
+    // Which column tiles this CTA (row tile x, split y of gridDim.y) walks, and in which order:
+    //   single device     : the contiguous range [y * tiles_per_split, ...)
+    //   peers push U       : every gridDim.y-th tile, counted from the first tile of THIS rank's own
+    //                        rows (which need no waiting) on through the ranks behind it, wrapping
+    //                        around: every CTA starts on rows that are there already and meets the
+    //                        peers' rows as late as possible, one rank after the other.
+    const bool rotated = u_ready.flags != nullptr;
+    const int rot = rotated ? (int)((row_begin / kTile) % col_tiles) : 0;
+    const int jt0 = rotated ? (rot + (int)blockIdx.y) % col_tiles : (int)blockIdx.y * tiles_per_split;
+    const int jt_step = rotated ? (int)gridDim.y : 1;
+    const int n_tiles = rotated ? (col_tiles - (int)blockIdx.y + jt_step - 1) / jt_step
+                                : min(tiles_per_split, col_tiles - jt0);
+    auto next_tile = [&](int jt) {  // (jt + jt_step) mod col_tiles; jt_step <= col_tiles
+        jt += jt_step;
+        return jt >= col_tiles ? jt - col_tiles : jt;
+    };
 
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmap);
@@ -149,16 +163,16 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
             mbar_arrive_expect_tx(q_full, C::kTileBytes);
             for (int a = 0; a < C::kAtoms; ++a)
                 tma_load_2d(q_tile + a * kAtomBytes, &tmap, q_full, a * C::kAtomCols, (int32_t)a0);
-            for (int it = 0; it < n_tiles; ++it) {
+            for (int it = 0, jt = jt0; it < n_tiles; ++it, jt = next_tile(jt)) {
                 const int st = it % NS;
                 const uint32_t ph = (it / NS) & 1;
-                const int64_t c0 = (int64_t)(jt0 + it) * kTile;
+                const int64_t c0 = (int64_t)jt * kTile;
                 wait_rows(c0, min(M, c0 + kTile));
                 mbar_wait(&k_empty[st], ph ^ 1);
                 mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                 for (int a = 0; a < C::kAtoms; ++a)
                     tma_load_2d(k_tiles + st * C::kTileBytes + a * kAtomBytes, &tmap, &k_full[st],
-                                a * C::kAtomCols, (jt0 + it) * kTile);
+                                a * C::kAtomCols, jt * kTile);
             }
         }
         __syncwarp();
@@ -244,13 +258,18 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 #ifdef NTX_FWD_NOPOS  // A/B build: no capture here, the finalize kernel forms the dot products
         const bool pos_seen = false;
 #else
-        const bool pos_seen = (pos_hj & 1) == half && (pos_hj >> 1) >= jt0 && (pos_hj >> 1) < jt0 + n_tiles;
+        // (the rotated walk covers the tiles whose number counted from `rot` is y, y + S, y + 2 S, ...)
+        const int pos_jt = pos_hj >> 1;
+        const int pos_v = pos_jt >= rot ? pos_jt - rot : pos_jt - rot + col_tiles;
+        const bool pos_in_walk = rotated ? (pos_v >= (int)blockIdx.y && (pos_v - (int)blockIdx.y) % jt_step == 0)
+                                         : (pos_jt >= jt0 && pos_jt < jt0 + n_tiles);
+        const bool pos_seen = (pos_hj & 1) == half && pos_in_walk;
 #endif
         const int pos_col32 = (int)pos_col;
         float pos_t = 0.f;
-        for (int it = 0; it < n_tiles; ++it) {
+        for (int it = 0, jt = jt0; it < n_tiles; ++it, jt = next_tile(jt)) {
             const int buf = it & 1;
-            const int hj = 2 * (jt0 + it) + half;
+            const int hj = 2 * jt + half;
             const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged;
             // the half tile(s) that hold this warp's positives: pick the logit out of the registers
             // (a rare branch of its own: it must not sit in the exponential loops)
@@ -369,6 +388,27 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
                                              const float* __restrict__ cc, float k_scale, float row_c,
                                              int64_t col0, int64_t row, int64_t b_end) {
     static_assert(NOUT == (kPacked ? 16 : 32), "output size");
+#ifndef NTX_BWD_UNPACKED  // (A/B build switch)
+    if (MODE == kSym && !kTwoExp && !kSpecial && kBwdPoly == 0) {
+        // the common case, on packed pairs: 2^t (2^-l_a + 2^-l_b) as one FADD2 + one FMUL2 per two
+        // weights instead of two FADD + two FMUL
+        const f32x2 rc2 = pack2(row_c, row_c);
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+            const f32x2 sum = add2(rc2, pack2(cc[e], cc[e + 1]));
+            const f32x2 x = mul2(pack2(ex2(__uint_as_float(v[e])), ex2(__uint_as_float(v[e + 1]))), sum);
+            float w0, w1;
+            unpack2(x, w0, w1);
+            if (kPacked) {
+                packed[e >> 1] = pack_bf16(w0, w1);
+            } else {
+                packed[e] = to_tf32(w0);
+                packed[e + 1] = to_tf32(w1);
+            }
+        }
+        return;
+    }
+#endif
 #pragma unroll
     for (int e = 0; e < 32; e += 2) {
         float w[2];

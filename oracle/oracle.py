@@ -55,6 +55,11 @@ def lib() -> ctypes.CDLL:
         L.ntxent_oracle_rowblock_f32.argtypes = [fp, i64, i64, ctypes.c_float, i64, i64,
                                                  fp, fp, fp, fp]
         L.ntxent_oracle_rowblock_f32.restype = ctypes.c_int
+        ip64 = ctypes.POINTER(ctypes.c_int64)
+        L.ntxent_oracle_forward_pos_f64.argtypes = [dp, ip64, i64, i64, ctypes.c_double, dp, dp]
+        L.ntxent_oracle_forward_pos_f64.restype = ctypes.c_int
+        L.ntxent_oracle_backward_pos_f64.argtypes = [dp, ip64, dp, ctypes.c_double, i64, i64, ctypes.c_double, dp]
+        L.ntxent_oracle_backward_pos_f64.restype = ctypes.c_int
         L.ntxent_literal_reference_forward_f64.argtypes = [dp, i64, i64, ctypes.c_double, dp]
         L.ntxent_literal_reference_forward_f64.restype = ctypes.c_int
         _lib = L
@@ -125,6 +130,23 @@ def forward_backward(z, tau: float, grad_out: float = 1.0):
     return loss, lse, dz
 
 
+def forward_backward_pos(z, pos, tau: float, grad_out: float = 1.0):
+    """fp64 loss / l / dz with the positive of row i given by pos[i].
+    Returns (loss, lse[M], dz[M,D])."""
+    z = np.ascontiguousarray(z, dtype=np.float64)
+    pos = np.ascontiguousarray(pos, dtype=np.int64)
+    M, D = z.shape
+    loss, lse, dz = np.zeros(1), np.zeros(M), np.zeros((M, D))
+    ip = pos.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))
+    rc = lib().ntxent_oracle_forward_pos_f64(_dptr(z), ip, M, D, float(tau), _dptr(loss), _dptr(lse))
+    if rc == 0:
+        rc = lib().ntxent_oracle_backward_pos_f64(_dptr(z), ip, _dptr(lse), float(grad_out), M, D, float(tau),
+                                                  _dptr(dz))
+    if rc != 0:
+        raise ValueError(f"ntxent_oracle_*_pos_f64 rc={rc}")
+    return float(loss[0]), lse, dz
+
+
 def rowblock_f32(z, tau: float, row_begin: int, row_count: int):
     """fp32/OpenMP row-block contract form (the timed CPU baseline).
 
@@ -158,18 +180,19 @@ def literal_reference_forward(z, T: float) -> float:
 # --------------------------------------------------------------------------
 # Independent numpy restatement (dense, fp64, small cases only).
 # --------------------------------------------------------------------------
-def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e-12):
+def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e-12, pos=None):
     """Dense numpy fp64 NT-Xent.  Returns dict(loss, lse, dz, dU, pos_prob, dtau, ...); dtau is
-    d loss / d tau = -(1/tau) sum_ij G_ij S_ij."""
+    d loss / d tau = -(1/tau) sum_ij G_ij S_ij.  `pos`: the positive of
+    every row as an index vector (default (i + N) mod M)."""
     z = np.asarray(z, dtype=np.float64)
     M, D = z.shape
-    assert M % 2 == 0
+    assert M % 2 == 0 or pos is not None
     N = M // 2
     nrm = np.maximum(np.linalg.norm(z, axis=1, keepdims=True), eps)
     u = z / nrm
     S = (u @ u.T) / tau
     idx = np.arange(M)
-    pos = (idx + N) % M
+    pos = (idx + N) % M if pos is None else np.asarray(pos, dtype=np.int64)
     Sm = S.copy()
     Sm[idx, idx] = -np.inf
     mx = Sm.max(axis=1, keepdims=True)

@@ -20,14 +20,14 @@ def _tools():
 
 
 def test_cpp_operator_tests():
-    exe, _ = _tools()
+    exe = _tools()[0]
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "7 of 7 tests passed" in r.stdout
 
 
 def test_cpp_benchmark_quick(tmp_path):
-    _, bench = _tools()
+    bench = _tools()[1]
     out = tmp_path / "bench.json"
     r = subprocess.run([bench, "--quick", "--runs", "10", "--json", str(out)], capture_output=True, text=True,
                        timeout=300)
@@ -36,6 +36,19 @@ def test_cpp_benchmark_quick(tmp_path):
     assert len(rows) >= 6 and all(row["fwd_ms_mean"] > 0 and row["tflops"] > 0 for row in rows)
     big = [row for row in rows if row["rows"] == 32768][0]
     assert big["tflops"] > 100  # the tcgen05 path, not a fallback
+
+
+def test_cpp_dist_benchmark_one_gpu():
+    """The multi-GPU C++ benchmark (C-ABI communicator, no torch) at --gpus 1: every exchange form,
+    directly and through `ntxent_benchmark --gpus`."""
+    tools = _tools()
+    for exe, extra in ((tools[2], []), (tools[1], []), (tools[2], ["--exchange", "nccl", "--bwd", "contract"])):
+        r = subprocess.run([exe, "--gpus", "1", "--M", "4096", "--steps", "5", "--warmup", "2", *extra],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        d = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+        assert d["gpus"] == 1 and d["ms_mean"] > 0 and d["loss_same_on_all_ranks"] is True
+        assert abs(d["loss"] - 8.7) < 1.0  # ~ ln(4096) + O(1)
 
 
 def test_python_operator_sweep(tmp_path):

@@ -181,3 +181,30 @@ def test_bad_arguments(oracle):
         oracle.forward(np.zeros((3, 4)), 0.5)  # odd M
     with pytest.raises(ValueError):
         oracle.forward(np.zeros((4, 4)), 0.0)  # tau <= 0
+
+
+# ------------------------------------------------ arbitrary positives
+def test_arbitrary_positives_c_against_numpy_and_finite_differences(oracle):
+    rng = np.random.default_rng(3)
+    M, D, tau = 24, 8, 0.3
+    z = rng.standard_normal((M, D))
+    pos = np.array([(i + 5) % M for i in range(M)])
+    pos[3] = pos[9] = 7  # not an involution, and two rows share a positive
+    loss, lse, dz = oracle.forward_backward_pos(z, pos, tau, 1.5)
+    ref = oracle.numpy_forward_backward(z, tau, 1.5, pos=pos)
+    assert loss == pytest.approx(ref["loss"], rel=1e-12)
+    np.testing.assert_allclose(dz, ref["dz"], rtol=0, atol=1e-13)
+    # the default positives are the canonical NT-Xent
+    l2, _, dz2 = oracle.forward_backward_pos(z, (np.arange(M) + M // 2) % M, tau, 1.5)
+    l3, _, dz3 = oracle.forward_backward(z, tau, 1.5)
+    assert l2 == pytest.approx(l3, rel=1e-14)
+    np.testing.assert_allclose(dz2, dz3, rtol=0, atol=1e-14)
+    eps = 1e-6
+    for i, k in ((0, 0), (3, 2), (7, 5), (9, 1)):
+        zp, zm = z.copy(), z.copy()
+        zp[i, k] += eps
+        zm[i, k] -= eps
+        fd = (oracle.forward_backward_pos(zp, pos, tau)[0] - oracle.forward_backward_pos(zm, pos, tau)[0]) / (2 * eps)
+        assert 1.5 * fd == pytest.approx(dz[i, k], abs=1e-8)
+    with pytest.raises(ValueError):
+        oracle.forward_backward_pos(z, np.arange(M), tau)  # a row cannot be its own positive
