@@ -31,7 +31,7 @@ EXPORTS = [
     "ntxent_b200_set_peer_wait_timeout_ms", "ntxent_b200_backward_rows_part",
     "ntxent_b200_comm_init_all", "ntxent_b200_comm_unique_id", "ntxent_b200_comm_init_rank",
     "ntxent_b200_comm_destroy", "ntxent_b200_comm_info", "ntxent_b200_comm_status",
-    "ntxent_b200_dist_forward_backward",
+    "ntxent_b200_dist_forward_backward", "ntxent_b200_forward_backward_pos",
 ]
 EXCHANGE_PUSH, EXCHANGE_NCCL = 0, 1
 
@@ -156,6 +156,9 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_comm_status.argtypes = [vp]
     L.ntxent_b200_dist_forward_backward.restype = ci
     L.ntxent_b200_dist_forward_backward.argtypes = [vp, vp, vp, f32, ci, ci, vp, vp, vp]
+    L.ntxent_b200_forward_backward_pos.restype = ci
+    L.ntxent_b200_forward_backward_pos.argtypes = [vp, vp, vp, vp, vp, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
+                                                   vp]
     L.ntxent_b200_debug_set_trace.restype = ci
     L.ntxent_b200_debug_set_trace.argtypes = [vp]
     L.ntxent_b200_forward_static.restype = ci
@@ -309,6 +312,44 @@ def forward_backward(z: torch.Tensor, tau: float, grad_out: torch.Tensor | None 
         check(lib().ntxent_b200_forward_backward(_ptr(z), _ptr(grad_out), M, D, float(tau),
                                                  _dtype_code(z), fl, _ptr(ws), ws.numel(), _ptr(loss),
                                                  _ptr(lse), _ptr(dz), None, _stream()))
+    return loss, lse, dz
+
+
+def inverse_positives(pos: torch.Tensor):
+    """pos int[M] -> (pos int32, inv_ptr int32[M+1], inv_idx int32[M]): inv_idx[inv_ptr[a]:inv_ptr[a+1]]
+    are the rows whose positive is row a (stable order, so the gradient is reproducible)."""
+    M = pos.numel()
+    pos64 = pos.reshape(-1).to(torch.int64)
+    if M and (int(pos64.min()) < 0 or int(pos64.max()) >= M or bool((pos64 == torch.arange(M, device=pos.device)).any())):
+        raise NTXentError("positives must be row indices in [0, M) and no row may be its own positive")
+    inv_idx = torch.argsort(pos64, stable=True).to(torch.int32)
+    inv_ptr = torch.zeros(M + 1, dtype=torch.int64, device=pos.device)
+    inv_ptr[1:] = torch.cumsum(torch.bincount(pos64, minlength=M), 0)
+    return pos64.to(torch.int32).contiguous(), inv_ptr.to(torch.int32).contiguous(), inv_idx.contiguous()
+
+
+def forward_backward_pos(z: torch.Tensor, pos_lists, tau: float, grad_out: torch.Tensor | None = None,
+                         use_mixed_precision: bool = False, flags: int = 0, ws: torch.Tensor | None = None,
+                         want_dz: bool = True):
+    """NT-Xent whose positives come from an index vector (ntxent_b200_forward_backward_pos).
+    pos_lists = inverse_positives(pos).  -> (loss[1], lse[M], dz[M,D] or None)."""
+    _require_cuda(z, grad_out, *pos_lists)
+    z = z.contiguous()
+    M, D = z.shape
+    pos, inv_ptr, inv_idx = pos_lists
+    if pos.numel() != M:
+        raise NTXentError(f"need one positive per row: {pos.numel()} indices for {M} rows")
+    if grad_out is not None:
+        grad_out = grad_out.reshape(-1)[:1].contiguous().float()
+    fl = _flags(use_mixed_precision, flags)
+    with torch.cuda.device(z.device):
+        ws = workspace(M, D, z, fl) if ws is None else ws
+        loss = torch.empty(1, dtype=torch.float32, device=z.device)
+        lse = torch.empty(M, dtype=torch.float32, device=z.device)
+        dz = torch.empty_like(z) if want_dz else None
+        check(lib().ntxent_b200_forward_backward_pos(_ptr(z), _ptr(pos), _ptr(inv_ptr), _ptr(inv_idx), _ptr(grad_out),
+                                                     M, D, float(tau), _dtype_code(z), fl, _ptr(ws), ws.numel(),
+                                                     _ptr(loss), _ptr(lse), _ptr(dz), _stream()))
     return loss, lse, dz
 
 

@@ -242,7 +242,7 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                           int64_t row_count, float tau, const Plans& p, const RowsWs& w,
                           const PeerList& lse_outs, int64_t lse_offset, const PeerList& loss_outs,
                           int loss_index, float loss_scale, const PeerWait& u_ready,
-                          const PeerSignal& lse_signal, cudaStream_t st) {
+                          const PeerSignal& lse_signal, cudaStream_t st, const int* pos_index = nullptr) {
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
@@ -251,6 +251,14 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, u_ready, st));
     g_timer.stop(0, st);
+    if (pos_index) {  // positives from an index vector (whole-batch calls only): their logits, over
+                      // whatever the tile kernel captured for the default positives
+        NTX_TRY(launch_pos_dot(u_all, op_bf16, M, D, pos_index, kLog2e / tau, w.pos_t, st));
+        NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
+                                         w.part_s, w.pos_t, lse_outs, lse_offset, w.block_partials, loss_outs,
+                                         loss_index, loss_scale, lse_signal, st));
+        return NTXENT_OK;
+    }
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
 #ifdef NTX_FWD_NOPOS
                                      w.part_m, w.part_s, nullptr, lse_outs, lse_offset,
@@ -263,21 +271,24 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
 
 int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                      int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
-                     float* loss_out, float loss_scale, cudaStream_t st) {
+                     float* loss_out, float loss_scale, cudaStream_t st, const int* pos_index = nullptr) {
     return run_forward_rows_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p, w,
                                  single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, no_wait(),
-                                 no_signal(), st);
+                                 no_signal(), st, pos_index);
 }
 
 // Forward of the whole batch on one device: over the upper triangle where that applies
 // (tc_fwd_sym.cu), else the row-block path with the full range.
 int run_forward_device(const void* U, bool op_bf16, int64_t M, int64_t D, float tau, const Plans& p,
-                       const RowsWs& w, float* lse_out, float* loss_out, cudaStream_t st) {
+                       const RowsWs& w, float* lse_out, float* loss_out, cudaStream_t st,
+                       const int* pos_index = nullptr) {
     if (!p.sym)
-        return run_forward_rows(U, op_bf16, M, D, 0, M, tau, p, w, lse_out, loss_out, 1.0f / (float)M, st);
+        return run_forward_rows(U, op_bf16, M, D, 0, M, tau, p, w, lse_out, loss_out, 1.0f / (float)M, st,
+                                pos_index);
     g_timer.start(0, st);
     NTX_TRY(tc_launch_fwd_sym(U, M, D, tau, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, st));
     g_timer.stop(0, st);
+    if (pos_index) NTX_TRY(launch_pos_dot(U, op_bf16, M, D, pos_index, kLog2e / tau, w.pos_t, st));
     NTX_TRY(tc_launch_fwd_sym_finalize(M, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, lse_out, w.block_partials,
                                        st));
     NTX_TRY(launch_loss_reduce(w.block_partials, p.symp.T, single_peer(loss_out), 0, 1.0f / (float)M, no_signal(),
@@ -382,7 +393,8 @@ int run_bwd_col_term(const void* u_all, bool opb, const float* lse_all, int64_t 
 int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_bf16, const float* lse,
                         const float* grad_out, int64_t M, int64_t D, float tau, const Plans& p,
                         void* dz_out, float* pos_prob_out, cudaStream_t st,
-                        float* tau_grad_rows_out = nullptr) {
+                        float* tau_grad_rows_out = nullptr, const int* pos_index = nullptr,
+                        const int* inv_ptr = nullptr, const int* inv_idx = nullptr) {
     int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows,
                            w.rows.acc_rows, w.rows.ut, st);
     if (rc != NTXENT_OK) return rc;
@@ -397,6 +409,7 @@ int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_b
     e.grad_out = grad_out; e.dz_out = dz_out;
     e.lse_all = lse; e.inv_tau = 1.0f / tau; e.pos_prob_out = pos_prob_out;
     e.tau_grad_rows_out = tau_grad_rows_out;
+    e.pos_index = pos_index; e.inv_ptr = inv_ptr; e.inv_idx = inv_idx;
     NTX_TRY(launch_bwd_epilogue(e, st));
     return NTXENT_OK;
 }
@@ -686,6 +699,28 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     if (rc != NTXENT_OK) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p,
                                dz_out, pos_prob_out, stream);
+}
+
+int ntxent_b200_forward_backward_pos(const void* z, const int32_t* pos, const int32_t* inv_ptr,
+                                     const int32_t* inv_idx, const float* grad_out, int64_t M, int64_t D,
+                                     float tau, int dtype, unsigned flags, void* workspace,
+                                     size_t workspace_bytes, float* loss_out, float* lse_out, void* dz_out,
+                                     ntxent_stream_t stream) {
+    if (!z || !pos || !workspace || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (dz_out && (!inv_ptr || !inv_idx)) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
+    int rc = check_shape(M, D, tau, dtype);
+    if (rc != NTXENT_OK) return rc;
+    const bool opb = op_is_bf16(dtype, flags);
+    const Plans p = make_plans(M, D, M, opb, flags, tau);
+    const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
+    if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
+    if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream, pos);
+    if (rc != NTXENT_OK || !dz_out) return rc;
+    return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p, dz_out, nullptr,
+                               stream, nullptr, pos, inv_ptr, inv_idx);
 }
 
 int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t row_begin,

@@ -114,6 +114,11 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
 cudaError_t launch_loss_reduce(const float* block_partials, int n, const PeerList& loss_outs, int loss_index,
                                float loss_scale, const PeerSignal& signal, cudaStream_t stream);
 
+// pos_t[i] = (log2(e)/tau) u_i . u_pos[i] for positives given by an index vector (fp32 dot of the
+// operand rows): what the tile kernels capture themselves for the default positives.
+cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, const int* pos_index,
+                           float k_scale, float* pos_t, cudaStream_t stream);
+
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b
     int nsplit;
@@ -136,6 +141,12 @@ struct BwdEpilogueArgs {
     const float* lse_all;    // [M] (needed only with pos_prob_out)
     float inv_tau;
     float* pos_prob_out;     // [a_count] or nullptr
+    // optional: positives from an index vector instead of (a + M/2) mod M.  pos_index[a] is row a's
+    // positive; rows b with pos_index[b] == a are inv_idx[inv_ptr[a] .. inv_ptr[a+1]).  The term
+    // subtracted from row a is then u_pos[a] + sum of those u_b (pos_coeff / pos_lo / pos_hi unused).
+    const int* pos_index;
+    const int* inv_ptr;
+    const int* inv_idx;
     // optional per-row temperature gradient (output B only): -(dU_a . u_a) / (2 tau); its sum
     // over all rows, times grad_out, is d loss / d tau
     float* tau_grad_rows_out;  // [a_count] or nullptr

@@ -211,6 +211,9 @@ struct BwdEpiDev {
     float inv_tau;
     float* pos_prob_out;
     float* tau_grad_rows_out;
+    const int* pos_index;
+    const int* inv_ptr;
+    const int* inv_idx;
 };
 
 // A warp owns kRows rows of kChunks x 128 columns each and issues the loads of all of them
@@ -236,8 +239,8 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
     for (int q = 0; q < kRows; ++q) {
         const int64_t r = min(r0 + q, p.a_count - 1);  // rows past the end redo the last row, unstored
         const int64_t row = p.a_begin + r;
-        pos[q] = (row + p.M / 2) % p.M;
-        pc[q] = (pos[q] >= p.pos_lo && pos[q] < p.pos_hi) ? p.pos_coeff : 0.f;
+        pos[q] = p.pos_index ? (int64_t)p.pos_index[row] : (row + p.M / 2) % p.M;
+        pc[q] = p.pos_index ? 1.f : ((pos[q] >= p.pos_lo && pos[q] < p.pos_hi) ? p.pos_coeff : 0.f);
         inv[q] = jac ? p.inv_norm[r] : 0.f;
 #pragma unroll
         for (int c = 0; c < kChunks; ++c) {
@@ -249,6 +252,24 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
                 if (pc[q] != 0.f) {
                     const float4 u = Elem<TOp>::ld4(U + pos[q] * D + k);
                     du[q][c] = make_float4(-pc[q] * u.x, -pc[q] * u.y, -pc[q] * u.z, -pc[q] * u.w);
+                }
+            }
+        }
+    }
+    // positives from an index vector: the rows that name this one as THEIR positive, in list order
+    if (p.pos_index) {
+#pragma unroll
+        for (int q = 0; q < kRows; ++q) {
+            const int64_t row = p.a_begin + min(r0 + q, p.a_count - 1);
+            for (int e = p.inv_ptr[row]; e < p.inv_ptr[row + 1]; ++e) {
+                const TOp* ub = U + (int64_t)p.inv_idx[e] * D;
+#pragma unroll
+                for (int c = 0; c < kChunks; ++c) {
+                    const int k = c * 128 + lane * 4;
+                    if (k < D) {
+                        const float4 u = Elem<TOp>::ld4(ub + k);
+                        du[q][c].x -= u.x; du[q][c].y -= u.y; du[q][c].z -= u.z; du[q][c].w -= u.w;
+                    }
                 }
             }
         }
@@ -361,11 +382,50 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
     p.scale = a.scale; p.du_out = a.du_out; p.inv_norm = a.inv_norm; p.grad_out = a.grad_out;
     p.lse_all = a.lse_all; p.inv_tau = a.inv_tau; p.pos_prob_out = a.pos_prob_out;
     p.tau_grad_rows_out = a.du_out ? nullptr : a.tau_grad_rows_out;
+    p.pos_index = a.pos_index; p.inv_ptr = a.inv_ptr; p.inv_idx = a.inv_idx;
     if (a.op_bf16)
         return a.z_bf16 ? launch_bwd_epilogue_t<__nv_bfloat16, __nv_bfloat16>(p, a, stream)
                         : launch_bwd_epilogue_t<__nv_bfloat16, float>(p, a, stream);
     return a.z_bf16 ? launch_bwd_epilogue_t<float, __nv_bfloat16>(p, a, stream)
                     : launch_bwd_epilogue_t<float, float>(p, a, stream);
+}
+
+// ------------------------------------------------------------------ pos dot ---
+template <typename T>
+__global__ void __launch_bounds__(256)
+pos_dot_kernel(const T* __restrict__ U, int64_t M, int D, const int* __restrict__ pos_index, float k_scale,
+               float* __restrict__ pos_t) {
+    pdl_trigger();
+    const int lane = threadIdx.x & 31;
+    const int64_t r0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 4;
+    if (r0 >= M) return;
+    pdl_wait();
+    float dot[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int64_t r = min(r0 + q, M - 1);
+        const T* ui = U + r * D;
+        const T* up = U + (int64_t)pos_index[r] * D;
+        for (int k = lane * 4; k < D; k += 128) {
+            const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
+            dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float d = warp_sum(dot[q]);
+        if (lane == 0 && r0 + q < M) pos_t[r0 + q] = d * k_scale;
+    }
+}
+
+cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, const int* pos_index,
+                           float k_scale, float* pos_t, cudaStream_t stream) {
+    dim3 grid((unsigned)((M + 31) / 32)), block(256);
+    if (op_bf16)
+        return launch_kernel(pos_dot_kernel<__nv_bfloat16>, grid, block, 0, stream, (const __nv_bfloat16*)u_all, M,
+                             (int)D, pos_index, k_scale, pos_t);
+    return launch_kernel(pos_dot_kernel<float>, grid, block, 0, stream, (const float*)u_all, M, (int)D, pos_index,
+                         k_scale, pos_t);
 }
 
 // --------------------------------------------------------------- finalize dz ---

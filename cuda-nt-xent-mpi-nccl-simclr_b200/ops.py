@@ -87,6 +87,23 @@ class _NTXentLearnableTauFunction(torch.autograd.Function):
         return dz, dtau.to(device=device, dtype=dtype), None
 
 
+class _NTXentPositivesFunction(torch.autograd.Function):
+    """NT-Xent with the positive of every row given by an index vector.
+    Forward and backward run as one fused call in forward(); backward scales the stored gradient."""
+
+    @staticmethod
+    def forward(ctx, z, pos_lists, T, use_mixed_precision):
+        need = z.requires_grad
+        loss, _, dz = capi.forward_backward_pos(z.detach(), pos_lists, T, None, use_mixed_precision, want_dz=need)
+        ctx.dz = dz
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        dz = ctx.dz
+        return (dz.float() * grad_loss.reshape(-1)[:1].float()).to(dz.dtype), None, None, None
+
+
 class GraphedNTXent:
     """Fused forward+backward for a fixed [M, D] shape, captured once into a CUDA graph and replayed
     (SURVEY.md section 8f-2): for projection-head sized batches (2N ~ 4096) the six launches of a
@@ -117,9 +134,14 @@ class GraphedNTXent:
 
 
 def ntxent_loss(z: torch.Tensor, temperature: float = 0.07,
-                use_mixed_precision: bool = False) -> torch.Tensor:
+                use_mixed_precision: bool = False, positives: torch.Tensor | None = None) -> torch.Tensor:
     """Scalar (0-dim) differentiable NT-Xent loss of the stacked batch z[2N, D].  A 0-dim tensor
-    temperature that requires grad receives d loss / d tau."""
+    temperature that requires grad receives d loss / d tau.  `positives`: an int tensor [M] naming
+    the positive of every row (default: row i's positive is row (i + N) mod 2N); pass the result
+    of capi.inverse_positives() instead to skip the per-call sort."""
+    if positives is not None:
+        lists = positives if isinstance(positives, tuple) else capi.inverse_positives(positives.to(z.device))
+        return _NTXentPositivesFunction.apply(z, lists, float(temperature), use_mixed_precision).squeeze(0)
     if isinstance(temperature, torch.Tensor):
         if temperature.requires_grad:
             return _NTXentLearnableTauFunction.apply(z, temperature, use_mixed_precision).squeeze(0)

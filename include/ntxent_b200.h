@@ -113,6 +113,23 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out,
                                  float* loss_out, float* lse_out, void* dz_out,
                                  float* pos_prob_out, ntxent_stream_t stream);
 
+/* Positives from an index vector (supervised pairs, any
+ * pairing of the rows; no counterpart in the reference, which hard-wires the
+ * positive, src/ntxent_kernel.cu:117).  pos[i] (device int32[M], != i) is the
+ * positive of row i; everything else is as in ntxent_b200_forward_backward: the
+ * denominators still run over all j != i.  The gradient needs the inverse
+ * relation too -- inv_idx[inv_ptr[a] .. inv_ptr[a+1]) (device int32[M+1] /
+ * int32[M]) lists the rows b with pos[b] == a, in any fixed order -- because
+ * row a's gradient holds  -u_pos[a] - sum of those u_b.  The default positives
+ * are the involution pos[i] = (i + M/2) mod M, for which both are u_pos[i].
+ * dz_out == NULL: forward only (inv_* may then be NULL).  M need not split
+ * into two views here, but must still be even. */
+int ntxent_b200_forward_backward_pos(const void* z, const int32_t* pos, const int32_t* inv_ptr,
+                                     const int32_t* inv_idx, const float* grad_out, int64_t M, int64_t D,
+                                     float tau, int dtype, unsigned flags, void* workspace,
+                                     size_t workspace_bytes, float* loss_out, float* lse_out, void* dz_out,
+                                     ntxent_stream_t stream);
+
 /* ---- Row-partitioned (multi-GPU) building blocks ---------------------------
  * The reference names NCCL/MPI only as link options (CMakeLists.txt:13-14,
  * 41-47,115-121) and has no call sites; these are the pieces a data-parallel

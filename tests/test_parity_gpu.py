@@ -371,6 +371,39 @@ def test_learnable_temperature_module():
     assert abs(mod.temperature.grad.item() - tb.grad.item()) <= 2e-4 * abs(tb.grad.item())
 
 
+@pytest.mark.parametrize("M,D,tau,dtype", [(512, 64, 0.2, torch.float32), (2048, 128, 0.5, torch.float32),
+                                           (1024, 128, 0.1, torch.bfloat16), (8192, 128, 0.1, torch.bfloat16)])
+def test_arbitrary_positives(oracle, M, D, tau, dtype):
+    """the positive of every row from an index vector (not an involution, with
+    rows sharing a positive), through ntxent_b200_forward_backward_pos, against the fp64 oracle; the
+    default positives through the same entry point give the ordinary result bit for bit."""
+    z_t = dev(seeded_z(M, D, seed=M + 1), dtype)
+    rng = np.random.default_rng(M)
+    pos = rng.permutation(M)
+    pos[pos == np.arange(M)] = (np.arange(M)[pos == np.arange(M)] + 1) % M  # no row is its own positive
+    pos[: M // 8] = pos[M // 8: M // 4]                                      # shared positives
+    pos[pos == np.arange(M)] = (np.arange(M)[pos == np.arange(M)] + 1) % M
+    lists = capi.inverse_positives(torch.from_numpy(pos).cuda())
+    g = torch.tensor([0.75], device="cuda")
+    loss, lse, dz = capi.forward_backward_pos(z_t, lists, tau, g)
+    torch.cuda.synchronize()
+    rl, rlse, rdz = oracle.forward_backward_pos(z_t.double().cpu().numpy(), pos, tau, 0.75)
+    bf = dtype == torch.bfloat16
+    assert loss.item() == pytest.approx(rl, rel=LOSS_RTOL_BF16 if bf else LOSS_RTOL_F32)
+    assert dz_err(dz.double().cpu().numpy(), rdz) <= (dz_tol_bf16(tau) if bf else DZ_TOL_F32)
+    # the canonical positives through the index path
+    canon = capi.inverse_positives((torch.arange(M, device="cuda") + M // 2) % M)
+    l2, lse2, dz2 = capi.forward_backward_pos(z_t, canon, tau, g)
+    l1, lse1, dz1 = capi.forward_backward(z_t, tau, g)
+    assert torch.equal(lse2, lse1)
+    assert l2.item() == pytest.approx(l1.item(), rel=1e-5 if not bf else 1e-3)
+    assert dz_err(dz2.double().cpu().numpy(), dz1.double().cpu().numpy()) <= (1e-2 if bf else 1e-5)
+    # autograd front end
+    za = z_t.clone().requires_grad_(True)
+    (ntxent_b200.ntxent_loss(za, tau, positives=torch.from_numpy(pos).cuda()) * 0.75).backward()
+    assert dz_err(za.grad.double().cpu().numpy(), dz.double().cpu().numpy()) <= (2.0 ** -7 if bf else 1e-6)
+
+
 def test_fused_equals_separate_and_is_deterministic():
     z_t = dev(seeded_z(1024, 128, seed=5), torch.bfloat16)
     loss, lse = capi.forward(z_t, 0.1)
