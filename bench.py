@@ -282,7 +282,7 @@ def run_reference(args):
         "note": "the reference has no CPU NT-Xent and its CUDA sources do not compile; this is "
                 "the oracle port on the host cores (a rate: FLOP of the rows it processed / time)",
     }
-    print(json.dumps(line))
+    OUT.emit(json.dumps(line))
     return 0
 
 
@@ -584,13 +584,33 @@ def run_native(args):
                                 "sample": sample_text(cpu["rows"], M, cpu["seconds"])}
         line["parity"] = parity_vs_oracle(zq, tau, cpu, loss_val, lse_last.astype(np.float64),
                                           dz_last.float().numpy().astype(np.float64))
-    print(json.dumps(line))
+    OUT.emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+class CleanStdout:
+    """The driver reads ONE JSON line from stdout.  Libraries print there too (NCCL announces its
+    version on the first communicator): send everything to stderr while the benchmark runs and
+    write the line to the real stdout at the end."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, text):
+        sys.stdout.flush()
+        os.write(self.real, (text.rstrip("\n") + "\n").encode())
+
+
+OUT = None
+
+
 def main():
+    global OUT
+    OUT = CleanStdout()
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -396,7 +396,7 @@ __device__ __forceinline__ void weight_chunk(const uint32_t (&v)[32], uint32_t (
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
             const f32x2 sum = add2(rc2, pack2(cc[e], cc[e + 1]));
-            const f32x2 x = mul2(pack2(ex2(__uint_as_float(v[e])), ex2(__uint_as_float(v[e + 1]))), sum);
+            const f32x2 x = mul2(ex2_pair<kBwdPolyPairs>(v[e], v[e + 1], e >> 1), sum);
             float w0, w1;
             unpack2(x, w0, w1);
             if (kPacked) {

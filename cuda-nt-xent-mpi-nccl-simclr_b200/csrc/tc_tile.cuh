@@ -27,6 +27,11 @@ constexpr int kFwdPoly = NTX_FWD_POLY, kBwdPoly = NTX_BWD_POLY;
 #define NTX_FWD_POLY_PAIRS 1
 #endif
 constexpr int kFwdPolyPairs = NTX_FWD_POLY_PAIRS;
+// the same choice for the backward's packed weight loop (0: every exponential on the MUFU)
+#ifndef NTX_BWD_POLY_PAIRS
+#define NTX_BWD_POLY_PAIRS 0
+#endif
+constexpr int kBwdPolyPairs = NTX_BWD_POLY_PAIRS;
 
 // TF32 = false: bf16 operands, .kind::f16 (K = 16 per MMA).  TF32 = true: fp32 operands read as
 // tf32, .kind::tf32 (K = 8 per MMA).  Either way one MMA consumes 32 bytes of every operand row
