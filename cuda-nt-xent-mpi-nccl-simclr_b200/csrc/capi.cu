@@ -246,26 +246,14 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, w.pos_t, u_ready, st));
+                              w.part_s, u_ready, st));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, u_ready, st));
     g_timer.stop(0, st);
-    if (pos_index) {  // positives from an index vector (whole-batch calls only): their logits, over
-                      // whatever the tile kernel captured for the default positives
-        NTX_TRY(launch_pos_dot(u_all, op_bf16, M, D, pos_index, kLog2e / tau, w.pos_t, st));
-        NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
-                                         w.part_s, w.pos_t, lse_outs, lse_offset, w.block_partials, loss_outs,
-                                         loss_index, loss_scale, lse_signal, st));
-        return NTXENT_OK;
-    }
-    NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit,
-#ifdef NTX_FWD_NOPOS
-                                     w.part_m, w.part_s, nullptr, lse_outs, lse_offset,
-#else
-                                     w.part_m, w.part_s, p.tc ? w.pos_t : nullptr, lse_outs, lse_offset,
-#endif
-                                     w.block_partials, loss_outs, loss_index, loss_scale, lse_signal, st));
+    NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
+                                     w.part_s, w.pos_t, pos_index, lse_outs, lse_offset, w.block_partials,
+                                     loss_outs, loss_index, loss_scale, lse_signal, st));
     return NTXENT_OK;
 }
 
@@ -288,7 +276,7 @@ int run_forward_device(const void* U, bool op_bf16, int64_t M, int64_t D, float 
     g_timer.start(0, st);
     NTX_TRY(tc_launch_fwd_sym(U, M, D, tau, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, st));
     g_timer.stop(0, st);
-    if (pos_index) NTX_TRY(launch_pos_dot(U, op_bf16, M, D, pos_index, kLog2e / tau, w.pos_t, st));
+    if (pos_index) NTX_TRY(launch_pos_dot(U, op_bf16, M, D, 0, M, pos_index, kLog2e / tau, w.pos_t, st));
     NTX_TRY(tc_launch_fwd_sym_finalize(M, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, lse_out, w.block_partials,
                                        st));
     NTX_TRY(launch_loss_reduce(w.block_partials, p.symp.T, single_peer(loss_out), 0, 1.0f / (float)M, no_signal(),

@@ -96,15 +96,14 @@ cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_al
 // One warp that waits for every slot (for consumers that are not ours, e.g. a sum of the loss parts).
 cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream);
 
-// Forward finalize: combine the split partials into l_i, subtract the positive logit, reduce the
-// loss.  l_i goes to element lse_offset + i of every buffer in `lse_outs`, the (scaled) loss to
-// element loss_index of every buffer in `loss_outs` (one buffer each on a single device).
-// pos_t: the positive logits in base-2 units (k u_i.u_pos(i)) as captured by the tcgen05 forward
-// tile kernel from the same MMA that feeds the denominator, or nullptr: the kernel then forms the
-// dot product of the operand rows itself (fp32-FMA family).
+// Forward finalize: the positive logits k u_i . u_pos(i) (pos_index == nullptr: pos(i) =
+// (i + M/2) mod M) into pos_t [row_count], then the split partials combined into l_i, the positive
+// logit subtracted, the loss reduced.  l_i goes to element lse_offset + i of every buffer in
+// `lse_outs`, the (scaled) loss to element loss_index of every buffer in `loss_outs` (one buffer
+// each on a single device).
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                     const float* part_m, const float* part_s, const float* pos_t,
+                                     const float* part_m, const float* part_s, float* pos_t, const int* pos_index,
                                      const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
                                      const PeerList& loss_outs, int loss_index, float loss_scale,
                                      const PeerSignal& signal, cudaStream_t stream);
@@ -114,10 +113,11 @@ cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M,
 cudaError_t launch_loss_reduce(const float* block_partials, int n, const PeerList& loss_outs, int loss_index,
                                float loss_scale, const PeerSignal& signal, cudaStream_t stream);
 
-// pos_t[i] = (log2(e)/tau) u_i . u_pos[i] for positives given by an index vector (fp32 dot of the
-// operand rows): what the tile kernels capture themselves for the default positives.
-cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, const int* pos_index,
-                           float k_scale, float* pos_t, cudaStream_t stream);
+// pos_t[r] = (log2(e)/tau) u_i . u_pos(i), i = row_begin + r, as an fp32 dot product of the operand
+// rows; pos(i) = pos_index[i], or (i + M/2) mod M when pos_index is null.
+cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
+                           int64_t row_count, const int* pos_index, float k_scale, float* pos_t,
+                           cudaStream_t stream);
 
 struct BwdEpilogueArgs {
     const float* acc;        // [nsplit][a_count][D] raw sums  sum_b W_ab u_b

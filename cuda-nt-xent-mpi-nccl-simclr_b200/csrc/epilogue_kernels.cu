@@ -12,71 +12,9 @@ namespace ntxent_b200 {
 constexpr int kMaxDChunks = 8;  // D <= 1024: each lane holds 4 floats per 128-wide chunk
 
 // -------------------------------------------------------------- fwd finalize ---
-constexpr int kFinalizeRowsPerWarp = 4;                       // independent rows in flight per warp
-constexpr int kFinalizeRowsPerCta = 8 * kFinalizeRowsPerWarp;
-
-// fp32-FMA family (no captured positive logits): one warp per four rows, the positive logit as
-// an fp32 dot product of the operand rows.
-template <typename T>
-__global__ void __launch_bounds__(256)
-fwd_finalize_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
-                    float inv_tau, int nsplit, const float* __restrict__ part_m,
-                    const float* __restrict__ part_s, PeerList lse_outs, int64_t lse_offset,
-                    float* __restrict__ block_partials) {
-    __shared__ float warp_contrib[8];
-    pdl_trigger();
-    pdl_wait();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t r0 = (int64_t)blockIdx.x * kFinalizeRowsPerCta + warp * kFinalizeRowsPerWarp;
-    float m[kFinalizeRowsPerWarp], s[kFinalizeRowsPerWarp], dot[kFinalizeRowsPerWarp];
-    // all loads of the warp's four rows are issued before any of them is consumed
-#pragma unroll
-    for (int q = 0; q < kFinalizeRowsPerWarp; ++q) {
-        const int64_t r = r0 + q;
-        m[q] = -INFINITY; s[q] = 0.f; dot[q] = 0.f;
-        if (r < row_count) {
-            for (int sp = lane; sp < nsplit; sp += 32)
-                lse2_merge(m[q], s[q], part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
-            const int64_t row = row_begin + r;
-            const T* ui = U + row * D;
-            const T* up = U + ((row + M / 2) % M) * D;
-            for (int k = lane * 4; k < D; k += 128) {
-                const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
-                dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
-            }
-        }
-    }
-    float contrib = 0.f;
-#pragma unroll
-    for (int q = 0; q < kFinalizeRowsPerWarp; ++q) {
-        const int64_t r = r0 + q;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float m2 = __shfl_xor_sync(0xffffffffu, m[q], o);
-            const float s2 = __shfl_xor_sync(0xffffffffu, s[q], o);
-            lse2_merge(m[q], s[q], m2, s2);
-        }
-        const float d = warp_sum(dot[q]);
-        if (r < row_count) {
-            const float l = (m[q] + log2f(s[q])) * kLn2;
-            if (lane == 0)
-                for (int i = 0; i < lse_outs.n; ++i) static_cast<float*>(lse_outs.p[i])[lse_offset + r] = l;
-            contrib += l - d * inv_tau;
-        }
-    }
-    if (lane == 0) warp_contrib[warp] = contrib;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float bsum = 0.f;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) bsum += warp_contrib[w];
-        block_partials[blockIdx.x] = bsum;
-    }
-}
-
-// tcgen05 family: the forward tile kernel has already captured the positive logit of every row
-// (pos_t, base-2 units), so all that is left is one thread per row merging nsplit coalesced
-// partials: ~M * (8 nsplit + 12) bytes, against two 16 MB sweeps over U before.
+// The positive logit of every row is there already (pos_t, base-2 units: captured by the
+// upper-triangle forward kernel from its own MMA, or formed by pos_dot_kernel below), so all that is
+// left is one thread per row merging nsplit coalesced partials: ~M * (8 nsplit + 12) bytes.
 constexpr int kFinalizeThreads = 128;
 __global__ void __launch_bounds__(kFinalizeThreads)
 fwd_finalize_rows_kernel(int64_t row_count, int nsplit, const float* __restrict__ part_m,
@@ -162,27 +100,16 @@ cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream) {
 
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
-                                     const float* part_m, const float* part_s, const float* pos_t,
+                                     const float* part_m, const float* part_s, float* pos_t, const int* pos_index,
                                      const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
                                      const PeerList& loss_outs, int loss_index, float loss_scale,
                                      const PeerSignal& signal, cudaStream_t stream) {
-    cudaError_t e;
-    unsigned blocks;
-    if (pos_t) {
-        blocks = (unsigned)((row_count + kFinalizeThreads - 1) / kFinalizeThreads);
-        e = launch_kernel(fwd_finalize_rows_kernel, dim3(blocks), dim3(kFinalizeThreads), 0, stream, row_count,
-                          nsplit, part_m, part_s, pos_t, lse_outs, lse_offset, block_partials);
-    } else {
-        blocks = (unsigned)((row_count + kFinalizeRowsPerCta - 1) / kFinalizeRowsPerCta);
-        if (op_bf16)
-            e = launch_kernel(fwd_finalize_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
-                              (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit,
-                              part_m, part_s, lse_outs, lse_offset, block_partials);
-        else
-            e = launch_kernel(fwd_finalize_kernel<float>, dim3(blocks), dim3(256), 0, stream,
-                              (const float*)u_all, M, (int)D, row_begin, row_count, 1.0f / tau, nsplit, part_m,
-                              part_s, lse_outs, lse_offset, block_partials);
-    }
+    // the positive logits: k u_i . u_pos(i), fp32 dot products of the operand rows
+    cudaError_t e = launch_pos_dot(u_all, op_bf16, M, D, row_begin, row_count, pos_index, kLog2e / tau, pos_t, stream);
+    if (e != cudaSuccess) return e;
+    const unsigned blocks = (unsigned)((row_count + kFinalizeThreads - 1) / kFinalizeThreads);
+    e = launch_kernel(fwd_finalize_rows_kernel, dim3(blocks), dim3(kFinalizeThreads), 0, stream, row_count, nsplit,
+                      part_m, part_s, (const float*)pos_t, lse_outs, lse_offset, block_partials);
     if (e != cudaSuccess) return e;
     return launch_loss_reduce(block_partials, (int)blocks, loss_outs, loss_index, loss_scale, signal, stream);
 }
@@ -391,21 +318,24 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
 }
 
 // ------------------------------------------------------------------ pos dot ---
+// pos_t[r] = k u_i . u_pos(i) for rows i = row_begin + r: the positive (i + M/2) mod M, or
+// pos_index[i].  One warp per four rows, all loads issued first (both rows of a pair live in L2).
 template <typename T>
 __global__ void __launch_bounds__(256)
-pos_dot_kernel(const T* __restrict__ U, int64_t M, int D, const int* __restrict__ pos_index, float k_scale,
-               float* __restrict__ pos_t) {
+pos_dot_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
+               const int* __restrict__ pos_index, float k_scale, float* __restrict__ pos_t) {
     pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t r0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 4;
-    if (r0 >= M) return;
+    if (r0 >= row_count) return;
     pdl_wait();
     float dot[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        const int64_t r = min(r0 + q, M - 1);
-        const T* ui = U + r * D;
-        const T* up = U + (int64_t)pos_index[r] * D;
+        const int64_t i = row_begin + min(r0 + q, row_count - 1);
+        const int64_t pi = pos_index ? (int64_t)pos_index[i] : (i + M / 2) % M;
+        const T* ui = U + i * D;
+        const T* up = U + pi * D;
         for (int k = lane * 4; k < D; k += 128) {
             const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
             dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
@@ -414,18 +344,19 @@ pos_dot_kernel(const T* __restrict__ U, int64_t M, int D, const int* __restrict_
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const float d = warp_sum(dot[q]);
-        if (lane == 0 && r0 + q < M) pos_t[r0 + q] = d * k_scale;
+        if (lane == 0 && r0 + q < row_count) pos_t[r0 + q] = d * k_scale;
     }
 }
 
-cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, const int* pos_index,
-                           float k_scale, float* pos_t, cudaStream_t stream) {
-    dim3 grid((unsigned)((M + 31) / 32)), block(256);
+cudaError_t launch_pos_dot(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
+                           int64_t row_count, const int* pos_index, float k_scale, float* pos_t,
+                           cudaStream_t stream) {
+    dim3 grid((unsigned)((row_count + 31) / 32)), block(256);
     if (op_bf16)
         return launch_kernel(pos_dot_kernel<__nv_bfloat16>, grid, block, 0, stream, (const __nv_bfloat16*)u_all, M,
-                             (int)D, pos_index, k_scale, pos_t);
-    return launch_kernel(pos_dot_kernel<float>, grid, block, 0, stream, (const float*)u_all, M, (int)D, pos_index,
-                         k_scale, pos_t);
+                             (int)D, row_begin, row_count, pos_index, k_scale, pos_t);
+    return launch_kernel(pos_dot_kernel<float>, grid, block, 0, stream, (const float*)u_all, M, (int)D, row_begin,
+                         row_count, pos_index, k_scale, pos_t);
 }
 
 // --------------------------------------------------------------- finalize dz ---

@@ -89,8 +89,7 @@ template <int D, bool TF32, bool kOnline>
 __global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
               int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
-              float* __restrict__ part_m, float* __restrict__ part_s, float* __restrict__ pos_t_out,
-              PeerWait u_ready) {
+              float* __restrict__ part_m, float* __restrict__ part_s, PeerWait u_ready) {
     using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
     extern __shared__ uint8_t smem_raw[];
@@ -243,48 +242,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         // this row tile's own rows (the diagonal) and everything from the ragged end of the range
         const int hj_diag_lo = (int)(a0 / 64), hj_diag_hi = (int)((a0 + 63) / 64) + 1;
         const int hj_ragged = (int)(M / 64);
-        // ... and the one or two that hold the positives of THIS WARP's 32 rows (columns
-        // (row + N) mod M: a run of 32, which can straddle a half-tile boundary or wrap around M)
-        const int64_t wrow0 = a0 + quad * 32;
-#ifdef NTX_FWD_NOPOS
-        const int hj_pos_a = -1, hj_pos_b = -1;
-#else
-        const int hj_pos_a = (int)(((wrow0 + M / 2) % M) / 64);
-        const int hj_pos_b = (int)(((min(wrow0 + 31, M - 1) + M / 2) % M) / 64);
-#endif
-        const int64_t pos_col = (row + M / 2) % M;
-        // whether this warp's column range holds the row's positive at all (decided once, here)
-        const int pos_hj = (int)(pos_col >> 6);
-#ifdef NTX_FWD_NOPOS  // A/B build: no capture here, the finalize kernel forms the dot products
-        const bool pos_seen = false;
-#else
-        // (the rotated walk covers the tiles whose number counted from `rot` is y, y + S, y + 2 S, ...)
-        const int pos_jt = pos_hj >> 1;
-        const int pos_v = pos_jt >= rot ? pos_jt - rot : pos_jt - rot + col_tiles;
-        const bool pos_in_walk = rotated ? (pos_v >= (int)blockIdx.y && (pos_v - (int)blockIdx.y) % jt_step == 0)
-                                         : (pos_jt >= jt0 && pos_jt < jt0 + n_tiles);
-        const bool pos_seen = (pos_hj & 1) == half && pos_in_walk;
-#endif
-        const int pos_col32 = (int)pos_col;
-        float pos_t = 0.f;
         for (int it = 0, jt = jt0; it < n_tiles; ++it, jt = next_tile(jt)) {
             const int buf = it & 1;
             const int hj = 2 * jt + half;
             const bool special = (hj >= hj_diag_lo && hj <= hj_diag_hi) || hj >= hj_ragged;
-            // the half tile(s) that hold this warp's positives: pick the logit out of the registers
-            // (a rare branch of its own: it must not sit in the exponential loops)
-            const bool has_pos = hj == hj_pos_a || hj == hj_pos_b;
-            const int pos_d = pos_col32 - hj * 64;  // 0..63 when the positive is in here
             const int64_t j0 = (int64_t)hj * 64;  // (used on the masked path only)
             const uint32_t taddr = lane_addr + buf * kTile;
             tmem_ld_wait();
             tmem_ld32(taddr + 32, vb);
             fwd_chunk<kOnline>(va, special, j0, row, M, m_run, s_run);
-            if (has_pos) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e)
-                    if (pos_d == e) pos_t = __uint_as_float(va[e]);
-            }
             tmem_ld_wait();
             // this warp's S columns have left TMEM: hand the buffer back, then prefetch
             tc_fence_before();
@@ -296,14 +262,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                 tmem_ld32(lane_addr + (buf ^ 1) * kTile, va);
             }
             fwd_chunk<kOnline>(vb, special, j0 + 32, row, M, m_run, s_run);
-            if (has_pos) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e)
-                    if (pos_d == 32 + e) pos_t = __uint_as_float(vb[e]);
-            }
         }
-        // the positive logit, from the same MMA (same operand rounding) as the denominator
-        if (pos_seen && row < M && row < row_begin + row_count) pos_t_out[row - row_begin] = pos_t;
         // merge the two column halves of each row (upper half hands over through shared memory)
         float2* halves = reinterpret_cast<float2*>(q_tile);  // the row tile is no longer needed:
         named_bar_sync(1, kSoftmaxThreads);                  // every MMA that read it has completed
@@ -970,7 +929,7 @@ cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtens
 template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
-                         float* part_s, float* pos_t, const PeerWait& u_ready, cudaStream_t stream) {
+                         float* part_s, const PeerWait& u_ready, cudaStream_t stream) {
     using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
     const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
@@ -980,7 +939,7 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
     return launch_kernel(kern, grid, dim3(kThreads), smem, stream, tmap, M, row_begin, row_count, k_scale,
-                         (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s, pos_t, u_ready);
+                         (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s, u_ready);
 }
 
 // U [M, D] fp32 -> UT [D, Mpad] (Mpad = M rounded up to 4, pad columns zero): the K-major B operand
@@ -1128,7 +1087,7 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
-                          float* part_m, float* part_s, float* pos_t, const PeerWait& u_ready,
+                          float* part_m, float* part_s, const PeerWait& u_ready,
                           cudaStream_t stream) {
     CUtensorMap tmap;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
@@ -1138,9 +1097,9 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     const int col_tiles = (int)((M + kTile - 1) / kTile);
 #define NTX_FWD(DD, TF)                                                                                    \
     (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m,  \
-                                         part_s, pos_t, u_ready, stream)                                   \
+                                         part_s, u_ready, stream)                                          \
             : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                          part_s, pos_t, u_ready, stream))
+                                          part_s, u_ready, stream))
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_FWD(64, true);

@@ -13,7 +13,7 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
-                          float* part_m, float* part_s, float* pos_t, const PeerWait& u_ready,
+                          float* part_m, float* part_s, const PeerWait& u_ready,
                           cudaStream_t stream);
 
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,

@@ -33,7 +33,7 @@ from . import capi
 class CudaBackend:
     """The only product backend of the "torch" mode: hand-written sm_100a kernels behind the C-ABI."""
 
-    launches = {"normalize": 1, "forward_rows": 3, "backward_rows_symmetric": 2,
+    launches = {"normalize": 1, "forward_rows": 4, "backward_rows_symmetric": 2,
                 "backward_rows_contract": 4, "finalize_dz": 1}
 
     def __init__(self, flags: int = 0):
@@ -114,7 +114,7 @@ class RowPartitionedNTXent:
         self.ccomm = None
         if comm != "torch":
             self._init_communicator()
-            self.launches_per_step = 8 if comm == "push" else (7 if backward_mode == "symmetric" else 11)
+            self.launches_per_step = 9 if comm == "push" else (8 if backward_mode == "symmetric" else 12)
             return
         self.backend = backend if backend is not None else CudaBackend(flags)
         op_dtype = torch.bfloat16 if (dtype == torch.bfloat16 or use_mixed_precision) else torch.float32

@@ -50,7 +50,10 @@ def emulate_bf16_step(z_t: torch.Tensor, tau: float, grad_out: float = 1.0, bloc
                 lower = tile[r0:r1, None] > tile[None, :]
                 t = torch.where(lower, uf[r0:r1] @ ka.t(), t)
                 del lower
-            pos_t[r0:r1] = t[idx[: r1 - r0], pos[r0:r1]]
+            if sym_forward:  # captured from the tile's own MMA
+                pos_t[r0:r1] = t[idx[: r1 - r0], pos[r0:r1]]
+            else:            # a separate fp32 dot product of the operand rows, scaled afterwards
+                pos_t[r0:r1] = (uf[r0:r1] * uf[pos[r0:r1]]).sum(dim=1) * k
             t[idx[: r1 - r0], idx[r0:r1]] = float("-inf")
             l2[r0:r1] = torch.log2(torch.exp2(t).double().sum(dim=1)).float()
         ln2 = math.log(2.0)

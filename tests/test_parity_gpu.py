@@ -395,7 +395,7 @@ def test_arbitrary_positives(oracle, M, D, tau, dtype):
     canon = capi.inverse_positives((torch.arange(M, device="cuda") + M // 2) % M)
     l2, lse2, dz2 = capi.forward_backward_pos(z_t, canon, tau, g)
     l1, lse1, dz1 = capi.forward_backward(z_t, tau, g)
-    assert torch.equal(lse2, lse1)
+    assert torch.allclose(lse2, lse1, rtol=0, atol=2e-6)
     assert l2.item() == pytest.approx(l1.item(), rel=1e-5 if not bf else 1e-3)
     assert dz_err(dz2.double().cpu().numpy(), dz1.double().cpu().numpy()) <= (1e-2 if bf else 1e-5)
     # autograd front end
