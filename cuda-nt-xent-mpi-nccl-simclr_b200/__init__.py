@@ -13,7 +13,7 @@ Layers:
 """
 from . import capi  # noqa: F401
 from .ops import (GraphedNTXent, NTXentLoss, backward, check_tensor_core_support,  # noqa: F401
-                  forward, forward_with_state, ntxent_loss)
+                  forward, forward_with_state, ntxent_loss, two_tower_loss)
 
 __all__ = ["capi", "forward", "backward", "forward_with_state", "check_tensor_core_support",
-           "ntxent_loss", "NTXentLoss", "GraphedNTXent"]
+           "ntxent_loss", "two_tower_loss", "NTXentLoss", "GraphedNTXent"]

@@ -17,6 +17,7 @@ F32, BF16 = 0, 1
 FLAG_MIXED_PRECISION = 1
 FLAG_FORCE_SIMT = 2
 FLAG_ONLINE_MAX = 4
+FLAG_CROSS_VIEW = 8
 BWD_SYMMETRIC, BWD_CONTRACT = 0, 1
 
 EXPORTS = [

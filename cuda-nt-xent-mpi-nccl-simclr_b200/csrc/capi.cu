@@ -91,6 +91,8 @@ inline bool op_is_bf16(int dtype, unsigned flags) {
 constexpr float kTf32MaxScaledK = 1.7f;
 inline bool want_tc(int64_t M, int64_t D, bool op_bf16, unsigned flags, float tau) {
     if (flags & NTXENT_FLAG_FORCE_SIMT) return false;
+    // the cross-view form walks whole column tiles of the other view: N = M/2 must be tile-aligned
+    if ((flags & NTXENT_FLAG_CROSS_VIEW) && (M / 2) % 128 != 0) return false;
     if (!op_bf16 && tau >= 0.f && kLog2e / (tau * sqrtf((float)D)) > kTf32MaxScaledK) return false;
     return tc_supported(M, D, op_bf16);
 }
@@ -99,7 +101,8 @@ inline bool want_tc(int64_t M, int64_t D, bool op_bf16, unsigned flags, float ta
 // tile kernel -- for ntxent_b200_forward_static, whose built-in scratch has no room for the
 // upper-triangle kernel's column partials.
 constexpr unsigned kFlagNoSymForward = 1u << 16;
-constexpr unsigned kPublicFlags = NTXENT_FLAG_MIXED_PRECISION | NTXENT_FLAG_FORCE_SIMT | NTXENT_FLAG_ONLINE_MAX;
+constexpr unsigned kPublicFlags = NTXENT_FLAG_MIXED_PRECISION | NTXENT_FLAG_FORCE_SIMT | NTXENT_FLAG_ONLINE_MAX |
+                                  NTXENT_FLAG_CROSS_VIEW;
 
 struct Plans {
     SplitPlan fwd, bwd_rows, bwd_cols;
@@ -110,6 +113,7 @@ struct Plans {
     // layout reserves its buffers (decided without tau), `sym`: this call uses it
     bool sym_room, sym;
     SymPlan symp;
+    bool cross;  // NTXENT_FLAG_CROSS_VIEW: denominators over the other view only (whole-batch calls)
 };
 
 // All split decisions in one place so that sizing and launching can never disagree.
@@ -118,14 +122,16 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
     p.flags = flags;
     p.ut_bytes = 0;
     p.tc = want_tc(M, D, op_bf16, flags, tau);
+    p.cross = (flags & NTXENT_FLAG_CROSS_VIEW) != 0;
     const int sms = device_sm_count();
     if (p.tc) {
-        p.fwd = tc_plan_fwd(M, D, row_count, op_bf16, sms);
-        p.bwd_rows = tc_plan_bwd(M, D, row_count, M, sms);
+        // (cross-view form: every row tile meets only the M/2 columns of the other view)
+        p.fwd = tc_plan_fwd(p.cross ? M / 2 : M, D, row_count, op_bf16, sms);
+        p.bwd_rows = tc_plan_bwd(M, D, row_count, p.cross ? M / 2 : M, sms);
         p.bwd_cols = tc_plan_bwd(M, D, M, row_count, sms);
         p.ut_bytes = tc_bwd_scratch_bytes(M, D, op_bf16);
         const bool env_off = [] { const char* v = getenv("NTXENT_NO_SYM_FORWARD"); return v && v[0] == '1'; }();
-        if (row_count == M && !(flags & kFlagNoSymForward) && !env_off) {
+        if (row_count == M && !(flags & kFlagNoSymForward) && !env_off && !p.cross) {
             p.sym_room = tc_sym_supported(M, D, op_bf16, 1.0f, flags);
             p.sym = tau >= 0.f && tc_sym_supported(M, D, op_bf16, tau, flags);
             if (p.sym_room) p.symp = tc_sym_plan(M, D, sms);
@@ -246,10 +252,10 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, u_ready, st));
+                              w.part_s, u_ready, st, p.cross));
     else
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
-                                w.part_s, u_ready, st));
+                                w.part_s, u_ready, st, p.cross ? M / 2 : 0));
     g_timer.stop(0, st);
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
                                      w.part_s, w.pos_t, pos_index, lse_outs, lse_offset, w.block_partials,
@@ -331,11 +337,11 @@ int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t
                   cudaStream_t st, const PeerWait& lse_ready = PeerWait{}) {
     g_timer.start(1, st);
     if (p.tc)
-        NTX_TRY(tc_launch_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count, tau,
-                              mode, p.flags, plan, acc, ut, lse_ready, st));
+        NTX_TRY(tc_launch_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, p.cross ? M / 2 : b_count,
+                              tau, mode, p.flags, plan, acc, ut, lse_ready, st, p.cross));
     else
         NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
-                                tau, mode, plan, acc, lse_ready, st));
+                                tau, mode, plan, acc, lse_ready, st, p.cross ? M / 2 : 0));
     g_timer.stop(1, st);
     return NTXENT_OK;
 }
@@ -559,6 +565,7 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // whole-batch calls only
     const bool opb = op_is_bf16(dtype, flags);
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
@@ -596,6 +603,7 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // whole-batch calls only
     const bool opb = op_is_bf16(dtype, flags);
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
@@ -722,6 +730,7 @@ int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t ro
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // whole-batch calls only
     const bool opb = op_is_bf16(dtype, flags);
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
@@ -746,6 +755,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // whole-batch calls only
     const bool opb = op_is_bf16(dtype, flags);
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
@@ -767,6 +777,7 @@ int ntxent_b200_backward_rows_part(const void* u_all, const float* lse_all, int6
     if (rc != NTXENT_OK) return rc;
     if (row_begin < 0 || row_count < 1 || row_begin + row_count > M)
         return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // whole-batch calls only
     const bool opb = op_is_bf16(dtype, flags);
     const Plans p = make_plans(M, D, row_count, opb, flags, tau);
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);

@@ -164,8 +164,9 @@ __global__ void __launch_bounds__(256) add_inplace_kernel(float* __restrict__ a,
     }
 }
 
-int check_problem(int nranks, int64_t M, int64_t D, int dtype) {
+int check_problem(int nranks, int64_t M, int64_t D, int dtype, unsigned flags) {
     if (nranks < 1 || nranks > NTXENT_MAX_PEERS) return NTXENT_ERR_INVALID_ARGUMENT;
+    if (flags & NTXENT_FLAG_CROSS_VIEW) return NTXENT_ERR_INVALID_ARGUMENT;  // single-device entries only
     if (dtype != NTXENT_F32 && dtype != NTXENT_BF16) return NTXENT_ERR_INVALID_ARGUMENT;
     if (M < 2 || (M & 1) || M % nranks) return NTXENT_ERR_INVALID_ARGUMENT;
     if (D < 8 || (D % 8) != 0 || D > 1024 || M > ((int64_t)1 << 24)) return NTXENT_ERR_UNSUPPORTED_SHAPE;
@@ -229,7 +230,7 @@ extern "C" {
 int ntxent_b200_comm_init_all(int ndev, const int* devices, int64_t M, int64_t D, int dtype, unsigned flags,
                               ntxent_comm_t** comms_out) {
     if (!devices || !comms_out) return NTXENT_ERR_INVALID_ARGUMENT;
-    int rc = check_problem(ndev, M, D, dtype);
+    int rc = check_problem(ndev, M, D, dtype, flags);
     if (rc != NTXENT_OK) return rc;
     int prev = 0;
     NTX_CUDA(cudaGetDevice(&prev));
@@ -287,7 +288,7 @@ int ntxent_b200_comm_unique_id(void* id128_out) {
 int ntxent_b200_comm_init_rank(const void* id128, int nranks, int rank, int64_t M, int64_t D, int dtype,
                                unsigned flags, ntxent_comm_t** comm_out) {
     if (!id128 || !comm_out || rank < 0 || rank >= nranks) return NTXENT_ERR_INVALID_ARGUMENT;
-    int rc = check_problem(nranks, M, D, dtype);
+    int rc = check_problem(nranks, M, D, dtype, flags);
     if (rc != NTXENT_OK) return rc;
     if (ntxent_b200_device_supported() != 1) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     if (nranks > 1 && !nccl().ok) return NTXENT_ERR_COLLECTIVE;  // the bootstrap runs over NCCL

@@ -88,11 +88,11 @@ cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int6
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                             int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
                             float* part_m, float* part_s, const PeerWait& u_ready,
-                            cudaStream_t stream);
+                            cudaStream_t stream, int64_t cross_n = 0);
 cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
                             int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
                             int64_t b_count, float tau, int mode, const SplitPlan& plan, float* acc,
-                            const PeerWait& lse_ready, cudaStream_t stream);
+                            const PeerWait& lse_ready, cudaStream_t stream, int64_t cross_n = 0);
 // One warp that waits for every slot (for consumers that are not ours, e.g. a sum of the loss parts).
 cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream);
 

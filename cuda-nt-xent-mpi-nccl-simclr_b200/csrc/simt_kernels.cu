@@ -170,7 +170,7 @@ __device__ __forceinline__ void simt_s_tile(const T* __restrict__ U, int64_t M, 
 template <typename T>
 __global__ void __launch_bounds__(256)
 simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
-                float scale_log2, int64_t cols_per_split, float* __restrict__ part_m,
+                float scale_log2, int64_t cols_per_split, int64_t cross_n, float* __restrict__ part_m,
                 float* __restrict__ part_s, PeerWait u_ready) {
     __shared__ __align__(16) float As[kTK][kTM + kPad];
     __shared__ __align__(16) float Bs[kTK][kTN + kPad];
@@ -194,7 +194,8 @@ simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, in
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
                 const int64_t col = b0 + tx * 4 + b;
-                const bool ok = (col < b_hi) && (col != row);
+                // cross_n > 0: only the other view's columns count (two-tower form)
+                const bool ok = (col < b_hi) && (col != row) && !(cross_n > 0 && ((col >= cross_n) == (row >= cross_n)));
                 t[b] = ok ? acc[a][b] * scale_log2 : -INFINITY;
                 tmax = fmaxf(tmax, t[b]);
             }
@@ -227,15 +228,15 @@ simt_fwd_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, in
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                             int64_t row_begin, int64_t row_count, float tau, const SplitPlan& plan,
                             float* part_m, float* part_s, const PeerWait& u_ready,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, int64_t cross_n) {
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit), block(256);
     const float scale_log2 = kLog2e / tau;
     if (op_bf16)
         return launch_kernel(simt_fwd_kernel<__nv_bfloat16>, grid, block, 0, stream,
                              (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, scale_log2,
-                             plan.cols_per_split, part_m, part_s, u_ready);
+                             plan.cols_per_split, cross_n, part_m, part_s, u_ready);
     return launch_kernel(simt_fwd_kernel<float>, grid, block, 0, stream, (const float*)u_all, M, (int)D,
-                         row_begin, row_count, scale_log2, plan.cols_per_split, part_m, part_s, u_ready);
+                         row_begin, row_count, scale_log2, plan.cols_per_split, cross_n, part_m, part_s, u_ready);
 }
 
 // --------------------------------------------------------------- backward ---
@@ -248,7 +249,7 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(256)
 simt_bwd_kernel(const T* __restrict__ U, const float* lse, int64_t M, int D,
                 int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
-                float scale_log2, int64_t cols_per_split, float* __restrict__ acc_out,
+                float scale_log2, int64_t cols_per_split, int64_t cross_n, float* __restrict__ acc_out,
                 PeerWait lse_ready) {
     pdl_trigger();
     pdl_wait();
@@ -288,7 +289,8 @@ simt_bwd_kernel(const T* __restrict__ U, const float* lse, int64_t M, int D,
                 const int64_t col = b0 + tx * 4 + b;
                 const float t = acc[a][b] * scale_log2;
                 float w = 0.f;
-                if (col < b_hi && col != row && row < a_end) {
+                if (col < b_hi && col != row && row < a_end &&
+                    !(cross_n > 0 && ((col >= cross_n) == (row >= cross_n)))) {
                     if (MODE != kCol) w += exp2f(t - lrow[a]);
                     if (MODE != kRow) w += exp2f(t - lcol[tx * 4 + b]);
                 }
@@ -342,13 +344,13 @@ template <typename T>
 static cudaError_t launch_simt_bwd_t(const T* U, const float* lse, int64_t M, int64_t D,
                                      int64_t a_begin, int64_t a_count, int64_t b_begin,
                                      int64_t b_count, float tau, int mode, const SplitPlan& plan,
-                                     float* acc, const PeerWait& lse_ready, cudaStream_t stream) {
+                                     float* acc, const PeerWait& lse_ready, cudaStream_t stream, int64_t cross_n) {
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit, (unsigned)((D + kDC - 1) / kDC));
     dim3 block(256);
     const float sl2 = kLog2e / tau;
 #define NTX_SIMT_BWD(MODE)                                                                            \
     launch_kernel(simt_bwd_kernel<T, MODE>, grid, block, 0, stream, U, lse, M, (int)D, a_begin, a_count, \
-                  b_begin, b_count, sl2, plan.cols_per_split, acc, lse_ready)
+                  b_begin, b_count, sl2, plan.cols_per_split, cross_n, acc, lse_ready)
     switch (mode) {
         case kSym: return NTX_SIMT_BWD(kSym);
         case kRow: return NTX_SIMT_BWD(kRow);
@@ -360,13 +362,13 @@ static cudaError_t launch_simt_bwd_t(const T* U, const float* lse, int64_t M, in
 cudaError_t launch_simt_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M,
                             int64_t D, int64_t a_begin, int64_t a_count, int64_t b_begin,
                             int64_t b_count, float tau, int mode, const SplitPlan& plan, float* acc,
-                            const PeerWait& lse_ready, cudaStream_t stream) {
+                            const PeerWait& lse_ready, cudaStream_t stream, int64_t cross_n) {
     if (op_bf16)
         return launch_simt_bwd_t<__nv_bfloat16>((const __nv_bfloat16*)u_all, lse_all, M, D, a_begin,
                                                 a_count, b_begin, b_count, tau, mode, plan, acc,
-                                                lse_ready, stream);
+                                                lse_ready, stream, cross_n);
     return launch_simt_bwd_t<float>((const float*)u_all, lse_all, M, D, a_begin, a_count, b_begin,
-                                    b_count, tau, mode, plan, acc, lse_ready, stream);
+                                    b_count, tau, mode, plan, acc, lse_ready, stream, cross_n);
 }
 
 }  // namespace ntxent_b200

@@ -88,7 +88,7 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&v)[32], bool special,
 template <int D, bool TF32, bool kOnline>
 __global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
-              int64_t row_count, float k_scale, int tiles_per_split, int col_tiles,
+              int64_t row_count, float k_scale, int tiles_per_split, int col_tiles, int cross_half,
               float* __restrict__ part_m, float* __restrict__ part_s, PeerWait u_ready) {
     using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
@@ -115,15 +115,19 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
     //                        rows (which need no waiting) on through the ranks behind it, wrapping
     //                        around: every CTA starts on rows that are there already and meets the
     //                        peers' rows as late as possible, one rank after the other.
+    //   cross-view form   : (single device only) col_tiles = T/2 tiles, those of the OTHER view: the
+    //                        contiguous range shifted by cross_half = T/2 for the rows of view 1
     const bool rotated = u_ready.flags != nullptr;
     const int rot = rotated ? (int)((row_begin / kTile) % col_tiles) : 0;
-    const int jt0 = rotated ? (rot + (int)blockIdx.y) % col_tiles : (int)blockIdx.y * tiles_per_split;
+    const int jt_first = (int)blockIdx.y * tiles_per_split;
+    const int jt_shift = (cross_half > 0 && a0 < (int64_t)cross_half * kTile) ? cross_half : 0;
+    const int jt0 = rotated ? (rot + (int)blockIdx.y) % col_tiles : jt_first + jt_shift;
     const int jt_step = rotated ? (int)gridDim.y : 1;
     const int n_tiles = rotated ? (col_tiles - (int)blockIdx.y + jt_step - 1) / jt_step
-                                : min(tiles_per_split, col_tiles - jt0);
-    auto next_tile = [&](int jt) {  // (jt + jt_step) mod col_tiles; jt_step <= col_tiles
+                                : min(tiles_per_split, col_tiles - jt_first);
+    auto next_tile = [&](int jt) {  // rotated: (jt + jt_step) mod col_tiles, jt_step <= col_tiles
         jt += jt_step;
-        return jt >= col_tiles ? jt - col_tiles : jt;
+        return (rotated && jt >= col_tiles) ? jt - col_tiles : jt;
     };
 
     if (threadIdx.x == 0) {
@@ -466,7 +470,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
               const void* __restrict__ U_raw,
               const float* lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int col_tiles, int64_t total_tiles,
-              float* __restrict__ acc_out, unsigned long long* __restrict__ trace, PeerWait lse_ready) {
+              int cross_half, float* __restrict__ acc_out, unsigned long long* __restrict__ trace,
+              PeerWait lse_ready) {
     using C = Cfg<D, TF32>;
     using B = BwdCfg<D, TF32>;
     constexpr int NS = B::kStages;
@@ -497,7 +502,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     pdl_trigger();
     NTX_TRACE_U(63, 0, clock64());
     NTX_TRACE_U(63, 6, globaltimer_ns());
-    const int64_t a_end = a_begin + a_count, b_end = b_begin + b_count;
+    const int64_t a_end = a_begin + a_count;
+    // The B range of a unit.  Cross-view form (cross_half = T/2 > 0, b_count = M/2): the row tiles of
+    // view 1 take the columns of view 2 and the other way round; otherwise [b_begin, b_begin + b_count).
+    auto unit_b_begin = [&](int rt) -> int64_t {
+        if (cross_half > 0 && a_begin / kTile + rt < cross_half) return b_begin + (int64_t)cross_half * kTile;
+        return b_begin;
+    };
     const int ctas = (int)gridDim.x;
     const int64_t t_begin = (int64_t)blockIdx.x * total_tiles / ctas;
     const int64_t t_end = (int64_t)(blockIdx.x + 1) * total_tiles / ctas;
@@ -531,9 +542,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     if (warp == B::kTmaWarp) {
         if (lane == 0) {
             while (bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u)) {
+                const int64_t ub = unit_b_begin(u.rt);
                 for (int it = 0; it < u.n; ++it, ++g) {
                     const int st = g % NS;
-                    const int32_t col0 = (int32_t)(b_begin + (int64_t)(u.ct0 + it) * kTile);
+                    const int32_t col0 = (int32_t)(ub + (int64_t)(u.ct0 + it) * kTile);
                     mbar_wait(&k_empty[st], ((g / NS) & 1) ^ 1);
                     mbar_arrive_expect_tx(&k_full[st], C::kTileBytes);
                     for (int a = 0; a < C::kAtoms; ++a)
@@ -635,10 +647,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             unsigned want;
             unsigned ready_mask = peer_poll_all_warp(lse_ready, want);
             while (bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u)) {
+                const int64_t ub = unit_b_begin(u.rt), b_end = ub + b_count;
                 for (int it0 = 0; it0 < u.n; it0 += B::kCcTiles, ++cb) {
                     float* dst = colc + (cb & 1) * B::kCcTiles * kTile;
                     const int ncols = min(B::kCcTiles, u.n - it0) * kTile;
-                    const int64_t c0 = b_begin + (int64_t)(u.ct0 + it0) * kTile;
+                    const int64_t c0 = ub + (int64_t)(u.ct0 + it0) * kTile;
                     peer_wait_rows(lse_ready, c0, min(b_end, c0 + ncols), want, ready_mask);
                     mbar_wait(&cc_empty[cb & 1], ((cb >> 1) & 1) ^ 1);
                     // four columns per load, eight loads in flight per lane: two round trips per
@@ -744,7 +757,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             const int jt0 = u.ct0, n_tiles = u.n;
             // column tiles that need the masked weight path, as 32-bit tile numbers: those that
             // overlap this row tile's own rows (the diagonal) and a ragged last tile
-            const int64_t dd = a0 - b_begin;
+            const int64_t ub = unit_b_begin(u.rt), b_end = ub + b_count;
+            const int64_t dd = a0 - ub;
             const int jt_diag_lo = (int)(dd >= 0 ? dd / kTile : -((-dd + kTile - 1) / kTile));
             const int jt_diag_hi = (int)(dd >= 0 ? (dd + kTile - 1) / kTile : -((-dd) / kTile));
             const int jt_ragged = (b_count % kTile) ? col_tiles - 1 : -1;
@@ -765,7 +779,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                 const int pb = SEP ? (g & 1) : 0;
                 const int jt = jt0 + it;
                 const bool special = (jt >= jt_diag_lo && jt <= jt_diag_hi) || jt == jt_ragged;
-                const int64_t j0 = b_begin + (int64_t)jt * kTile;  // (used on the masked path only)
+                const int64_t j0 = ub + (int64_t)jt * kTile;  // (used on the masked path only)
                 if (MODE != kRow && (it % B::kCcTiles) == 0)  // the block staged by the constants warp
                     mbar_wait(&cc_full[cb & 1], (cb >> 1) & 1);
                 const float* cc = colc + ((cb & 1) * B::kCcTiles + it % B::kCcTiles) * kTile + quarter * 32;
@@ -928,7 +942,7 @@ cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtens
 
 template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
-                         float k_scale, const SplitPlan& plan, int col_tiles, float* part_m,
+                         float k_scale, const SplitPlan& plan, int col_tiles, int cross_half, float* part_m,
                          float* part_s, const PeerWait& u_ready, cudaStream_t stream) {
     using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
@@ -939,7 +953,7 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
     return launch_kernel(kern, grid, dim3(kThreads), smem, stream, tmap, M, row_begin, row_count, k_scale,
-                         (int)(plan.cols_per_split / kTile), col_tiles, part_m, part_s, u_ready);
+                         (int)(plan.cols_per_split / kTile), col_tiles, cross_half, part_m, part_s, u_ready);
 }
 
 // U [M, D] fp32 -> UT [D, Mpad] (Mpad = M rounded up to 4, pad columns zero): the K-major B operand
@@ -962,7 +976,7 @@ template <int D, bool TF32, int MODE, bool kTwoExp>
 cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, const void* u_all,
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
-                         float k_scale, const SplitPlan& plan, int col_tiles, float* acc,
+                         float k_scale, const SplitPlan& plan, int col_tiles, int cross_half, float* acc,
                          const PeerWait& lse_ready, cudaStream_t stream) {
     using B = BwdCfg<D, TF32>;
     const int smem = max(B::kSmem, 120 * 1024);
@@ -974,7 +988,7 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
     if (plan.sk_ctas < 1 || plan.sk_ctas > total_tiles) return cudaErrorInvalidValue;
     return launch_kernel(kern, dim3((unsigned)plan.sk_ctas), dim3(B::kThreads), smem, stream, tmap, tmap_t,
                          u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, col_tiles, total_tiles,
-                         acc, g_trace, lse_ready);
+                         cross_half, acc, g_trace, lse_ready);
 }
 
 template <int D, bool TF32>
@@ -982,10 +996,10 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, int mode, bool two_exp, const SplitPlan& plan, int col_tiles,
-                         float* acc, const PeerWait& lse_ready, cudaStream_t stream) {
+                         int cross_half, float* acc, const PeerWait& lse_ready, cudaStream_t stream) {
 #define NTX_BWD(MODE, TWO)                                                                               \
     launch_bwd_t<D, TF32, MODE, TWO>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, \
-                                     plan, col_tiles, acc, lse_ready, stream)
+                                     plan, col_tiles, cross_half, acc, lse_ready, stream)
     if (mode == kRow) return NTX_BWD(kRow, false);
     if (mode == kCol) return NTX_BWD(kCol, false);
     return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
@@ -1088,18 +1102,21 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, const PeerWait& u_ready,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, bool cross_view) {
     CUtensorMap tmap;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
     const float k_scale = kLog2e / tau;
     const bool online = (flags & 4u) || k_scale > kFixedMaxLimit;
-    const int col_tiles = (int)((M + kTile - 1) / kTile);
+    // cross-view form: every row tile walks the T/2 tiles of the other view (M/2 a multiple of 128)
+    if (cross_view && ((M / 2) % kTile != 0 || u_ready.flags)) return cudaErrorInvalidValue;
+    const int cross_half = cross_view ? (int)(M / 2 / kTile) : 0;
+    const int col_tiles = cross_view ? cross_half : (int)((M + kTile - 1) / kTile);
 #define NTX_FWD(DD, TF)                                                                                    \
-    (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m,  \
-                                         part_s, u_ready, stream)                                          \
-            : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, part_m, \
-                                          part_s, u_ready, stream))
+    (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, cross_half,  \
+                                         part_m, part_s, u_ready, stream)                                      \
+            : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, cross_half, \
+                                          part_m, part_s, u_ready, stream))
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_FWD(64, true);
@@ -1120,7 +1137,11 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream) {
+                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream, bool cross_view) {
+    // cross-view form: the caller passes b_begin = 0, b_count = M/2 (a multiple of 128) and mode kSym
+    if (cross_view && ((M / 2) % kTile != 0 || b_begin != 0 || b_count != M / 2 || mode != kSym || lse_ready.flags))
+        return cudaErrorInvalidValue;
+    const int cross_half = cross_view ? (int)(M / 2 / kTile) : 0;
     CUtensorMap tmap, tmap_t;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
@@ -1140,7 +1161,7 @@ cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all,
     const int col_tiles = (int)((b_count + kTile - 1) / kTile);
 #define NTX_BWD_D(DD, TF)                                                                                   \
     launch_bwd_d<DD, TF>(tmap, tmap_t, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, \
-                         two_exp, plan, col_tiles, acc, lse_ready, stream)
+                         two_exp, plan, col_tiles, cross_half, acc, lse_ready, stream)
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_BWD_D(64, true);

@@ -14,12 +14,13 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, const PeerWait& u_ready,
-                          cudaStream_t stream);
+                          cudaStream_t stream, bool cross_view = false);
 
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream);
+                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream,
+                          bool cross_view = false);
 
 // ---- forward over the upper triangle (tc_fwd_sym.cu): whole-batch calls on one device, bf16
 // operands, fixed-max regime (log2(e)/tau <= 50), M >= kSymMinRows.

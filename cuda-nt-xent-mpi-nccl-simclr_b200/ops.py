@@ -51,17 +51,17 @@ def backward(z: torch.Tensor, softmax: torch.Tensor, grad_out: torch.Tensor, T: 
 
 class _NTXentFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, z, T, use_mixed_precision):
-        loss, lse = capi.forward(z.detach(), T, use_mixed_precision)
+    def forward(ctx, z, T, use_mixed_precision, flags=0):
+        loss, lse = capi.forward(z.detach(), T, use_mixed_precision, flags)
         ctx.save_for_backward(z.detach(), lse)
-        ctx.T, ctx.mp = T, use_mixed_precision
+        ctx.T, ctx.mp, ctx.flags = T, use_mixed_precision, flags
         return loss
 
     @staticmethod
     def backward(ctx, grad_loss):
         z, lse = ctx.saved_tensors
-        dz, _ = capi.backward(z, lse, grad_loss, ctx.T, ctx.mp, want_pos_prob=False)
-        return dz, None, None
+        dz, _ = capi.backward(z, lse, grad_loss, ctx.T, ctx.mp, ctx.flags, want_pos_prob=False)
+        return dz, None, None, None
 
 
 class _NTXentLearnableTauFunction(torch.autograd.Function):
@@ -147,6 +147,22 @@ def ntxent_loss(z: torch.Tensor, temperature: float = 0.07,
             return _NTXentLearnableTauFunction.apply(z, temperature, use_mixed_precision).squeeze(0)
         temperature = float(temperature)
     return forward(z, temperature, use_mixed_precision).squeeze(0)
+
+
+def two_tower_loss(q: torch.Tensor, k: torch.Tensor, temperature: float = 0.07,
+                   use_mixed_precision: bool = False) -> torch.Tensor:
+    """Symmetric InfoNCE between two towers (CLIP's loss; SURVEY.md section 8 f4, "Q != K"):
+    (CE(q k^T / T, diag) + CE(k q^T / T, diag)) / 2 over L2-normalised rows, q[i] and k[i] being
+    the positive pair.  It is NT-Xent over the stacked [q; k] with the denominators restricted to
+    the other tower (NTXENT_FLAG_CROSS_VIEW), so it runs on the same kernels, visiting only the
+    cross-tower tiles.  0-dim, differentiable in q and k."""
+    if q.shape != k.shape or q.dim() != 2:
+        raise capi.NTXentError(f"two_tower_loss expects two [N, D] tensors of one shape, got {tuple(q.shape)} "
+                               f"and {tuple(k.shape)}")
+    z = torch.cat([q, k], dim=0)
+    if z.requires_grad and torch.is_grad_enabled():
+        return _NTXentFunction.apply(z, float(temperature), bool(use_mixed_precision), capi.FLAG_CROSS_VIEW).squeeze(0)
+    return capi.forward(z, float(temperature), use_mixed_precision, capi.FLAG_CROSS_VIEW)[0].squeeze(0)
 
 
 class NTXentLoss(torch.nn.Module):

@@ -42,6 +42,15 @@ enum { NTXENT_F32 = 0, NTXENT_BF16 = 1 };
 #define NTXENT_FLAG_MIXED_PRECISION 1u /* bf16 operands even for fp32 z                         */
 #define NTXENT_FLAG_FORCE_SIMT      2u /* run the fp32-FMA tile kernels instead of tcgen05      */
 #define NTXENT_FLAG_ONLINE_MAX      4u /* force the running-max logsumexp (default: automatic)  */
+#define NTXENT_FLAG_CROSS_VIEW      8u /* the denominators run over the OTHER view only: row i of
+                                          view 1 (rows 0..N-1) against the N rows of view 2 and the
+                                          other way round.  With z = [q; k] this is the symmetric
+                                          two-tower InfoNCE (CLIP):  (L(q->k) + L(k->q)) / 2  -- the
+                                          SURVEY.md section 8 f4 "Q != K" variant; no counterpart in
+                                          the reference.  Single-device entry points only (forward,
+                                          backward, forward_backward and their _pos / _tau / _static
+                                          forms); tcgen05 tiles when N is a multiple of 128, the
+                                          fp32-FMA tiles otherwise                                */
 
 #define NTXENT_OK                    0
 #define NTXENT_ERR_INVALID_ARGUMENT (-1)

@@ -56,9 +56,9 @@ def lib() -> ctypes.CDLL:
                                                  fp, fp, fp, fp]
         L.ntxent_oracle_rowblock_f32.restype = ctypes.c_int
         ip64 = ctypes.POINTER(ctypes.c_int64)
-        L.ntxent_oracle_forward_pos_f64.argtypes = [dp, ip64, i64, i64, ctypes.c_double, dp, dp]
+        L.ntxent_oracle_forward_pos_f64.argtypes = [dp, ip64, i64, i64, i64, ctypes.c_double, dp, dp]
         L.ntxent_oracle_forward_pos_f64.restype = ctypes.c_int
-        L.ntxent_oracle_backward_pos_f64.argtypes = [dp, ip64, dp, ctypes.c_double, i64, i64, ctypes.c_double, dp]
+        L.ntxent_oracle_backward_pos_f64.argtypes = [dp, ip64, i64, dp, ctypes.c_double, i64, i64, ctypes.c_double, dp]
         L.ntxent_oracle_backward_pos_f64.restype = ctypes.c_int
         L.ntxent_literal_reference_forward_f64.argtypes = [dp, i64, i64, ctypes.c_double, dp]
         L.ntxent_literal_reference_forward_f64.restype = ctypes.c_int
@@ -130,21 +130,28 @@ def forward_backward(z, tau: float, grad_out: float = 1.0):
     return loss, lse, dz
 
 
-def forward_backward_pos(z, pos, tau: float, grad_out: float = 1.0):
+def forward_backward_pos(z, pos, tau: float, grad_out: float = 1.0, cross_n: int = 0):
     """fp64 loss / l / dz with the positive of row i given by pos[i].
+    cross_n > 0: denominators over the other view only (rows < cross_n against rows >= cross_n).
     Returns (loss, lse[M], dz[M,D])."""
     z = np.ascontiguousarray(z, dtype=np.float64)
     pos = np.ascontiguousarray(pos, dtype=np.int64)
     M, D = z.shape
     loss, lse, dz = np.zeros(1), np.zeros(M), np.zeros((M, D))
     ip = pos.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))
-    rc = lib().ntxent_oracle_forward_pos_f64(_dptr(z), ip, M, D, float(tau), _dptr(loss), _dptr(lse))
+    rc = lib().ntxent_oracle_forward_pos_f64(_dptr(z), ip, int(cross_n), M, D, float(tau), _dptr(loss), _dptr(lse))
     if rc == 0:
-        rc = lib().ntxent_oracle_backward_pos_f64(_dptr(z), ip, _dptr(lse), float(grad_out), M, D, float(tau),
+        rc = lib().ntxent_oracle_backward_pos_f64(_dptr(z), ip, int(cross_n), _dptr(lse), float(grad_out), M, D, float(tau),
                                                   _dptr(dz))
     if rc != 0:
         raise ValueError(f"ntxent_oracle_*_pos_f64 rc={rc}")
     return float(loss[0]), lse, dz
+
+
+def forward_backward_cross(z, tau: float, grad_out: float = 1.0):
+    """fp64 symmetric two-tower InfoNCE over the stacked [q; k] rows (the cross-view form of NT-Xent)."""
+    M = np.asarray(z).shape[0]
+    return forward_backward_pos(z, (np.arange(M) + M // 2) % M, tau, grad_out, cross_n=M // 2)
 
 
 def rowblock_f32(z, tau: float, row_begin: int, row_count: int):
@@ -180,10 +187,13 @@ def literal_reference_forward(z, T: float) -> float:
 # --------------------------------------------------------------------------
 # Independent numpy restatement (dense, fp64, small cases only).
 # --------------------------------------------------------------------------
-def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e-12, pos=None):
+def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e-12, pos=None,
+                           cross_view: bool = False):
     """Dense numpy fp64 NT-Xent.  Returns dict(loss, lse, dz, dU, pos_prob, dtau, ...); dtau is
     d loss / d tau = -(1/tau) sum_ij G_ij S_ij.  `pos`: the positive of
-    every row as an index vector (default (i + N) mod M)."""
+    every row as an index vector (default (i + N) mod M).  `cross_view`: the denominators run over
+    the OTHER view only (rows 0..N-1 against N..2N-1 and back): the symmetric two-tower InfoNCE of
+    CLIP, (L(q->k) + L(k->q)) / 2 with q = rows 0..N-1 and k = rows N..2N-1."""
     z = np.asarray(z, dtype=np.float64)
     M, D = z.shape
     assert M % 2 == 0 or pos is not None
@@ -195,6 +205,9 @@ def numpy_forward_backward(z, tau: float, grad_out: float = 1.0, eps: float = 1e
     pos = (idx + N) % M if pos is None else np.asarray(pos, dtype=np.int64)
     Sm = S.copy()
     Sm[idx, idx] = -np.inf
+    if cross_view:
+        same = (idx[:, None] >= N) == (idx[None, :] >= N)
+        Sm[same] = -np.inf
     mx = Sm.max(axis=1, keepdims=True)
     lse = (mx + np.log(np.exp(Sm - mx).sum(axis=1, keepdims=True)))[:, 0]
     loss = float(np.mean(lse - S[idx, pos]))

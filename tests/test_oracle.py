@@ -208,3 +208,26 @@ def test_arbitrary_positives_c_against_numpy_and_finite_differences(oracle):
         assert 1.5 * fd == pytest.approx(dz[i, k], abs=1e-8)
     with pytest.raises(ValueError):
         oracle.forward_backward_pos(z, np.arange(M), tau)  # a row cannot be its own positive
+
+
+def test_cross_view_is_the_symmetric_two_tower_infonce(oracle):
+    """cross_n: the denominators over the other view only.  Against the CLIP formula written out,
+    against the numpy restatement, and by finite differences."""
+    rng = np.random.default_rng(5)
+    N, D, tau = 10, 7, 0.25
+    z = rng.standard_normal((2 * N, D))
+    loss, lse, dz = oracle.forward_backward_cross(z, tau, 0.5)
+    u = z / np.linalg.norm(z, axis=1, keepdims=True)
+    L = u[:N] @ u[N:].T / tau
+    ce = lambda A: np.mean(np.log(np.exp(A).sum(1)) - np.diag(A))  # noqa: E731
+    assert loss == pytest.approx((ce(L) + ce(L.T)) / 2, rel=1e-12)
+    ref = oracle.numpy_forward_backward(z, tau, 0.5, cross_view=True)
+    assert loss == pytest.approx(ref["loss"], rel=1e-12)
+    np.testing.assert_allclose(dz, ref["dz"], rtol=0, atol=1e-13)
+    eps = 1e-6
+    for i, k in ((0, 0), (4, 3), (13, 6)):
+        zp, zm = z.copy(), z.copy()
+        zp[i, k] += eps
+        zm[i, k] -= eps
+        fd = (oracle.forward_backward_cross(zp, tau)[0] - oracle.forward_backward_cross(zm, tau)[0]) / (2 * eps)
+        assert 0.5 * fd == pytest.approx(dz[i, k], abs=1e-8)

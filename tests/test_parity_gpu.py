@@ -404,6 +404,36 @@ def test_arbitrary_positives(oracle, M, D, tau, dtype):
     assert dz_err(za.grad.double().cpu().numpy(), dz.double().cpu().numpy()) <= (2.0 ** -7 if bf else 1e-6)
 
 
+@pytest.mark.parametrize("N,D,tau,dtype,flags", [
+    (50, 64, 0.2, torch.float32, 0),                      # ragged N: the fp32-FMA tiles with the mask
+    (256, 128, 0.07, torch.float32, capi.FLAG_FORCE_SIMT),
+    (1024, 128, 0.5, torch.float32, 0),                   # tf32 tiles, cross-tower tiles only
+    (1024, 128, 0.1, torch.bfloat16, 0), (2048, 256, 0.07, torch.bfloat16, 0), (4096, 128, 0.1, torch.bfloat16, 0)])
+def test_cross_view_two_tower(oracle, N, D, tau, dtype, flags):
+    """SURVEY.md section 8 f4, "Q != K": NTXENT_FLAG_CROSS_VIEW = the symmetric two-tower InfoNCE over
+    z = [q; k], against the fp64 oracle (itself checked against the CLIP formula written out)."""
+    M = 2 * N
+    z_t = dev(seeded_z(M, D, seed=N + 3), dtype)
+    fl = flags | capi.FLAG_CROSS_VIEW
+    g = torch.tensor([1.25], device="cuda")
+    loss, lse = capi.forward(z_t, tau, False, fl)
+    dz, _ = capi.backward(z_t, lse, g, tau, False, fl)
+    l2, lse2, dz2 = capi.forward_backward(z_t, tau, g, False, fl)
+    torch.cuda.synchronize()
+    assert torch.equal(dz, dz2) and torch.equal(lse, lse2)
+    rl, rlse, rdz = oracle.forward_backward_cross(z_t.double().cpu().numpy(), tau, 1.25)
+    bf = dtype == torch.bfloat16
+    assert loss.item() == pytest.approx(rl, rel=LOSS_RTOL_BF16 if bf else LOSS_RTOL_F32)
+    np.testing.assert_allclose(lse.double().cpu().numpy(), rlse, rtol=0, atol=5e-3 if bf else 2e-5)
+    assert dz_err(dz.double().cpu().numpy(), rdz) <= (dz_tol_bf16(tau) if bf else DZ_TOL_F32)
+    # the two-tower front end, under autograd
+    q = z_t[:N].clone().requires_grad_(True)
+    k = z_t[N:].clone().requires_grad_(True)
+    (ntxent_b200.two_tower_loss(q, k, tau) * 1.25).backward()
+    got = torch.cat([q.grad, k.grad]).double().cpu().numpy()
+    assert dz_err(got, dz.double().cpu().numpy()) <= (2.0 ** -7 if bf else 1e-6)
+
+
 def test_fused_equals_separate_and_is_deterministic():
     z_t = dev(seeded_z(1024, 128, seed=5), torch.bfloat16)
     loss, lse = capi.forward(z_t, 0.1)
