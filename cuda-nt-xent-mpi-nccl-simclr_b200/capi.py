@@ -57,7 +57,8 @@ class PeerList(ctypes.Structure):
 
 class PeerSignal(ctypes.Structure):
     """ntxent_peer_signal: where a producing call publishes its call number on every rank."""
-    _fields_ = [("flags", PeerList), ("epoch", ctypes.c_void_p), ("rank", ctypes.c_int)]
+    _fields_ = [("flags", PeerList), ("epoch", ctypes.c_void_p), ("rank", ctypes.c_int),
+                ("ticket", ctypes.c_void_p)]
 
 
 class PeerWait(ctypes.Structure):
@@ -139,7 +140,7 @@ def lib() -> ctypes.CDLL:
     L.ntxent_b200_set_peer_wait_timeout_ms.argtypes = [ctypes.c_uint64]
     L.ntxent_b200_backward_rows_dz.restype = ci
     L.ntxent_b200_backward_rows_dz.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, u32, vp, sz, vp, vp, vp,
-                                               vp, pw, vp]
+                                               vp, pw, vp, ci, vp, vp]
     L.ntxent_b200_backward_rows_part.restype = ci
     L.ntxent_b200_backward_rows_part.argtypes = [vp, vp, i64, i64, i64, i64, f32, ci, ci, u32, vp, sz, vp, vp]
     vpp, i64p = ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int64)
@@ -507,7 +508,7 @@ def backward_rows_dz(u_all: torch.Tensor, lse_all: torch.Tensor, row_begin: int,
         check(lib().ntxent_b200_backward_rows_dz(_ptr(u_all), _ptr(lse_all), M, D, row_begin, row_count,
                                                  float(tau), _dtype_code(z_rows), flags, _ptr(ws), ws.numel(),
                                                  _ptr(z_rows), _ptr(inv_norm), _ptr(grad_out), _ptr(dz),
-                                                 _ref(lse_ready), _stream()))
+                                                 _ref(lse_ready), None, 0, None, _stream()))
     return dz
 
 

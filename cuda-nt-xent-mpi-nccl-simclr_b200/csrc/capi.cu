@@ -145,8 +145,9 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
 }
 
 struct RowsWs {
-    float* pos_t;  // positive logits captured by the tcgen05 forward tile kernel (base-2 units)
+    float* pos_t;  // positive logits (base-2 units): captured by the upper-triangle forward, or dot products
     float* block_partials;
+    unsigned* counter;  // ticket of the fused forward finalize (whole-batch calls: zeroed by normalise)
     float* part_m;
     float* part_s;
     float* acc_rows;
@@ -168,6 +169,7 @@ RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Pla
     };
     w.pos_t = (float*)take(sizeof(float) * (size_t)row_count);
     w.block_partials = (float*)take(sizeof(float) * (size_t)((row_count + 7) / 8));
+    w.counter = (unsigned*)take(kAlign);
     w.part_m = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.part_s = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.acc_rows = (float*)take(sizeof(float) * (size_t)p.bwd_rows.nsplit * row_count * D);
@@ -248,7 +250,8 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                           int64_t row_count, float tau, const Plans& p, const RowsWs& w,
                           const PeerList& lse_outs, int64_t lse_offset, const PeerList& loss_outs,
                           int loss_index, float loss_scale, const PeerWait& u_ready,
-                          const PeerSignal& lse_signal, cudaStream_t st, const int* pos_index = nullptr) {
+                          const PeerSignal& lse_signal, cudaStream_t st, const int* pos_index = nullptr,
+                          unsigned* counter = nullptr) {
     g_timer.start(0, st);
     if (p.tc)
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
@@ -259,16 +262,17 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     g_timer.stop(0, st);
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
                                      w.part_s, w.pos_t, pos_index, lse_outs, lse_offset, w.block_partials,
-                                     loss_outs, loss_index, loss_scale, lse_signal, st));
+                                     loss_outs, loss_index, loss_scale, lse_signal, st, counter));
     return NTXENT_OK;
 }
 
 int run_forward_rows(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                      int64_t row_count, float tau, const Plans& p, const RowsWs& w, float* lse_rows,
-                     float* loss_out, float loss_scale, cudaStream_t st, const int* pos_index = nullptr) {
+                     float* loss_out, float loss_scale, cudaStream_t st, const int* pos_index = nullptr,
+                     unsigned* counter = nullptr) {
     return run_forward_rows_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p, w,
                                  single_peer(lse_rows), 0, single_peer(loss_out), 0, loss_scale, no_wait(),
-                                 no_signal(), st, pos_index);
+                                 no_signal(), st, pos_index, counter);
 }
 
 // Forward of the whole batch on one device: over the upper triangle where that applies
@@ -278,15 +282,13 @@ int run_forward_device(const void* U, bool op_bf16, int64_t M, int64_t D, float 
                        const int* pos_index = nullptr) {
     if (!p.sym)
         return run_forward_rows(U, op_bf16, M, D, 0, M, tau, p, w, lse_out, loss_out, 1.0f / (float)M, st,
-                                pos_index);
+                                pos_index, w.counter);
     g_timer.start(0, st);
     NTX_TRY(tc_launch_fwd_sym(U, M, D, tau, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, st));
     g_timer.stop(0, st);
     if (pos_index) NTX_TRY(launch_pos_dot(U, op_bf16, M, D, 0, M, pos_index, kLog2e / tau, w.pos_t, st));
-    NTX_TRY(tc_launch_fwd_sym_finalize(M, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, lse_out, w.block_partials,
-                                       st));
-    NTX_TRY(launch_loss_reduce(w.block_partials, p.symp.T, single_peer(loss_out), 0, 1.0f / (float)M, no_signal(),
-                               st));
+    NTX_TRY(tc_launch_fwd_sym_finalize(M, p.symp, w.sym_part_s, w.sym_cpart, w.pos_t, lse_out, w.block_partials, st,
+                                       w.counter, loss_out, 1.0f / (float)M));
     return NTXENT_OK;
 }
 
@@ -312,6 +314,7 @@ bool to_peer_signal(const ntxent_peer_signal* in, PeerSignal* out) {
         return false;
     out->epoch = in->epoch;
     out->rank = in->rank;
+    out->ticket = in->ticket;
     return true;
 }
 // How long a kernel waits for a peer's flag before it gives up (ntxent_b200_set_peer_wait_timeout_ms).
@@ -572,7 +575,7 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
     return run_forward_rows_push(u_all, opb, M, D, row_begin, row_count, tau, p, w, lse_outs, row_begin,
-                                 loss_outs, loss_index, 1.0f, wait, sig, stream);
+                                 loss_outs, loss_index, 1.0f, wait, sig, stream, nullptr, sig.ticket);
 }
 
 int ntxent_b200_set_peer_wait_timeout_ms(uint64_t milliseconds) {
@@ -592,6 +595,7 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
                                  unsigned flags, void* workspace, size_t workspace_bytes,
                                  const void* z_rows, const float* inv_norm_rows, const float* grad_out,
                                  void* dz_out, const ntxent_peer_wait* lse_ready,
+                                 const float* loss_parts, int loss_parts_count, float* loss_out,
                                  ntxent_stream_t stream) {
     PeerWait wait{};
     if (!u_all || !lse_all || !workspace || !z_rows || !inv_norm_rows || !dz_out ||
@@ -621,6 +625,10 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
     e.scale = 1.0f / (tau * (float)M);
     e.du_out = nullptr; e.z_rows = z_rows; e.z_bf16 = (dtype == NTXENT_BF16); e.inv_norm = inv_norm_rows;
     e.grad_out = grad_out; e.dz_out = dz_out;
+    if (loss_out) {
+        if (!loss_parts || loss_parts_count < 1 || loss_parts_count > kMaxPeers) return NTXENT_ERR_INVALID_ARGUMENT;
+        e.loss_parts = loss_parts; e.loss_n = loss_parts_count; e.loss_scale = 1.0f / (float)M; e.loss_out = loss_out;
+    }
     NTX_TRY(launch_bwd_epilogue(e, stream));
     return NTXENT_OK;
 }
@@ -637,7 +645,7 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     return run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
 }
 
@@ -654,7 +662,7 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                pos_prob_out, stream);
 }
@@ -672,7 +680,7 @@ int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                nullptr, stream, tau_grad_rows_out);
 }
@@ -690,7 +698,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
     if (rc != NTXENT_OK) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p,
@@ -712,7 +720,7 @@ int ntxent_b200_forward_backward_pos(const void* z, const int32_t* pos, const in
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream, pos);
     if (rc != NTXENT_OK || !dz_out) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p, dz_out, nullptr,
@@ -891,7 +899,7 @@ extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, f
     const DeviceWs w = carve_device(base, M, D, opb, p);
     // Nothing in the array has to start at zero: every region is written before it is read, so
     // whatever the previous call left behind is harmless.
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
     return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
                             1.0f / (float)M, stream);
 }

@@ -107,8 +107,9 @@ inline bool debug_on() {
 constexpr size_t kAl = 256;
 inline size_t al(size_t n) { return (n + kAl - 1) / kAl * kAl; }
 
-// sync block of a buffer set (256 bytes): flag_u[16] | flag_lse[16] | epoch_u | . | epoch_lse | . | status
-constexpr size_t kOffFlagU = 0, kOffFlagLse = 64, kOffEpochU = 128, kOffEpochLse = 136, kOffStatus = 144;
+// sync block of a buffer set (256 bytes): flag_u[16] | flag_lse[16] | epoch_u | . | epoch_lse | . | status | . | ticket
+constexpr size_t kOffFlagU = 0, kOffFlagLse = 64, kOffEpochU = 128, kOffEpochLse = 136, kOffStatus = 144,
+                 kOffTicket = 152;
 
 }  // namespace
 }  // namespace ntxent_b200
@@ -402,6 +403,7 @@ SetView view_of(const ntxent_comm* c, int k) {
     v.sig_u.rank = c->rank;
     v.sig_lse.epoch = (uint32_t*)(sync + kOffEpochLse);
     v.sig_lse.rank = c->rank;
+    v.sig_lse.ticket = (uint32_t*)(sync + kOffTicket);
     v.wait_u.flags = (const uint32_t*)(sync + kOffFlagU);
     v.wait_u.epoch = (const uint32_t*)(sync + kOffEpochU);
     v.wait_lse.flags = (const uint32_t*)(sync + kOffFlagLse);
@@ -412,8 +414,8 @@ SetView view_of(const ntxent_comm* c, int k) {
     return v;
 }
 
-// PUSH: normalise -> (flags) -> forward tiles -> finalize -> (flags) -> backward tiles -> epilogue;
-// seven launches, no collective.  Two buffer sets alternate so that a fast rank's step t+1 never
+// PUSH: normalise -> signal -> forward tiles (wait flags) -> fused finalize (signal) -> backward tiles
+// (wait flags) -> epilogue: six launches, no collective.  Two buffer sets alternate so that a fast rank's step t+1 never
 // lands in what a slow rank still reads for step t.
 int step_push(ntxent_comm* c, const void* z, const float* g, float tau, float* loss_out, void* dz_out,
               cudaStream_t st) {
@@ -425,12 +427,11 @@ int step_push(ntxent_comm* c, const void* z, const float* g, float tau, float* l
     NTX_RC(ntxent_b200_forward_rows_push(v.u_all, c->M, c->D, c->row_begin, c->rows, tau, c->op_dtype, c->flags,
                                          c->ws, c->ws_bytes, &v.lse_peers, &v.loss_peers, c->rank,
                                          multi ? &v.wait_u : nullptr, multi ? &v.sig_lse : nullptr, st));
+    // (the backward tile kernel waits for every rank's l, hence for every partial loss: its
+    // epilogue sums them)
     NTX_RC(ntxent_b200_backward_rows_dz(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
                                         c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out,
-                                        multi ? &v.wait_lse : nullptr, st));
-    // the backward tile kernel has waited for every rank's l, hence for every partial loss
-    NTX_CUDA(launch_kernel(loss_sum_kernel, dim3(1), dim3(32), 0, st, (const float*)v.loss_parts, c->nranks,
-                           1.0f / (float)c->M, loss_out));
+                                        multi ? &v.wait_lse : nullptr, v.loss_parts, c->nranks, loss_out, st));
     return NTXENT_OK;
 }
 
@@ -458,7 +459,8 @@ int step_nccl(ntxent_comm* c, const void* z, const float* g, float tau, int bwd_
     if (bwd_mode == NTXENT_BWD_SYMMETRIC) {
         if (multi) NTX_NCCL(n.AllGather(lse_mine, v.lse_all, (size_t)c->rows, ncclFloat32, c->nccl_comm, st));
         NTX_RC(ntxent_b200_backward_rows_dz(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
-                                            c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out, nullptr, st));
+                                            c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out, nullptr,
+                                            nullptr, 0, nullptr, st));
     } else {
         // contract form: column term of every global row first, its reduce-scatter on the second
         // stream while the row term is computed on the first

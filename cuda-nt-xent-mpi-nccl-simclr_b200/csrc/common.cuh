@@ -41,6 +41,7 @@ struct PeerSignal {
     PeerList flags;         // uint32 flag array [kMaxPeers] on every rank (this rank's own included)
     unsigned* epoch;        // local call counter; nullptr: no signalling
     int rank;
+    unsigned* ticket;       // optional ticket counter for the fused forward finalize
 };
 struct PeerWait {
     const unsigned* flags;  // this rank's flag array; nullptr: no waiting
@@ -77,12 +78,15 @@ SplitPlan plan_splits(int64_t a_count, int64_t b_count, int row_tile, int col_ti
 int device_sm_count();  // SM count of the current device; 148 when there is none
 
 // ---- launchers (all asynchronous on `stream`; return the launch status) ----------
+// zero_word (optional): a device word the kernel sets to zero -- the ticket counter of the fused
+// forward finalize, cleared by the kernel that starts every whole-batch call.
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
-                             bool op_bf16, float* inv_norm, cudaStream_t stream);
+                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_word = nullptr);
 // Same, storing the rows at row `row_offset` of every buffer in `outs`.
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
-                                  float* inv_norm, const PeerSignal& signal, cudaStream_t stream);
+                                  float* inv_norm, const PeerSignal& signal, cudaStream_t stream,
+                                  unsigned* zero_word = nullptr);
 
 // SIMT (fp32 FMA) tile kernels.
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
@@ -100,13 +104,15 @@ cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream);
 // (i + M/2) mod M) into pos_t [row_count], then the split partials combined into l_i, the positive
 // logit subtracted, the loss reduced.  l_i goes to element lse_offset + i of every buffer in
 // `lse_outs`, the (scaled) loss to element loss_index of every buffer in `loss_outs` (one buffer
-// each on a single device).
+// each on a single device).  `counter`: a device word that is zero before the first call (and
+// again after every call): with it the three kernels of this step run as one (a last-block ticket
+// replaces the kernel boundaries); without it they are launched one after the other.
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
                                      const float* part_m, const float* part_s, float* pos_t, const int* pos_index,
                                      const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
                                      const PeerList& loss_outs, int loss_index, float loss_scale,
-                                     const PeerSignal& signal, cudaStream_t stream);
+                                     const PeerSignal& signal, cudaStream_t stream, unsigned* counter = nullptr);
 
 // The loss: n per-CTA partials summed by one CTA in a fixed order, scaled, stored to element
 // loss_index of every buffer in `loss_outs` (and, multi-GPU push path, published with `signal`).
@@ -147,6 +153,13 @@ struct BwdEpilogueArgs {
     const int* pos_index;
     const int* inv_ptr;
     const int* inv_idx;
+    // optional: loss_out[0] = loss_scale * (loss_parts[0] + ... + loss_parts[loss_n - 1]), by one thread
+    // of the grid -- the global loss of the push path, whose parts are all there once the backward
+    // tile kernel has run (it waited for every rank's flag)
+    const float* loss_parts;
+    int loss_n;
+    float loss_scale;
+    float* loss_out;
     // optional per-row temperature gradient (output B only): -(dU_a . u_a) / (2 tau); its sum
     // over all rows, times grad_out, is d loss / d tau
     float* tau_grad_rows_out;  // [a_count] or nullptr

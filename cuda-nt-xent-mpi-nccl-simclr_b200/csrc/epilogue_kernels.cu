@@ -98,12 +98,123 @@ cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream) {
     return launch_kernel(peer_wait_kernel, dim3(1), dim3(32), 0, stream, wait);
 }
 
+// Everything after the forward tile pass in ONE kernel, for callers that can give it a ticket
+// counter (a device word that is zero before the first call; it leaves every call at zero again):
+// a warp per four rows forms the positive logit (fp32 dot of the operand rows), merges the row's
+// split partials, stores l_i (to every peer), and the last block to finish -- known by the ticket
+// it draws after a system-scope fence -- sums the per-block loss partials in a fixed order, stores
+// the loss and publishes the signal.  Replaces pos_dot + finalize_rows + loss_reduce: three
+// launches on the critical path of a 0.16 ms multi-GPU step.
+constexpr int kFusedRowsPerWarp = 4, kFusedRowsPerCta = 8 * kFusedRowsPerWarp;
+template <typename T>
+__global__ void __launch_bounds__(256)
+fwd_finalize_fused_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
+                          float k_scale, int nsplit, const float* __restrict__ part_m,
+                          const float* __restrict__ part_s, const int* __restrict__ pos_index,
+                          PeerList lse_outs, int64_t lse_offset, float* __restrict__ block_partials,
+                          unsigned* __restrict__ counter, PeerList loss_outs, int loss_index,
+                          float loss_scale, PeerSignal signal) {
+    __shared__ float warp_contrib[8];
+    __shared__ unsigned ticket_s;
+    __shared__ double red[256];
+    pdl_trigger();
+    pdl_wait();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * kFusedRowsPerCta + warp * kFusedRowsPerWarp;
+    float m[kFusedRowsPerWarp], s[kFusedRowsPerWarp], dot[kFusedRowsPerWarp];
+    // all loads of the warp's four rows are issued before any of them is consumed
+#pragma unroll
+    for (int q = 0; q < kFusedRowsPerWarp; ++q) {
+        const int64_t r = r0 + q;
+        m[q] = -INFINITY; s[q] = 0.f; dot[q] = 0.f;
+        if (r < row_count) {
+            for (int sp = lane; sp < nsplit; sp += 32)
+                lse2_merge(m[q], s[q], part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
+            const int64_t row = row_begin + r;
+            const int64_t pi = pos_index ? (int64_t)pos_index[row] : (row + M / 2) % M;
+            const T* ui = U + row * D;
+            const T* up = U + pi * D;
+            for (int k = lane * 4; k < D; k += 128) {
+                const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
+                dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+            }
+        }
+    }
+    float contrib = 0.f;
+#pragma unroll
+    for (int q = 0; q < kFusedRowsPerWarp; ++q) {
+        const int64_t r = r0 + q;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[q], o);
+            const float s2 = __shfl_xor_sync(0xffffffffu, s[q], o);
+            lse2_merge(m[q], s[q], m2, s2);
+        }
+        const float d = warp_sum(dot[q]);
+        if (r < row_count) {
+            const float l2 = m[q] + log2f(s[q]);
+            const float l = l2 * kLn2;
+            if (lane < lse_outs.n) static_cast<float*>(lse_outs.p[lane])[lse_offset + r] = l;  // lane i serves peer i
+            contrib += (l2 - d * k_scale) * kLn2;
+        }
+    }
+    if (lane == 0) warp_contrib[warp] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float bsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) bsum += warp_contrib[w];
+        block_partials[blockIdx.x] = bsum;
+    }
+    // the ticket: every thread's stores (l_i to the peers, the block partial) are fenced at system
+    // scope before the block draws it, so whoever draws the last one sees and covers them all
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) ticket_s = atomicAdd(counter, 1u);
+    __syncthreads();
+    if (ticket_s != gridDim.x - 1) return;
+    __threadfence();
+    double acc = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += 256) acc += (double)__ldcg(block_partials + b);
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x < 32) {
+        unsigned e = signal.epoch ? *signal.epoch + 1u : 0u;
+        __syncwarp();
+        if (threadIdx.x == 0) {
+            if (signal.epoch) *signal.epoch = e;
+            *counter = 0u;  // ready for the next call
+        }
+        if ((int)threadIdx.x < loss_outs.n) {
+            static_cast<float*>(loss_outs.p[threadIdx.x])[loss_index] = (float)(red[0] * (double)loss_scale);
+            if (signal.epoch)
+                st_release_sys(static_cast<unsigned*>(signal.flags.p[threadIdx.x]) + signal.rank, e);
+        }
+    }
+}
+
 cudaError_t launch_fwd_finalize_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                                      int64_t row_begin, int64_t row_count, float tau, int nsplit,
                                      const float* part_m, const float* part_s, float* pos_t, const int* pos_index,
                                      const PeerList& lse_outs, int64_t lse_offset, float* block_partials,
                                      const PeerList& loss_outs, int loss_index, float loss_scale,
-                                     const PeerSignal& signal, cudaStream_t stream) {
+                                     const PeerSignal& signal, cudaStream_t stream, unsigned* counter) {
+    if (counter) {
+        const unsigned blocks = (unsigned)((row_count + kFusedRowsPerCta - 1) / kFusedRowsPerCta);
+        if (op_bf16)
+            return launch_kernel(fwd_finalize_fused_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, stream,
+                                 (const __nv_bfloat16*)u_all, M, (int)D, row_begin, row_count, kLog2e / tau, nsplit,
+                                 part_m, part_s, pos_index, lse_outs, lse_offset, block_partials, counter, loss_outs,
+                                 loss_index, loss_scale, signal);
+        return launch_kernel(fwd_finalize_fused_kernel<float>, dim3(blocks), dim3(256), 0, stream,
+                             (const float*)u_all, M, (int)D, row_begin, row_count, kLog2e / tau, nsplit, part_m,
+                             part_s, pos_index, lse_outs, lse_offset, block_partials, counter, loss_outs, loss_index,
+                             loss_scale, signal);
+    }
     // the positive logits: k u_i . u_pos(i), fp32 dot products of the operand rows
     cudaError_t e = launch_pos_dot(u_all, op_bf16, M, D, row_begin, row_count, pos_index, kLog2e / tau, pos_t, stream);
     if (e != cudaSuccess) return e;
@@ -141,6 +252,10 @@ struct BwdEpiDev {
     const int* pos_index;
     const int* inv_ptr;
     const int* inv_idx;
+    const float* loss_parts;
+    int loss_n;
+    float loss_scale;
+    float* loss_out;
 };
 
 // A warp owns kRows rows of kChunks x 128 columns each and issues the loads of all of them
@@ -156,6 +271,11 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
     const int64_t r0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * kRows;
     if (r0 >= p.a_count) return;
     pdl_wait();
+    if (p.loss_out && blockIdx.x == 0 && threadIdx.x == 0) {  // the global loss, in rank order
+        float acc = 0.f;
+        for (int i = 0; i < p.loss_n; ++i) acc += p.loss_parts[i];
+        *p.loss_out = acc * p.loss_scale;
+    }
     const int D = p.D;
     float4 du[kRows][kChunks], zz[kRows][kChunks];
     int64_t pos[kRows];
@@ -310,6 +430,7 @@ cudaError_t launch_bwd_epilogue(const BwdEpilogueArgs& a, cudaStream_t stream) {
     p.lse_all = a.lse_all; p.inv_tau = a.inv_tau; p.pos_prob_out = a.pos_prob_out;
     p.tau_grad_rows_out = a.du_out ? nullptr : a.tau_grad_rows_out;
     p.pos_index = a.pos_index; p.inv_ptr = a.inv_ptr; p.inv_idx = a.inv_idx;
+    p.loss_parts = a.loss_parts; p.loss_n = a.loss_n; p.loss_scale = a.loss_scale; p.loss_out = a.loss_out;
     if (a.op_bf16)
         return a.z_bf16 ? launch_bwd_epilogue_t<__nv_bfloat16, __nv_bfloat16>(p, a, stream)
                         : launch_bwd_epilogue_t<__nv_bfloat16, float>(p, a, stream);

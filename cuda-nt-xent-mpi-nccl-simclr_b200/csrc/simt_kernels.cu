@@ -25,12 +25,13 @@ namespace ntxent_b200 {
 template <typename TIn, typename TOut, int kChunks, int kRows>
 __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ z, int64_t rows,
                                                         int D, PeerList outs, int64_t row_offset,
-                                                        float* __restrict__ inv_norm) {
+                                                        float* __restrict__ inv_norm, unsigned* zero_word) {
     pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t row0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * kRows;
     if (row0 >= rows) return;
     pdl_wait();  // the previous step's epilogue may still be reading the U this kernel overwrites
+    if (zero_word && blockIdx.x == 0 && threadIdx.x == 0) *zero_word = 0u;
     float4 v[kRows][kChunks];
 #pragma unroll
     for (int q = 0; q < kRows; ++q)
@@ -91,12 +92,13 @@ __global__ void __launch_bounds__(32) peer_signal_kernel(PeerSignal s) {
 
 template <typename TIn, typename TOut>
 static cudaError_t launch_normalize_t(const void* z, int64_t rows, int64_t D, const PeerList& outs,
-                                      int64_t row_offset, float* inv_norm, cudaStream_t stream) {
+                                      int64_t row_offset, float* inv_norm, cudaStream_t stream,
+                                      unsigned* zero_word) {
     const int chunks = (int)((D + 127) / 128);
     dim3 block(256);
 #define NTX_NORM(C, R)                                                                           \
     launch_kernel(normalize_kernel<TIn, TOut, C, R>, dim3((unsigned)((rows + 8 * R - 1) / (8 * R))), \
-                  block, 0, stream, (const TIn*)z, rows, (int)D, outs, row_offset, inv_norm)
+                  block, 0, stream, (const TIn*)z, rows, (int)D, outs, row_offset, inv_norm, zero_word)
     if (chunks <= 1) return NTX_NORM(1, 4);
     if (chunks <= 2) return NTX_NORM(2, 4);
     if (chunks <= 4) return NTX_NORM(4, 2);
@@ -106,25 +108,26 @@ static cudaError_t launch_normalize_t(const void* z, int64_t rows, int64_t D, co
 
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
-                                  float* inv_norm, const PeerSignal& signal, cudaStream_t stream) {
+                                  float* inv_norm, const PeerSignal& signal, cudaStream_t stream,
+                                  unsigned* zero_word) {
     if (rows == 0) return signal.epoch ? cudaErrorInvalidValue : cudaSuccess;
     cudaError_t e;
     if (z_bf16 && op_bf16)
-        e = launch_normalize_t<__nv_bfloat16, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream);
+        e = launch_normalize_t<__nv_bfloat16, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
     else if (z_bf16)
-        e = launch_normalize_t<__nv_bfloat16, float>(z, rows, D, outs, row_offset, inv_norm, stream);
+        e = launch_normalize_t<__nv_bfloat16, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
     else if (op_bf16)
-        e = launch_normalize_t<float, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream);
+        e = launch_normalize_t<float, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
     else
-        e = launch_normalize_t<float, float>(z, rows, D, outs, row_offset, inv_norm, stream);
+        e = launch_normalize_t<float, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
     if (e != cudaSuccess || !signal.epoch) return e;
     return launch_kernel(peer_signal_kernel, dim3(1), dim3(32), 0, stream, signal);
 }
 
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
-                             bool op_bf16, float* inv_norm, cudaStream_t stream) {
+                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_word) {
     return launch_normalize_push(z, z_bf16, rows, D, single_peer(u_out), 0, op_bf16, inv_norm, no_signal(),
-                                 stream);
+                                 stream, zero_word);
 }
 
 // ------------------------------------------------------------- 64x64 S tile ---

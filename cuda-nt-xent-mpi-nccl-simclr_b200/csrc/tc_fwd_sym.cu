@@ -386,9 +386,12 @@ constexpr int kSymFinThreads = 512;
 __global__ void __launch_bounds__(kSymFinThreads)
 fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_s,
                         const float* __restrict__ cpart, const float* __restrict__ pos_t,
-                        float* __restrict__ lse_out, float* __restrict__ block_partials) {
+                        float* __restrict__ lse_out, float* __restrict__ block_partials,
+                        unsigned* __restrict__ counter, float* __restrict__ loss_out, float loss_scale) {
     __shared__ float part[3][kTile];
     __shared__ float warp_contrib[kTile / 32];
+    __shared__ unsigned ticket_s;
+    __shared__ double red[kSymFinThreads];
     pdl_trigger();
     pdl_wait();
     const int j = blockIdx.x;  // row tile == column tile of these rows
@@ -428,6 +431,27 @@ fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_
     __syncthreads();
     if (threadIdx.x == 0)
         block_partials[blockIdx.x] = (warp_contrib[0] + warp_contrib[1]) + (warp_contrib[2] + warp_contrib[3]);
+    if (!counter) return;  // (the loss is then summed by a kernel of its own)
+    // the loss: the last block to finish (ticket drawn after a fence) adds the per-tile partials in
+    // a fixed order -- one launch less on the critical path, still run-to-run deterministic
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) ticket_s = atomicAdd(counter, 1u);
+    __syncthreads();
+    if (ticket_s != gridDim.x - 1) return;
+    __threadfence();
+    double acc = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += kSymFinThreads) acc += (double)__ldcg(block_partials + b);
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = kSymFinThreads / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        *loss_out = (float)(red[0] * (double)loss_scale);
+        *counter = 0u;
+    }
 }
 
 // chunk length: long enough to amortise a CTA's prologue (~1.5 tiles), short enough that the
@@ -498,9 +522,9 @@ cudaError_t tc_launch_fwd_sym(const void* u_all, int64_t M, int64_t D, float tau
 
 cudaError_t tc_launch_fwd_sym_finalize(int64_t M, const SymPlan& sp, const float* part_s, const float* cpart,
                                        const float* pos_t, float* lse_out, float* block_partials,
-                                       cudaStream_t stream) {
+                                       cudaStream_t stream, unsigned* counter, float* loss_out, float loss_scale) {
     return launch_kernel(fwd_sym_finalize_kernel, dim3((unsigned)sp.T), dim3(kSymFinThreads), 0, stream, M, sp.T,
-                         sp.L, part_s, cpart, pos_t, lse_out, block_partials);
+                         sp.L, part_s, cpart, pos_t, lse_out, block_partials, counter, loss_out, loss_scale);
 }
 
 }  // namespace ntxent_b200

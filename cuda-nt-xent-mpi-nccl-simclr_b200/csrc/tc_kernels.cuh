@@ -37,10 +37,12 @@ SymPlan tc_sym_plan(int64_t M, int64_t D, int num_sms);
 // part_s [slots][M], cpart [cpart_floats], pos_t [M] (positive logits, base-2 units)
 cudaError_t tc_launch_fwd_sym(const void* u_all, int64_t M, int64_t D, float tau, const SymPlan& sp,
                               float* part_s, float* cpart, float* pos_t, cudaStream_t stream);
-// -> lse_out [M], block_partials [T] (per-row-tile sums of l_i - S_i,pos(i))
+// -> lse_out [M], block_partials [T] (per-row-tile sums of l_i - S_i,pos(i)); with a ticket
+// `counter` (zero before the call, zero after it) also loss_out[0] = loss_scale * their sum
 cudaError_t tc_launch_fwd_sym_finalize(int64_t M, const SymPlan& sp, const float* part_s, const float* cpart,
                                        const float* pos_t, float* lse_out, float* block_partials,
-                                       cudaStream_t stream);
+                                       cudaStream_t stream, unsigned* counter = nullptr, float* loss_out = nullptr,
+                                       float loss_scale = 1.f);
 
 // Scratch the tf32 backward needs for its transposed copy of U ([D, M rounded up to 4] fp32);
 // zero for bf16 operands.

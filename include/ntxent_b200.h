@@ -215,6 +215,10 @@ typedef struct {
     ntxent_peer_list flags; /* uint32_t[NTXENT_MAX_PEERS] on every rank (own included) */
     uint32_t* epoch;        /* this rank's call counter for this signal (device memory) */
     int rank;               /* slot this rank publishes to */
+    uint32_t* ticket;       /* optional, forward_rows_push only: a device word, zero like the flags
+                               before the first call and the library's afterwards.  With it the
+                               positive logits, l_i, the loss and the signal come out of ONE kernel
+                               (its last block to finish does the reduction) instead of three. */
 } ntxent_peer_signal;
 typedef struct {
     const uint32_t* flags;  /* this rank's copy of the flag array */
@@ -257,12 +261,18 @@ int ntxent_b200_peer_wait(const ntxent_peer_wait* ready, ntxent_stream_t stream)
 /* Symmetric-form backward for rows [row_begin, row_begin+row_count) straight to
  * dz (ntxent_b200_backward_rows + ntxent_b200_finalize_dz in two launches
  * instead of three).  `lse_ready` (optional) makes the tile kernel wait for the
- * peers' forward_rows_push, block of columns by block of columns. */
+ * peers' forward_rows_push, block of columns by block of columns.
+ * loss_parts / loss_parts_count / loss_out (optional, NULL / 0 / NULL): the
+ * epilogue also writes loss_out[0] = (sum of loss_parts[0..count)) / M -- the
+ * global mean loss from the ranks' partial sums that forward_rows_push stored,
+ * all of which have landed once this call's tile kernel has waited on
+ * `lse_ready` -- which saves the caller a kernel of its own. */
 int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_t M, int64_t D,
                                  int64_t row_begin, int64_t row_count, float tau, int dtype,
                                  unsigned flags, void* workspace, size_t workspace_bytes,
                                  const void* z_rows, const float* inv_norm_rows, const float* grad_out,
                                  void* dz_out, const ntxent_peer_wait* lse_ready,
+                                 const float* loss_parts, int loss_parts_count, float* loss_out,
                                  ntxent_stream_t stream);
 
 /* Normalisation Jacobian: dz_i = g (dU_i - (dU_i . u_i) u_i) * inv_norm_i with
