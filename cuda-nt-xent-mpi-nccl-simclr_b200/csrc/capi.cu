@@ -144,6 +144,9 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
     return p;
 }
 
+// Tickets of the in-kernel forward finalize: one for the loss, one per 128-row tile.
+inline size_t ticket_words(int64_t row_count) { return 1 + (size_t)((row_count + 127) / 128); }
+
 struct RowsWs {
     float* pos_t;  // positive logits (base-2 units): captured by the upper-triangle forward, or dot products
     float* block_partials;
@@ -169,7 +172,7 @@ RowsWs carve_rows(char* base, int64_t M, int64_t D, int64_t row_count, const Pla
     };
     w.pos_t = (float*)take(sizeof(float) * (size_t)row_count);
     w.block_partials = (float*)take(sizeof(float) * (size_t)((row_count + 7) / 8));
-    w.counter = (unsigned*)take(kAlign);
+    w.counter = (unsigned*)take(sizeof(unsigned) * ticket_words(row_count));
     w.part_m = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.part_s = (float*)take(sizeof(float) * (size_t)p.fwd.nsplit * row_count);
     w.acc_rows = (float*)take(sizeof(float) * (size_t)p.bwd_rows.nsplit * row_count * D);
@@ -253,13 +256,24 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                           const PeerSignal& lse_signal, cudaStream_t st, const int* pos_index = nullptr,
                           unsigned* counter = nullptr) {
     g_timer.start(0, st);
-    if (p.tc)
+    if (p.tc) {
+        // with tickets the tile kernel finalizes in its own tail: no further launch
+        FwdTail tail{};
+        tail.tickets = counter;
+        tail.pos_index = pos_index;
+        tail.lse_outs = lse_outs; tail.lse_offset = lse_offset;
+        tail.block_partials = w.block_partials;
+        tail.loss_outs = loss_outs; tail.loss_index = loss_index; tail.loss_scale = loss_scale;
+        tail.signal = lse_signal;
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, u_ready, st, p.cross));
-    else
+                              w.part_s, u_ready, st, p.cross, counter ? &tail : nullptr));
+        g_timer.stop(0, st);
+        if (counter) return NTXENT_OK;
+    } else {
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, u_ready, st, p.cross ? M / 2 : 0));
-    g_timer.stop(0, st);
+        g_timer.stop(0, st);
+    }
     NTX_TRY(launch_fwd_finalize_push(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd.nsplit, w.part_m,
                                      w.part_s, w.pos_t, pos_index, lse_outs, lse_offset, w.block_partials,
                                      loss_outs, loss_index, loss_scale, lse_signal, st, counter));
@@ -645,7 +659,8 @@ int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtyp
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     return run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
 }
 
@@ -662,7 +677,8 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                pos_prob_out, stream);
 }
@@ -680,7 +696,8 @@ int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse, grad_out, M, D, tau, p, dz_out,
                                nullptr, stream, tau_grad_rows_out);
 }
@@ -698,7 +715,8 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream);
     if (rc != NTXENT_OK) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p,
@@ -720,7 +738,8 @@ int ntxent_b200_forward_backward_pos(const void* z, const int32_t* pos, const in
     const DeviceWs w = carve_device((char*)workspace, M, D, opb, p);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     rc = run_forward_device(w.U, opb, M, D, tau, p, w.rows, lse_out, loss_out, stream, pos);
     if (rc != NTXENT_OK || !dz_out) return rc;
     return run_backward_device(z, dtype == NTXENT_BF16, w, opb, lse_out, grad_out, M, D, tau, p, dz_out, nullptr,
@@ -899,7 +918,8 @@ extern "C" int ntxent_b200_forward_static(const void* z, int64_t M, int64_t D, f
     const DeviceWs w = carve_device(base, M, D, opb, p);
     // Nothing in the array has to start at zero: every region is written before it is read, so
     // whatever the previous call left behind is harmless.
-    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter));
+    NTX_TRY(launch_normalize(z, dtype == NTXENT_BF16, M, D, w.U, opb, w.inv_norm, stream, w.rows.counter,
+                             (int)ticket_words(M)));
     return run_forward_rows(w.U, opb, M, D, 0, M, tau, p, w.rows, lse_out, loss_out,
                             1.0f / (float)M, stream);
 }

@@ -107,9 +107,8 @@ inline bool debug_on() {
 constexpr size_t kAl = 256;
 inline size_t al(size_t n) { return (n + kAl - 1) / kAl * kAl; }
 
-// sync block of a buffer set (256 bytes): flag_u[16] | flag_lse[16] | epoch_u | . | epoch_lse | . | status | . | ticket
-constexpr size_t kOffFlagU = 0, kOffFlagLse = 64, kOffEpochU = 128, kOffEpochLse = 136, kOffStatus = 144,
-                 kOffTicket = 152;
+// sync block of a buffer set (256 bytes): flag_u[16] | flag_lse[16] | epoch_u | . | epoch_lse | . | status
+constexpr size_t kOffFlagU = 0, kOffFlagLse = 64, kOffEpochU = 128, kOffEpochLse = 136, kOffStatus = 144;
 
 }  // namespace
 }  // namespace ntxent_b200
@@ -128,6 +127,7 @@ struct ntxent_comm {
     void* ws = nullptr;
     size_t ws_bytes = 0;
     float* inv_norm = nullptr;
+    unsigned* tickets = nullptr;                // 1 + rows/128 words, zero between calls (in-kernel finalize)
     float* loss_part = nullptr;                 // [2]: partial, summed (NCCL paths)
     float* du_rows = nullptr;                   // contract backward: row term [rows, D]
     float* du_cols = nullptr;                   //                    column term [M, D]
@@ -187,7 +187,7 @@ void free_comm(ntxent_comm* c) {
     if (c->side) cudaStreamDestroy(c->side);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
-    for (void* p : {(void*)c->base, c->ws, (void*)c->inv_norm, (void*)c->loss_part, (void*)c->du_rows,
+    for (void* p : {(void*)c->base, c->ws, (void*)c->inv_norm, (void*)c->tickets, (void*)c->loss_part, (void*)c->du_rows,
                     (void*)c->du_cols, (void*)c->du_col_local})
         if (p) cudaFree(p);
     (void)cudaGetLastError();
@@ -211,6 +211,10 @@ int alloc_comm(ntxent_comm* c, int rank, int nranks, int64_t M, int64_t D, int d
     c->ws_bytes = ntxent_b200_rows_workspace_bytes(M, D, c->rows, dtype, flags);
     NTX_CUDA(cudaMalloc(&c->ws, c->ws_bytes));
     NTX_CUDA(cudaMalloc((void**)&c->inv_norm, al(sizeof(float) * c->rows)));
+    // tickets: [0] the loss, [1 .. row tiles] the forward's row tiles, [last] the normalise kernel's signal
+    const size_t tick_bytes = al(sizeof(unsigned) * (2 + (size_t)((c->rows + 127) / 128)));
+    NTX_CUDA(cudaMalloc((void**)&c->tickets, tick_bytes));
+    NTX_CUDA(cudaMemset(c->tickets, 0, tick_bytes));
     NTX_CUDA(cudaMalloc((void**)&c->loss_part, kAl));
     NTX_CUDA(cudaMalloc((void**)&c->du_rows, al(sizeof(float) * c->rows * D)));
     NTX_CUDA(cudaMalloc((void**)&c->du_col_local, al(sizeof(float) * c->rows * D)));
@@ -401,9 +405,10 @@ SetView view_of(const ntxent_comm* c, int k) {
     char* sync = c->base + o_sync;
     v.sig_u.epoch = (uint32_t*)(sync + kOffEpochU);
     v.sig_u.rank = c->rank;
+    v.sig_u.ticket = c->tickets + 1 + (c->rows + 127) / 128;
     v.sig_lse.epoch = (uint32_t*)(sync + kOffEpochLse);
     v.sig_lse.rank = c->rank;
-    v.sig_lse.ticket = (uint32_t*)(sync + kOffTicket);
+    v.sig_lse.ticket = c->tickets;
     v.wait_u.flags = (const uint32_t*)(sync + kOffFlagU);
     v.wait_u.epoch = (const uint32_t*)(sync + kOffEpochU);
     v.wait_lse.flags = (const uint32_t*)(sync + kOffFlagLse);
@@ -414,8 +419,9 @@ SetView view_of(const ntxent_comm* c, int k) {
     return v;
 }
 
-// PUSH: normalise -> signal -> forward tiles (wait flags) -> fused finalize (signal) -> backward tiles
-// (wait flags) -> epilogue: six launches, no collective.  Two buffer sets alternate so that a fast rank's step t+1 never
+// PUSH: normalise (its last block signals) -> forward tiles (wait flags; the last CTA of a row tile
+// finalizes it, the last row tile signals) -> backward tiles (wait flags) -> epilogue (+ global loss):
+// four launches, no collective.  Two buffer sets alternate so that a fast rank's step t+1 never
 // lands in what a slow rank still reads for step t.
 int step_push(ntxent_comm* c, const void* z, const float* g, float tau, float* loss_out, void* dz_out,
               cudaStream_t st) {

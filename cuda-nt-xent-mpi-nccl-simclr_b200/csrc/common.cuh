@@ -78,15 +78,16 @@ SplitPlan plan_splits(int64_t a_count, int64_t b_count, int row_tile, int col_ti
 int device_sm_count();  // SM count of the current device; 148 when there is none
 
 // ---- launchers (all asynchronous on `stream`; return the launch status) ----------
-// zero_word (optional): a device word the kernel sets to zero -- the ticket counter of the fused
-// forward finalize, cleared by the kernel that starts every whole-batch call.
+// zero_words (optional): n_zero device words the kernel sets to zero -- the tickets of the forward
+// finalize, cleared by the kernel that starts every whole-batch call.
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
-                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_word = nullptr);
+                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_words = nullptr,
+                             int n_zero = 0);
 // Same, storing the rows at row `row_offset` of every buffer in `outs`.
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
                                   float* inv_norm, const PeerSignal& signal, cudaStream_t stream,
-                                  unsigned* zero_word = nullptr);
+                                  unsigned* zero_words = nullptr, int n_zero = 0);
 
 // SIMT (fp32 FMA) tile kernels.
 cudaError_t launch_simt_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,

@@ -100,12 +100,13 @@ cudaError_t launch_peer_wait(const PeerWait& wait, cudaStream_t stream) {
 
 // Everything after the forward tile pass in ONE kernel, for callers that can give it a ticket
 // counter (a device word that is zero before the first call; it leaves every call at zero again):
-// a warp per four rows forms the positive logit (fp32 dot of the operand rows), merges the row's
-// split partials, stores l_i (to every peer), and the last block to finish -- known by the ticket
+// 64 rows per block: a thread per row merges the row's split partials (coalesced) and stores l_i (to
+// every peer), the warps form the positive logits (fp32 dots of the operand rows, four rows' loads in
+// flight), and the last block to finish -- known by the ticket
 // it draws after a system-scope fence -- sums the per-block loss partials in a fixed order, stores
 // the loss and publishes the signal.  Replaces pos_dot + finalize_rows + loss_reduce: three
 // launches on the critical path of a 0.16 ms multi-GPU step.
-constexpr int kFusedRowsPerWarp = 4, kFusedRowsPerCta = 8 * kFusedRowsPerWarp;
+constexpr int kFusedRowsPerCta = 64;  // 8 warps x 8 rows
 template <typename T>
 __global__ void __launch_bounds__(256)
 fwd_finalize_fused_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int64_t row_count,
@@ -114,50 +115,66 @@ fwd_finalize_fused_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row
                           PeerList lse_outs, int64_t lse_offset, float* __restrict__ block_partials,
                           unsigned* __restrict__ counter, PeerList loss_outs, int loss_index,
                           float loss_scale, PeerSignal signal) {
+    __shared__ float l2_s[kFusedRowsPerCta];
     __shared__ float warp_contrib[8];
     __shared__ unsigned ticket_s;
     __shared__ double red[256];
     pdl_trigger();
     pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t r0 = (int64_t)blockIdx.x * kFusedRowsPerCta + warp * kFusedRowsPerWarp;
-    float m[kFusedRowsPerWarp], s[kFusedRowsPerWarp], dot[kFusedRowsPerWarp];
-    // all loads of the warp's four rows are issued before any of them is consumed
-#pragma unroll
-    for (int q = 0; q < kFusedRowsPerWarp; ++q) {
-        const int64_t r = r0 + q;
-        m[q] = -INFINITY; s[q] = 0.f; dot[q] = 0.f;
+    const int64_t rb = (int64_t)blockIdx.x * kFusedRowsPerCta;
+    // (1) one thread per row: the split partials, coalesced (consecutive rows are consecutive words
+    //     of every split), eight pairs in flight; l_i to every peer's copy
+    if (threadIdx.x < kFusedRowsPerCta) {
+        const int64_t r = rb + threadIdx.x;
+        float l2 = 0.f;
         if (r < row_count) {
-            for (int sp = lane; sp < nsplit; sp += 32)
-                lse2_merge(m[q], s[q], part_m[(int64_t)sp * row_count + r], part_s[(int64_t)sp * row_count + r]);
-            const int64_t row = row_begin + r;
-            const int64_t pi = pos_index ? (int64_t)pos_index[row] : (row + M / 2) % M;
-            const T* ui = U + row * D;
-            const T* up = U + pi * D;
-            for (int k = lane * 4; k < D; k += 128) {
-                const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
-                dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+            float m = -INFINITY, s = 0.f;
+            for (int sp0 = 0; sp0 < nsplit; sp0 += 8) {
+                float pm[8], ps[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const bool ok = sp0 + j < nsplit;
+                    pm[j] = ok ? part_m[(int64_t)(sp0 + j) * row_count + r] : -INFINITY;
+                    ps[j] = ok ? part_s[(int64_t)(sp0 + j) * row_count + r] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) lse2_merge(m, s, pm[j], ps[j]);
+            }
+            l2 = m + log2f(s);
+            const float l = l2 * kLn2;
+            for (int i = 0; i < lse_outs.n; ++i) static_cast<float*>(lse_outs.p[i])[lse_offset + r] = l;
+        }
+        l2_s[threadIdx.x] = l2;
+    }
+    // (2) every warp: the positive logits of its eight rows (fp32 dot of the operand rows, both in
+    //     L2), four rows' loads in flight at a time
+    float dots[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float dot[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int64_t r = rb + warp * 8 + h * 4 + q;
+            if (r < row_count) {
+                const int64_t row = row_begin + r;
+                const int64_t pi = pos_index ? (int64_t)pos_index[row] : (row + M / 2) % M;
+                const T* ui = U + row * D;
+                const T* up = U + pi * D;
+                for (int k = lane * 4; k < D; k += 128) {
+                    const float4 a = Elem<T>::ld4(ui + k), b = Elem<T>::ld4(up + k);
+                    dot[q] += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+                }
             }
         }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) dots[h * 4 + q] = warp_sum(dot[q]);
     }
+    __syncthreads();
     float contrib = 0.f;
 #pragma unroll
-    for (int q = 0; q < kFusedRowsPerWarp; ++q) {
-        const int64_t r = r0 + q;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float m2 = __shfl_xor_sync(0xffffffffu, m[q], o);
-            const float s2 = __shfl_xor_sync(0xffffffffu, s[q], o);
-            lse2_merge(m[q], s[q], m2, s2);
-        }
-        const float d = warp_sum(dot[q]);
-        if (r < row_count) {
-            const float l2 = m[q] + log2f(s[q]);
-            const float l = l2 * kLn2;
-            if (lane < lse_outs.n) static_cast<float*>(lse_outs.p[lane])[lse_offset + r] = l;  // lane i serves peer i
-            contrib += (l2 - d * k_scale) * kLn2;
-        }
-    }
+    for (int q = 0; q < 8; ++q)
+        if (rb + warp * 8 + q < row_count) contrib += (l2_s[warp * 8 + q] - dots[q] * k_scale) * kLn2;
     if (lane == 0) warp_contrib[warp] = contrib;
     __syncthreads();
     if (threadIdx.x == 0) {

@@ -25,13 +25,16 @@ namespace ntxent_b200 {
 template <typename TIn, typename TOut, int kChunks, int kRows>
 __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ z, int64_t rows,
                                                         int D, PeerList outs, int64_t row_offset,
-                                                        float* __restrict__ inv_norm, unsigned* zero_word) {
+                                                        float* __restrict__ inv_norm, unsigned* zero_words, int n_zero,
+                                                        PeerSignal signal) {
+    __shared__ unsigned ticket_s;
     pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t row0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * kRows;
-    if (row0 >= rows) return;
     pdl_wait();  // the previous step's epilogue may still be reading the U this kernel overwrites
-    if (zero_word && blockIdx.x == 0 && threadIdx.x == 0) *zero_word = 0u;
+    if (zero_words && blockIdx.x == 0)
+        for (int i = threadIdx.x; i < n_zero; i += 256) zero_words[i] = 0u;
+    if (row0 < rows) {
     float4 v[kRows][kChunks];
 #pragma unroll
     for (int q = 0; q < kRows; ++q)
@@ -72,6 +75,27 @@ __global__ void __launch_bounds__(256) normalize_kernel(const TIn* __restrict__ 
                 Elem<TOut>::st4(static_cast<TOut*>(outs.p[i]) + (row_offset + row) * D + k, t);
         }
     }
+    }
+    // Push path with a ticket word: the block that finishes last publishes "this rank's rows have
+    // landed" itself (every block fences its peer stores at system scope before it draws its ticket),
+    // which saves the one-block signal kernel and its launch boundary.
+    if (signal.ticket) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) ticket_s = atomicAdd(signal.ticket, 1u);
+        __syncthreads();
+        if (ticket_s == gridDim.x - 1 && threadIdx.x < 32) {
+            unsigned e = 0;
+            if (threadIdx.x == 0) {
+                e = *signal.epoch + 1u;
+                *signal.epoch = e;
+                *signal.ticket = 0u;
+            }
+            e = __shfl_sync(0xffffffffu, e, 0);
+            if ((int)threadIdx.x < signal.flags.n)
+                st_release_sys(static_cast<unsigned*>(signal.flags.p[threadIdx.x]) + signal.rank, e);
+        }
+    }
 }
 
 // Publishes "the kernel before me on this stream has finished its peer stores": a grid's stores
@@ -93,12 +117,12 @@ __global__ void __launch_bounds__(32) peer_signal_kernel(PeerSignal s) {
 template <typename TIn, typename TOut>
 static cudaError_t launch_normalize_t(const void* z, int64_t rows, int64_t D, const PeerList& outs,
                                       int64_t row_offset, float* inv_norm, cudaStream_t stream,
-                                      unsigned* zero_word) {
+                                      unsigned* zero_words, int n_zero, const PeerSignal& signal) {
     const int chunks = (int)((D + 127) / 128);
     dim3 block(256);
 #define NTX_NORM(C, R)                                                                           \
     launch_kernel(normalize_kernel<TIn, TOut, C, R>, dim3((unsigned)((rows + 8 * R - 1) / (8 * R))), \
-                  block, 0, stream, (const TIn*)z, rows, (int)D, outs, row_offset, inv_norm, zero_word)
+                  block, 0, stream, (const TIn*)z, rows, (int)D, outs, row_offset, inv_norm, zero_words, n_zero, signal)
     if (chunks <= 1) return NTX_NORM(1, 4);
     if (chunks <= 2) return NTX_NORM(2, 4);
     if (chunks <= 4) return NTX_NORM(4, 2);
@@ -109,25 +133,28 @@ static cudaError_t launch_normalize_t(const void* z, int64_t rows, int64_t D, co
 cudaError_t launch_normalize_push(const void* z, bool z_bf16, int64_t rows, int64_t D,
                                   const PeerList& outs, int64_t row_offset, bool op_bf16,
                                   float* inv_norm, const PeerSignal& signal, cudaStream_t stream,
-                                  unsigned* zero_word) {
+                                  unsigned* zero_words, int n_zero) {
     if (rows == 0) return signal.epoch ? cudaErrorInvalidValue : cudaSuccess;
+    // with a ticket word the kernel publishes the signal itself; otherwise a one-block kernel after it
+    PeerSignal in_kernel = no_signal();
+    if (signal.epoch && signal.ticket) in_kernel = signal;
     cudaError_t e;
     if (z_bf16 && op_bf16)
-        e = launch_normalize_t<__nv_bfloat16, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
+        e = launch_normalize_t<__nv_bfloat16, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_words, n_zero, in_kernel);
     else if (z_bf16)
-        e = launch_normalize_t<__nv_bfloat16, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
+        e = launch_normalize_t<__nv_bfloat16, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_words, n_zero, in_kernel);
     else if (op_bf16)
-        e = launch_normalize_t<float, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
+        e = launch_normalize_t<float, __nv_bfloat16>(z, rows, D, outs, row_offset, inv_norm, stream, zero_words, n_zero, in_kernel);
     else
-        e = launch_normalize_t<float, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_word);
-    if (e != cudaSuccess || !signal.epoch) return e;
+        e = launch_normalize_t<float, float>(z, rows, D, outs, row_offset, inv_norm, stream, zero_words, n_zero, in_kernel);
+    if (e != cudaSuccess || !signal.epoch || signal.ticket) return e;
     return launch_kernel(peer_signal_kernel, dim3(1), dim3(32), 0, stream, signal);
 }
 
 cudaError_t launch_normalize(const void* z, bool z_bf16, int64_t rows, int64_t D, void* u_out,
-                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_word) {
+                             bool op_bf16, float* inv_norm, cudaStream_t stream, unsigned* zero_words, int n_zero) {
     return launch_normalize_push(z, z_bf16, rows, D, single_peer(u_out), 0, op_bf16, inv_norm, no_signal(),
-                                 stream, zero_word);
+                                 stream, zero_words, n_zero);
 }
 
 // ------------------------------------------------------------- 64x64 S tile ---

@@ -89,7 +89,8 @@ template <int D, bool TF32, bool kOnline>
 __global__ void __launch_bounds__(kThreads, Cfg<D, TF32>::kFwdCtasPerSm)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_begin,
               int64_t row_count, float k_scale, int tiles_per_split, int col_tiles, int cross_half,
-              float* __restrict__ part_m, float* __restrict__ part_s, PeerWait u_ready) {
+              float* __restrict__ part_m, float* __restrict__ part_s, PeerWait u_ready,
+              const void* __restrict__ U_raw, FwdTail tail) {
     using C = Cfg<D, TF32>;
     constexpr int NS = C::kFwdStages;
     extern __shared__ uint8_t smem_raw[];
@@ -280,6 +281,85 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
         if (half == 0 && r < row_count) {
             part_m[(int64_t)blockIdx.y * row_count + r] = m_run;
             part_s[(int64_t)blockIdx.y * row_count + r] = s_run;
+        }
+        if (tail.tickets) {
+            // ---- finalize in place of a kernel of its own (FwdTail, tc_kernels.cuh) ----
+            unsigned* tick_s = reinterpret_cast<unsigned*>(q_tile + 2048);
+            float* wsum_s = reinterpret_cast<float*>(q_tile + 2048 + 16);
+            __threadfence();  // this CTA's partials, before its ticket
+            named_bar_sync(1, kSoftmaxThreads);
+            if (threadIdx.x == 0) tick_s[0] = atomicAdd(&tail.tickets[1 + blockIdx.x], 1u);
+            named_bar_sync(1, kSoftmaxThreads);
+            if (tick_s[0] == gridDim.y - 1) {  // the last split of this row tile to finish
+                __threadfence();
+                float contrib = 0.f;
+                if (half == 0 && r < row_count) {
+                    float m = -INFINITY, s = 0.f;
+                    for (int sp = 0; sp < (int)gridDim.y; ++sp)
+                        lse2_merge(m, s, __ldcg(part_m + (int64_t)sp * row_count + r),
+                                   __ldcg(part_s + (int64_t)sp * row_count + r));
+                    // the positive logit: fp32 dot of the two operand rows (both in L2)
+                    const int64_t pi = tail.pos_index ? (int64_t)tail.pos_index[row] : (row + M / 2) % M;
+                    float dot = 0.f;
+                    if (TF32) {
+                        const float4* ua = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + row * D);
+                        const float4* ub = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + pi * D);
+#pragma unroll 4
+                        for (int k = 0; k < D / 4; ++k) {
+                            const float4 a = ua[k], b = ub[k];
+                            dot += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+                        }
+                    } else {
+                        const uint4* ua = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(U_raw) + row * D);
+                        const uint4* ub = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(U_raw) + pi * D);
+#pragma unroll 4
+                        for (int k = 0; k < D / 8; ++k) {
+                            const uint4 a = ua[k], b = ub[k];
+                            const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                dot += __uint_as_float(aw[j] << 16) * __uint_as_float(bw[j] << 16) +
+                                       __uint_as_float(aw[j] & 0xffff0000u) * __uint_as_float(bw[j] & 0xffff0000u);
+                        }
+                    }
+                    const float l2 = m + log2f(s);
+                    const float l = l2 * kLn2;
+                    for (int i = 0; i < tail.lse_outs.n; ++i)
+                        static_cast<float*>(tail.lse_outs.p[i])[tail.lse_offset + r] = l;
+                    contrib = (l2 - dot * k_scale) * kLn2;
+                }
+                contrib = warp_sum(contrib);
+                if (lane == 0) wsum_s[warp] = contrib;
+                __threadfence_system();  // l_i at the peers, before the ticket that may publish them
+                named_bar_sync(1, kSoftmaxThreads);
+                if (threadIdx.x == 0) {
+                    // (warps 0..3 hold the rows; 4..7 contributed zero)
+                    tail.block_partials[blockIdx.x] = (wsum_s[0] + wsum_s[1]) + (wsum_s[2] + wsum_s[3]);
+                    tail.tickets[1 + blockIdx.x] = 0u;  // ready for the next call
+                    __threadfence_system();
+                    tick_s[1] = atomicAdd(&tail.tickets[0], 1u);
+                }
+                named_bar_sync(1, kSoftmaxThreads);
+                if (tick_s[1] == gridDim.x - 1 && warp == 0) {  // the last row tile: the loss, the signal
+                    __threadfence();
+                    double acc = 0.0;
+                    for (int b = lane; b < (int)gridDim.x; b += 32) acc += (double)__ldcg(tail.block_partials + b);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                    unsigned e = tail.signal.epoch ? *tail.signal.epoch + 1u : 0u;
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (tail.signal.epoch) *tail.signal.epoch = e;
+                        tail.tickets[0] = 0u;
+                    }
+                    if (lane < tail.loss_outs.n) {
+                        static_cast<float*>(tail.loss_outs.p[lane])[tail.loss_index] =
+                            (float)(acc * (double)tail.loss_scale);
+                        if (tail.signal.epoch)
+                            st_release_sys(static_cast<unsigned*>(tail.signal.flags.p[lane]) + tail.signal.rank, e);
+                    }
+                }
+            }
         }
     }
     tc_fence_before();
@@ -943,7 +1023,8 @@ cudaError_t make_tmap(const void* u_all, bool tf32, int64_t M, int64_t D, CUtens
 template <int D, bool TF32, bool kOnline>
 cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, int64_t row_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, int cross_half, float* part_m,
-                         float* part_s, const PeerWait& u_ready, cudaStream_t stream) {
+                         float* part_s, const PeerWait& u_ready, const void* u_raw, const FwdTail& tail,
+                         cudaStream_t stream) {
     using C = Cfg<D, TF32>;
     // request enough shared memory that no more CTAs than the TMEM budget allows co-reside
     const int smem = C::kFwdCtasPerSm == 2 ? max(C::kFwdSmem, 80 * 1024) : max(C::kFwdSmem, 120 * 1024);
@@ -953,7 +1034,8 @@ cudaError_t launch_fwd_t(const CUtensorMap& tmap, int64_t M, int64_t row_begin, 
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)plan.row_tiles, (unsigned)plan.nsplit);
     return launch_kernel(kern, grid, dim3(kThreads), smem, stream, tmap, M, row_begin, row_count, k_scale,
-                         (int)(plan.cols_per_split / kTile), col_tiles, cross_half, part_m, part_s, u_ready);
+                         (int)(plan.cols_per_split / kTile), col_tiles, cross_half, part_m, part_s, u_ready, u_raw,
+                         tail);
 }
 
 // U [M, D] fp32 -> UT [D, Mpad] (Mpad = M rounded up to 4, pad columns zero): the K-major B operand
@@ -1102,7 +1184,9 @@ SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, in
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, const PeerWait& u_ready,
-                          cudaStream_t stream, bool cross_view) {
+                          cudaStream_t stream, bool cross_view, const FwdTail* tail_in) {
+    FwdTail tail{};
+    if (tail_in) tail = *tail_in;
     CUtensorMap tmap;
     cudaError_t e = make_tmap(u_all, !op_bf16, M, D, &tmap);
     if (e != cudaSuccess) return e;
@@ -1114,9 +1198,9 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
     const int col_tiles = cross_view ? cross_half : (int)((M + kTile - 1) / kTile);
 #define NTX_FWD(DD, TF)                                                                                    \
     (online ? launch_fwd_t<DD, TF, true>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, cross_half,  \
-                                         part_m, part_s, u_ready, stream)                                      \
+                                         part_m, part_s, u_ready, u_all, tail, stream)                         \
             : launch_fwd_t<DD, TF, false>(tmap, M, row_begin, row_count, k_scale, plan, col_tiles, cross_half, \
-                                          part_m, part_s, u_ready, stream))
+                                          part_m, part_s, u_ready, u_all, tail, stream))
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_FWD(64, true);

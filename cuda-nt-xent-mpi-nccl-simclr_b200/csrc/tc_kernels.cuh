@@ -11,10 +11,28 @@ bool tc_supported(int64_t M, int64_t D, bool op_bf16);
 SplitPlan tc_plan_fwd(int64_t M, int64_t D, int64_t row_count, bool op_bf16, int num_sms);
 SplitPlan tc_plan_bwd(int64_t M, int64_t D, int64_t a_count, int64_t b_count, int num_sms);
 
+// What the forward tile kernel does after its last tile when it is given tickets: the CTA that
+// finishes a row tile LAST (of its column splits) merges the tile's partials, forms the positive
+// logits, stores l_i (to every peer) and the tile's loss partial; the CTA that finishes the last row
+// tile sums the loss partials in a fixed order, stores the loss and publishes the signal.  No
+// finalize kernel is launched then.  tickets: 1 + row_tiles device words, zero before the call (and
+// again after it); nullptr: the partials are left for the finalize kernel.
+struct FwdTail {
+    unsigned* tickets;
+    const int* pos_index;  // positives from an index vector, or nullptr
+    PeerList lse_outs;
+    int64_t lse_offset;
+    float* block_partials;
+    PeerList loss_outs;
+    int loss_index;
+    float loss_scale;
+    PeerSignal signal;
+};
+
 cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D, int64_t row_begin,
                           int64_t row_count, float tau, unsigned flags, const SplitPlan& plan,
                           float* part_m, float* part_s, const PeerWait& u_ready,
-                          cudaStream_t stream, bool cross_view = false);
+                          cudaStream_t stream, bool cross_view = false, const FwdTail* tail = nullptr);
 
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,

@@ -215,10 +215,14 @@ typedef struct {
     ntxent_peer_list flags; /* uint32_t[NTXENT_MAX_PEERS] on every rank (own included) */
     uint32_t* epoch;        /* this rank's call counter for this signal (device memory) */
     int rank;               /* slot this rank publishes to */
-    uint32_t* ticket;       /* optional, forward_rows_push only: a device word, zero like the flags
-                               before the first call and the library's afterwards.  With it the
-                               positive logits, l_i, the loss and the signal come out of ONE kernel
-                               (its last block to finish does the reduction) instead of three. */
+    uint32_t* ticket;       /* optional device words, zero like the flags before the first call and
+                               the library's afterwards; they turn kernel boundaries into "the last
+                               block to finish does it".  normalize_push: ONE word -- the kernel
+                               publishes the signal itself instead of a one-block kernel after it.
+                               forward_rows_push: 1 + ceil(row_count / 128) words -- the positive
+                               logits, l_i, the loss and the signal come out of the tile kernel
+                               itself (the last CTA to finish a row tile, then the last row tile,
+                               do the work): no finalize launch. */
 } ntxent_peer_signal;
 typedef struct {
     const uint32_t* flags;  /* this rank's copy of the flag array */
