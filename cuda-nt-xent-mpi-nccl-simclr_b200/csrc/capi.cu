@@ -10,6 +10,8 @@
 #include <mutex>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>  // header-only: ranges are no-ops unless a profiler injects itself
+
 #include "common.cuh"
 #include "tc_kernels.cuh"
 
@@ -230,6 +232,20 @@ int check_shape(int64_t M, int64_t D, float tau, int dtype) {
     return NTXENT_OK;
 }
 
+// NVTX ranges around the compute entry points (the reference's ENABLE_PROFILING build option,
+// CMakeLists.txt:10,82-84): on with NTXENT_NVTX=1, for timelines in a profiler; off by default so
+// that a step costs no host time for them.
+struct NvtxRange {
+    bool on;
+    explicit NvtxRange(const char* name) {
+        static const bool enabled = [] { const char* v = getenv("NTXENT_NVTX"); return v && v[0] == '1'; }();
+        on = enabled;
+        if (on) nvtxRangePushA(name);
+    }
+    ~NvtxRange() { if (on) nvtxRangePop(); }
+};
+#define NTX_RANGE(name) NvtxRange nvtx_range__(name)
+
 // NTXENT_DEBUG=1 in the environment names the failing launch on stderr.
 inline bool debug_on() {
     static const bool on = [] { const char* v = getenv("NTXENT_DEBUG"); return v && v[0] == '1'; }();
@@ -257,18 +273,24 @@ int run_forward_rows_push(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                           unsigned* counter = nullptr) {
     g_timer.start(0, st);
     if (p.tc) {
-        // with tickets the tile kernel finalizes in its own tail: no further launch
+        // With tickets the tile kernel CAN finalize in its own tail (no further launch).  Measured
+        // slower than the finalize kernel it replaces -- the tail's chain of latencies (partials from
+        // L2, fence, ticket, peer stores, system fence, ticket, sum, flag) runs on a handful of CTAs at
+        // the very end of the kernel: +20 us on the tile kernel for -11 us of launches at a 4096-row
+        // shard (profiles/r2_fusion_ab.txt) -- so it is off unless NTXENT_FWD_TAIL=1.
+        static const bool use_tail = [] { const char* v = getenv("NTXENT_FWD_TAIL"); return v && v[0] == '1'; }();
+        unsigned* const tail_tickets = use_tail ? counter : nullptr;
         FwdTail tail{};
-        tail.tickets = counter;
+        tail.tickets = tail_tickets;
         tail.pos_index = pos_index;
         tail.lse_outs = lse_outs; tail.lse_offset = lse_offset;
         tail.block_partials = w.block_partials;
         tail.loss_outs = loss_outs; tail.loss_index = loss_index; tail.loss_scale = loss_scale;
         tail.signal = lse_signal;
         NTX_TRY(tc_launch_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.flags, p.fwd, w.part_m,
-                              w.part_s, u_ready, st, p.cross, counter ? &tail : nullptr));
+                              w.part_s, u_ready, st, p.cross, tail_tickets ? &tail : nullptr));
         g_timer.stop(0, st);
-        if (counter) return NTXENT_OK;
+        if (tail_tickets) return NTXENT_OK;
     } else {
         NTX_TRY(launch_simt_fwd(u_all, op_bf16, M, D, row_begin, row_count, tau, p.fwd, w.part_m,
                                 w.part_s, u_ready, st, p.cross ? M / 2 : 0));
@@ -550,6 +572,7 @@ int ntxent_b200_normalize_push(const void* z, int64_t rows, int64_t D, int dtype
                                const ntxent_peer_list* u_all_peers, int64_t row_begin,
                                float* inv_norm_out, const ntxent_peer_signal* u_signal,
                                ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_normalize_push");
     PeerList outs{};
     PeerSignal sig{};
     if (!z || rows < 0 || row_begin < 0 || !aligned(z, 16) || !to_peer_list(u_all_peers, &outs) ||
@@ -570,6 +593,7 @@ int ntxent_b200_forward_rows_push(const void* u_all, int64_t M, int64_t D, int64
                                   const ntxent_peer_list* loss_parts_peers, int loss_index,
                                   const ntxent_peer_wait* u_ready, const ntxent_peer_signal* lse_signal,
                                   ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_forward_rows_push");
     PeerList lse_outs{}, loss_outs{};
     PeerWait wait{};
     PeerSignal sig{};
@@ -611,6 +635,7 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
                                  void* dz_out, const ntxent_peer_wait* lse_ready,
                                  const float* loss_parts, int loss_parts_count, float* loss_out,
                                  ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_backward_rows_dz");
     PeerWait wait{};
     if (!u_all || !lse_all || !workspace || !z_rows || !inv_norm_rows || !dz_out ||
         !to_peer_wait(lse_ready, &wait))
@@ -650,6 +675,7 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
 int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,
                         void* workspace, size_t workspace_bytes, float* loss_out, float* lse_out,
                         ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_forward");
     if (!z || !workspace || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(z, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
@@ -668,6 +694,7 @@ int ntxent_b200_backward(const void* z, const float* lse, const float* grad_out,
                          int64_t D, float tau, int dtype, unsigned flags, void* workspace,
                          size_t workspace_bytes, void* dz_out, float* pos_prob_out,
                          ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_backward");
     if (!z || !lse || !workspace || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
@@ -687,6 +714,7 @@ int ntxent_b200_backward_tau(const void* z, const float* lse, const float* grad_
                              int64_t D, float tau, int dtype, unsigned flags, void* workspace,
                              size_t workspace_bytes, void* dz_out, float* tau_grad_rows_out,
                              ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_backward_tau");
     if (!z || !lse || !workspace || !dz_out || !tau_grad_rows_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
@@ -706,6 +734,7 @@ int ntxent_b200_forward_backward(const void* z, const float* grad_out, int64_t M
                                  float tau, int dtype, unsigned flags, void* workspace,
                                  size_t workspace_bytes, float* loss_out, float* lse_out,
                                  void* dz_out, float* pos_prob_out, ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_forward_backward");
     if (!z || !workspace || !loss_out || !lse_out || !dz_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
     int rc = check_shape(M, D, tau, dtype);
@@ -728,6 +757,7 @@ int ntxent_b200_forward_backward_pos(const void* z, const int32_t* pos, const in
                                      float tau, int dtype, unsigned flags, void* workspace,
                                      size_t workspace_bytes, float* loss_out, float* lse_out, void* dz_out,
                                      ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_forward_backward_pos");
     if (!z || !pos || !workspace || !loss_out || !lse_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (dz_out && (!inv_ptr || !inv_idx)) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(z, 16) || !aligned(dz_out, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
@@ -750,6 +780,7 @@ int ntxent_b200_forward_rows(const void* u_all, int64_t M, int64_t D, int64_t ro
                              int64_t row_count, float tau, int dtype, unsigned flags,
                              void* workspace, size_t workspace_bytes, float* lse_rows_out,
                              float* loss_partial_out, ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_forward_rows");
     if (!u_all || !workspace || !lse_rows_out || !loss_partial_out)
         return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(u_all, 16) || !aligned(workspace, 256)) return NTXENT_ERR_INVALID_ARGUMENT;
@@ -771,6 +802,7 @@ int ntxent_b200_backward_rows(const void* u_all, const float* lse_all, int64_t M
                               int64_t row_begin, int64_t row_count, float tau, int mode, int dtype,
                               unsigned flags, void* workspace, size_t workspace_bytes,
                               float* du_rows_out, float* du_cols_out, ntxent_stream_t stream) {
+    NTX_RANGE("ntxent_b200_backward_rows");
     if (!u_all || !lse_all || !workspace || !du_rows_out) return NTXENT_ERR_INVALID_ARGUMENT;
     if (!aligned(u_all, 16) || !aligned(workspace, 256) || !aligned(du_rows_out, 16) ||
         !aligned(du_cols_out, 16))

@@ -405,7 +405,9 @@ SetView view_of(const ntxent_comm* c, int k) {
     char* sync = c->base + o_sync;
     v.sig_u.epoch = (uint32_t*)(sync + kOffEpochU);
     v.sig_u.rank = c->rank;
-    v.sig_u.ticket = c->tickets + 1 + (c->rows + 127) / 128;
+    // (NTXENT_NO_NORM_TICKET=1: the one-block signal kernel instead, for A/B runs)
+    static const bool norm_ticket = [] { const char* e = getenv("NTXENT_NO_NORM_TICKET"); return !(e && e[0] == '1'); }();
+    v.sig_u.ticket = norm_ticket ? c->tickets + 1 + (c->rows + 127) / 128 : nullptr;
     v.sig_lse.epoch = (uint32_t*)(sync + kOffEpochLse);
     v.sig_lse.rank = c->rank;
     v.sig_lse.ticket = c->tickets;
