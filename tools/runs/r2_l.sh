@@ -12,17 +12,16 @@ except Exception as e:
     print(n, "FAILED", e)
 PY
 }
-tr() { # name, args...
+trun() { # name, args...
   name=$1; shift
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29561 \
       bench.py --gpus 2 --no-sustained "$@" > gpurun_out/r2_l_$name.json 2>> gpurun_out/r2_l_bench.err
   summ $name
 }
-for size in "--M 8192" "--M 32768"; do
-  tag=$(echo $size | tr -d ' -')
-  tr ${tag}_default $size
-  NTXENT_NO_NORM_TICKET=1 tr ${tag}_signalkernel $size
-  NTXENT_FWD_TAIL=1 tr ${tag}_fwdtail $size
-  tr ${tag}_default2 $size
+for m in 8192 32768; do
+  trun M${m}_default --M $m
+  NTXENT_NO_NORM_TICKET=1 trun M${m}_signalkernel --M $m
+  NTXENT_FWD_TAIL=1 trun M${m}_fwdtail --M $m
+  trun M${m}_default2 --M $m
 done
 grep -v "^\*\|^$\|OMP_NUM\|NCCL version" gpurun_out/r2_l_bench.err | tail -5
