@@ -333,13 +333,12 @@ def run_native(args):
                 return graphed(zin)
             loss, _, dz = capi.forward_backward(zin, tau, None, False, flags, ws, out)
             return loss, dz
-        # normalise, forward tiles (the full-matrix kernel finalizes in its own tail; the upper-triangle
-        # one has a finalize kernel), backward tiles, epilogue; fp32 operands on the tf32 tiles add the
-        # transpose of U
+        # normalise, forward tiles, finalize (+ loss, by its last block), backward tiles, epilogue; fp32
+        # operands on the tf32 tiles add the transpose of U
         import math
         sym_fwd = (dt == "bf16" and M >= 4096 and math.log2(math.e) / tau <= 50.0 and not args.simt
                    and os.environ.get("NTXENT_NO_SYM_FORWARD") != "1")
-        launches_per_step = (5 if sym_fwd else 4) + (1 if dt != "bf16" and not args.simt else 0)
+        launches_per_step = 5 + (1 if dt != "bf16" and not args.simt else 0)
         comm_used = comm_note = None
     else:
         from ntxent_b200.distributed import RowPartitionedNTXent

@@ -405,8 +405,10 @@ SetView view_of(const ntxent_comm* c, int k) {
     char* sync = c->base + o_sync;
     v.sig_u.epoch = (uint32_t*)(sync + kOffEpochU);
     v.sig_u.rank = c->rank;
-    // (NTXENT_NO_NORM_TICKET=1: the one-block signal kernel instead, for A/B runs)
-    static const bool norm_ticket = [] { const char* e = getenv("NTXENT_NO_NORM_TICKET"); return !(e && e[0] == '1'); }();
+    // The normalise kernel CAN publish the signal itself (its last block, after a system-scope fence
+    // per block).  Measured slower than the one-block signal kernel after it (0.415 vs 0.407 ms at
+    // C4 on 2 GPUs, profiles/r2_fusion_ab.txt): off unless NTXENT_NORM_TICKET=1.
+    static const bool norm_ticket = [] { const char* e = getenv("NTXENT_NORM_TICKET"); return e && e[0] == '1'; }();
     v.sig_u.ticket = norm_ticket ? c->tickets + 1 + (c->rows + 127) / 128 : nullptr;
     v.sig_lse.epoch = (uint32_t*)(sync + kOffEpochLse);
     v.sig_lse.rank = c->rank;
@@ -421,9 +423,10 @@ SetView view_of(const ntxent_comm* c, int k) {
     return v;
 }
 
-// PUSH: normalise (its last block signals) -> forward tiles (wait flags; the last CTA of a row tile
-// finalizes it, the last row tile signals) -> backward tiles (wait flags) -> epilogue (+ global loss):
-// four launches, no collective.  Two buffer sets alternate so that a fast rank's step t+1 never
+// PUSH: normalise -> signal -> forward tiles (wait flags) -> finalize (one kernel: positive logits, l,
+// loss, signal by its last block) -> backward tiles (wait flags) -> epilogue (+ global loss): six
+// launches, no collective.  (Folding the signal into the normalise kernel and the finalize into the
+// tile kernel's tail were both built and measured slower: profiles/r2_fusion_ab.txt.)  Two buffer sets alternate so that a fast rank's step t+1 never
 // lands in what a slow rank still reads for step t.
 int step_push(ntxent_comm* c, const void* z, const float* g, float tau, float* loss_out, void* dz_out,
               cudaStream_t st) {

@@ -114,7 +114,7 @@ class RowPartitionedNTXent:
         self.ccomm = None
         if comm != "torch":
             self._init_communicator()
-            self.launches_per_step = 4 if comm == "push" else (6 if backward_mode == "symmetric" else 10)
+            self.launches_per_step = 6 if comm == "push" else (6 if backward_mode == "symmetric" else 10)
             return
         self.backend = backend if backend is not None else CudaBackend(flags)
         op_dtype = torch.bfloat16 if (dtype == torch.bfloat16 or use_mixed_precision) else torch.float32
