@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <algorithm>
 #include <mutex>
+#include <type_traits>
 
 #include "tc_ptx.cuh"
 #include "tc_tile.cuh"
@@ -397,8 +398,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
 template <int D, bool TF32 = false>
 struct BwdCfg {
     static constexpr bool kSeparateP = !TF32 && (D <= 128);
-    static constexpr uint32_t kPCol = 128;
-    static constexpr uint32_t kAccCol = kSeparateP ? 256 : 128;
+    // separate W blocks come with TWO S buffers (S(g+1) is issued while the weight warps are still
+    // reading S(g)); W gets two blocks when the columns are there (D <= 64) and one otherwise
+    static constexpr int kSBufs = kSeparateP ? 2 : 1;
+    static constexpr int kPBufs = kSeparateP ? (D <= 64 ? 2 : 1) : 1;
+    static constexpr uint32_t kPCol = 128 * kSBufs;
+    static constexpr uint32_t kAccCol = kSeparateP ? kPCol + 64 * kPBufs : 128;
     static constexpr uint32_t kQCol = kAccCol + D;
     static constexpr uint32_t kQCols = TF32 ? D : D / 2;
     static_assert(kQCol + kQCols <= 512, "TMEM budget");
@@ -568,9 +573,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     uint64_t* k_empty = k_full + NS;
     uint64_t* kt_full = k_empty + NS;   // [2] (tf32)
     uint64_t* kt_empty = kt_full + 2;   // [2] (tf32)
-    uint64_t* s_full = kt_empty + 2;    // S tile complete (MMA commit)
-    uint64_t* s_free = s_full + 1;     // S buffer reusable: weight warps (SEP) or second MMA (aliased W)
-    uint64_t* p_full = s_free + 1;     // [2] weights stored by all sixteen warps
+    uint64_t* s_full = kt_empty + 2;    // [2] S tile complete (MMA commit)
+    uint64_t* s_free = s_full + 2;     // [2] S buffer reusable: weight warps (SEP) or second MMA (aliased W)
+    uint64_t* p_full = s_free + 2;     // [2] weights stored by all sixteen warps
     uint64_t* p_free = p_full + 2;     // [2] second MMA has consumed the W block (SEP only)
     uint64_t* acc_full = p_free + 2;   // a unit's accumulator is complete (commit after its last W U)
     uint64_t* acc_free = acc_full + 1; // ... and has been read out by all sixteen weight warps
@@ -603,8 +608,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         mbar_init(q_full, 16);
         for (int s = 0; s < NS; ++s) { mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&kt_full[s], 1); mbar_init(&kt_empty[s], 1); }
-        mbar_init(s_full, 1);
-        mbar_init(s_free, SEP ? 16 : 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(&s_full[b], 1); mbar_init(&s_free[b], SEP ? 16 : 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&p_full[b], 16); mbar_init(&p_free[b], 1); }
         mbar_init(acc_full, 1);
         mbar_init(acc_free, 16);
@@ -654,19 +658,21 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                 const int st = g % NS;
                 NTX_TRACE(0, it, 0);
                 mbar_wait(&k_full[st], (g / NS) & 1);
-                // separate W blocks: free once the weight warps have read S(g-1); aliased W: free
-                // once the second MMA of tile g-1 has consumed the weights stored over it
-                mbar_wait(s_free, (g & 1) ^ 1);
+                // separate W blocks: S buffer g % 2 is free once the weight warps have read S(g-2);
+                // aliased W: the one buffer is free once the second MMA of tile g-1 has consumed
+                // the weights stored over it
+                const int sb = g % B::kSBufs;
+                mbar_wait(&s_free[sb], ((g / B::kSBufs) & 1) ^ 1);
                 tc_fence_after();
                 NTX_TRACE(0, it, 2);
                 const uint32_t k_addr = smem_u32(k_tiles + st * C::kTileBytes);
                 if (leader) {
 #pragma unroll
                     for (int kk = 0; kk < C::kKSteps; ++kk)
-                        mma_ts_f16<TF32>(tmem_base, tmem_base + B::kQCol + kk * 8, desc_kmajor(k_addr, kk),
-                                         idesc_s, kk > 0);
+                        mma_ts_f16<TF32>(tmem_base + sb * 128, tmem_base + B::kQCol + kk * 8,
+                                         desc_kmajor(k_addr, kk), idesc_s, kk > 0);
                     if (TF32) tc_commit(&k_empty[st]);  // tf32: only this MMA reads the U_b tile
-                    tc_commit(s_full);
+                    tc_commit(&s_full[sb]);
                 }
                 __syncwarp();
                 NTX_TRACE(0, it, 3);
@@ -684,9 +690,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         }
         for (int it = 0; it < u.n; ++it, ++g) {
             const int st = g % NS;
-            const int pb = SEP ? (g & 1) : 0;
+            const int pb = g % B::kPBufs;
             NTX_TRACE(0, it, 4);
-            mbar_wait(&p_full[pb], (SEP ? (g >> 1) : g) & 1);
+            mbar_wait(&p_full[pb], (g / B::kPBufs) & 1);
             tc_fence_after();
             NTX_TRACE(0, it, 5);
             if (TF32) mbar_wait(&kt_full[g & 1], (g >> 1) & 1);
@@ -709,7 +715,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                                      (it > 0) || (kk > 0));
                 }
                 tc_commit(TF32 ? &kt_empty[g & 1] : &k_empty[st]);
-                tc_commit(SEP ? &p_free[pb] : s_free);
+                tc_commit(SEP ? &p_free[pb] : &s_free[0]);
             }
             __syncwarp();
             NTX_TRACE(0, it, 6);
@@ -779,7 +785,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
         const int row_in_tile = quad * 32 + lane;
         const int wt = threadIdx.x;  // 0..511: the weight threads come first
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-        const int trole = warp == 0 ? 1 : (warp == 15 ? 2 : 3);
+        const int trole = warp == 0 ? 1 : (warp == 8 ? 2 : 3);  // two warps of scheduler 0
         (void)trole;
 
         // park k U_a of row tile `rt` in TMEM (bf16 pairs, or fp32 for tf32): column groups of the
@@ -855,55 +861,59 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                     row_c = (MODE == kSym && !kTwoExp) ? 0.f : INFINITY;  // rows past the range: W = 0
                 }
             }
-            for (int it = 0; it < n_tiles; ++it, ++g) {
-                const int pb = SEP ? (g & 1) : 0;
-                const int jt = jt0 + it;
-                const bool special = (jt >= jt_diag_lo && jt <= jt_diag_hi) || jt == jt_ragged;
-                const int64_t j0 = ub + (int64_t)jt * kTile;  // (used on the masked path only)
-                if (MODE != kRow && (it % B::kCcTiles) == 0)  // the block staged by the constants warp
-                    mbar_wait(&cc_full[cb & 1], (cb >> 1) & 1);
-                const float* cc = colc + ((cb & 1) * B::kCcTiles + it % B::kCcTiles) * kTile + quarter * 32;
-                const uint32_t taddr = lane_addr + quarter * 32;  // this warp's 32 S columns
+            // The tile loop.  A tile's barriers, TMEM columns and phase bits depend on g & 1 (and on
+            // g >> 1, which flips every other tile): the body exists once per parity so that all of
+            // them are immediates.  The rare masked tiles (diagonal, ragged edge) and the hand-over of
+            // the column-constant blocks are kept out of the steady-state loop: every reconvergence
+            // point and every dependent address computation in it was 30-50 clk of a 1550 clk tile
+            // (profiles/r2_ncu_bwd_summary.csv and the source view behind it).
+            int it = 0;
+            uint32_t half = ((uint32_t)g >> 1) & 1u;  // (g >> 1) & 1, kept incrementally
+            const float* cc = colc;
+            auto tile = [&](auto par_c, auto special_c) {
+                constexpr int PAR = decltype(par_c)::value;  // g & 1
+                constexpr bool kSpecial = decltype(special_c)::value;
+                constexpr int sb = B::kSBufs == 2 ? PAR : 0, pb = B::kPBufs == 2 ? PAR : 0;
+                const uint32_t s_par = B::kSBufs == 2 ? half : (uint32_t)PAR;       // (g / kSBufs) & 1
+                const uint32_t p_par = (B::kPBufs == 2 ? half : (uint32_t)PAR) ^ 1u;  // W block free again
+                const uint32_t taddr = lane_addr + sb * 128 + quarter * 32;  // this warp's 32 S columns
                 uint32_t v[32], packed[16];
                 (void)packed;
+                (void)p_par;
                 NTX_TRACE(trole, it, 0);
-                mbar_wait(s_full, g & 1);
+                mbar_wait(&s_full[sb], s_par);
                 tc_fence_after();
                 NTX_TRACE(trole, it, 1);
                 if (it == 0) NTX_TRACE_U(un, 1, clock64());
                 tmem_ld32(taddr, v);
-                // W block pb was last read by the second MMA of tile g-2, issued a whole tile ago:
-                // checked here so that the barrier's latency hides under the TMEM load
-                if (SEP && g >= 2) mbar_wait(&p_free[pb], ((g - 2) >> 1) & 1);
+                // two W blocks: block pb was last read by the second MMA of tile g-2, issued a whole
+                // tile ago: checked here so that the barrier's latency hides under the TMEM load
+                if (SEP && B::kPBufs == 2) mbar_wait(&p_free[pb], p_par);
                 tmem_ld_wait();
-                if (SEP) {  // S is in registers: the buffer can take the next S tile already
+                if (SEP) {  // S is in registers: the buffer can take the S tile after the next
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(s_free);
+                    if (lane == 0) mbar_arrive(&s_free[sb]);
                 }
                 NTX_TRACE(trole, it, 2);
-                if (TF32) {  // 32-bit weights, in place over the S values
-                    if (!special)
-                        weight_chunk<MODE, kTwoExp, false, false, 32>(v, v, cc, k_scale, row_c, 0, 0, 0);
-                    else
-                        weight_chunk<MODE, kTwoExp, true, false, 32>(v, v, cc, k_scale, row_c,
-                                                                     j0 + quarter * 32, row, b_end);
-                } else if (!special) {
-                    weight_chunk<MODE, kTwoExp, false>(v, packed, cc, k_scale, row_c, 0, 0, 0);
-                } else {
-                    weight_chunk<MODE, kTwoExp, true>(v, packed, cc, k_scale, row_c, j0 + quarter * 32, row,
-                                                      b_end);
-                }
+                const int64_t j0 = ub + (int64_t)(jt0 + it) * kTile + quarter * 32;  // (masked path only)
+                if (TF32)  // 32-bit weights, in place over the S values
+                    weight_chunk<MODE, kTwoExp, kSpecial, false, 32>(v, v, cc, k_scale, row_c, j0, row, b_end);
+                else
+                    weight_chunk<MODE, kTwoExp, kSpecial>(v, packed, cc, k_scale, row_c, j0, row, b_end);
 #ifdef NTXENT_DROP_TILE
                 // Fault injection for the parity tests' own test (tools/drop_tile_proof.py): a build
                 // with this define loses the weights of ONE tile; the full-size comparison must notice.
-                if (u.rt == 100 && jt == 37) {
+                if (u.rt == 100 && jt0 + it == 37) {
 #pragma unroll
                     for (int e = 0; e < 16; ++e) packed[e] = 0u;
                 }
 #endif
                 NTX_TRACE(trole, it, 3);
                 if (SEP) {
+                    // one W block: the second MMA of the previous tile, issued while this tile's
+                    // weights were being computed, must have read it
+                    if (B::kPBufs == 1) mbar_wait(&p_free[0], p_par);
                     tc_fence_after();
                     NTX_TRACE(trole, it, 4);
                     tmem_st16(lane_addr + B::kPCol + pb * 64 + quarter * 16, packed);
@@ -917,8 +927,43 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_full[pb]);
                 NTX_TRACE(trole, it, 5);
-                if (MODE != kRow && ((it + 1) % B::kCcTiles == 0 || it + 1 == n_tiles)) {
-                    if (lane == 0) mbar_arrive(&cc_empty[cb & 1]);  // (after the __syncwarp above)
+                ++it;
+                ++g;
+                cc += kTile;
+                if (PAR) half ^= 1u;
+            };
+            using Even = std::integral_constant<int, 0>;
+            using Odd = std::integral_constant<int, 1>;
+            // masked tiles, as positions in this unit's walk
+            const int sp_lo = jt_diag_lo - jt0, sp_hi = jt_diag_hi - jt0, sp_rg = jt_ragged - jt0;
+            while (it < n_tiles) {
+                // one block of column constants (staged by the constants warp)
+                const int blk_end = min(n_tiles, it + B::kCcTiles);
+                if (MODE != kRow) mbar_wait(&cc_full[cb & 1], (cb >> 1) & 1);
+                cc = colc + (cb & 1) * B::kCcTiles * kTile + quarter * 32;
+                while (it < blk_end) {
+                    int ns = blk_end;  // the next masked tile of the block
+                    if (it <= sp_hi) ns = min(ns, max(it, sp_lo));
+                    if (sp_rg >= it) ns = min(ns, sp_rg);
+                    int n = ns - it;
+                    if (n > 0 && (g & 1)) {
+                        tile(Odd{}, std::false_type{});
+                        --n;
+                    }
+                    for (; n >= 2; n -= 2) {
+                        tile(Even{}, std::false_type{});
+                        tile(Odd{}, std::false_type{});
+                    }
+                    if (n) tile(Even{}, std::false_type{});
+                    if (it < blk_end) {  // it == ns: a masked tile
+                        if (g & 1)
+                            tile(Odd{}, std::true_type{});
+                        else
+                            tile(Even{}, std::true_type{});
+                    }
+                }
+                if (MODE != kRow) {
+                    if (lane == 0) mbar_arrive(&cc_empty[cb & 1]);  // (after the last tile's __syncwarp)
                     ++cb;
                 }
             }

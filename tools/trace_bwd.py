@@ -22,13 +22,19 @@ torch.cuda.synchronize()
 capi.lib().ntxent_b200_debug_set_trace(None)
 t = trace.cpu().numpy().reshape(5, 64, 8)
 t0 = t[0, 0, 0]
-names = ["MMA", "W0 ", "W15"]
+names = ["MMA", "W0 ", "W8 "]
 ev = {0: ["S:start", "kfull", "sfree", "S:issued", "PV:start", "pfull", "PV:issued"],
       1: ["start", "sfull", "ld", "computed", "pfree", "arrived"], 2: ["start", "sfull", "ld", "computed", "pfree", "arrived"]}
 for it in list(range(0, 6)) + list(range(20, 26)):
     for r in range(3):
         vals = [(ev[r][e], int(t[r, it, e] - t0)) for e in range(len(ev[r])) if t[r, it, e]]
         print(f"tile {it:2d} {names[r]}: " + "  ".join(f"{n}={v}" for n, v in vals))
+for r in (1, 2):  # mean phase lengths of the weight warps over tiles 10..40
+    d = t[r, 10:41].astype(np.int64)
+    ph = [("wait s_full", d[:, 1] - d[:, 0]), ("tmem ld + s_free", d[:, 2] - d[:, 1]), ("weights", d[:, 3] - d[:, 2]),
+          ("fence", d[:, 4] - d[:, 3]), ("st + p_full", d[:, 5] - d[:, 4]), ("loop back", d[1:, 0] - d[:-1, 5])]
+    print(names[r], "phases:", "  ".join(f"{n} {v.mean():.0f}" for n, v in ph))
+print("W8 - W0 at 'sfull' (tiles 10..40):", (t[2, 10:41, 1] - t[1, 10:41, 1]).tolist())
 per_tile = (t[1, 40, 5] - t[1, 10, 5]) / 30
 print("steady-state clk per tile (W0 arrivals, tiles 10..40):", per_tile)
 
