@@ -197,6 +197,12 @@ inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, 
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 #ifdef __CUDACC__
+// Row i's positive in the stacked-views layout, (i + M/2) mod M, without the 64-bit division
+// (a hundred instructions per call in kernels that are a few hundred long).
+__device__ __forceinline__ int64_t pair_row(int64_t i, int64_t M) {
+    const int64_t h = M / 2, j = i + h;
+    return j >= M ? j - M : j;
+}
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif

@@ -158,7 +158,7 @@ fwd_finalize_fused_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row
             const int64_t r = rb + warp * 8 + h * 4 + q;
             if (r < row_count) {
                 const int64_t row = row_begin + r;
-                const int64_t pi = pos_index ? (int64_t)pos_index[row] : (row + M / 2) % M;
+                const int64_t pi = pos_index ? (int64_t)pos_index[row] : pair_row(row, M);
                 const T* ui = U + row * D;
                 const T* up = U + pi * D;
                 for (int k = lane * 4; k < D; k += 128) {
@@ -294,16 +294,32 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
         *p.loss_out = acc * p.loss_scale;
     }
     const int D = p.D;
-    float4 du[kRows][kChunks], zz[kRows][kChunks];
+    const bool jac = p.du_out == nullptr;
+    // The kRows rows of a warp lie in one 128-row tile (r0 is a multiple of kRows, kRows divides 128):
+    // one slot count per warp, worked out first so that the loads of the first two slots go out
+    // together with z and u_pos -- one round trip to L2/HBM for the common case instead of three.
+    int nsplit = p.nsplit;
+    if (p.sk_ctas > 0) {  // CTAs whose tile ranges touch this row tile (tc_kernels.cu, BwdUnit)
+        const int64_t first = (r0 / 128) * p.sk_col_tiles;
+        if (p.sk_total * p.sk_ctas < (int64_t)0x7fffffff) {  // the usual case: 32-bit divisions
+            const unsigned tot = (unsigned)p.sk_total, f32 = (unsigned)first, ctas = (unsigned)p.sk_ctas;
+            nsplit = (int)(((f32 + (unsigned)p.sk_col_tiles) * ctas - 1u) / tot - ((f32 + 1u) * ctas - 1u) / tot) + 1;
+        } else {
+            nsplit = (int)(((first + p.sk_col_tiles) * p.sk_ctas - 1) / p.sk_total -
+                           ((first + 1) * p.sk_ctas - 1) / p.sk_total) + 1;
+        }
+    }
+    float4 du[kRows][kChunks], zz[kRows][kChunks], t0[kRows][kChunks], t1[kRows][kChunks];
     int64_t pos[kRows];
     float pc[kRows], inv[kRows];
-    const bool jac = p.du_out == nullptr;
-    // loads first: z, 1/|z|, u_pos ...
+    auto slot = [&](int sp, int64_t r, int k) {
+        return *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
+    };
 #pragma unroll
     for (int q = 0; q < kRows; ++q) {
         const int64_t r = min(r0 + q, p.a_count - 1);  // rows past the end redo the last row, unstored
         const int64_t row = p.a_begin + r;
-        pos[q] = p.pos_index ? (int64_t)p.pos_index[row] : (row + p.M / 2) % p.M;
+        pos[q] = p.pos_index ? (int64_t)p.pos_index[row] : pair_row(row, p.M);
         pc[q] = p.pos_index ? 1.f : ((pos[q] >= p.pos_lo && pos[q] < p.pos_hi) ? p.pos_coeff : 0.f);
         inv[q] = jac ? p.inv_norm[r] : 0.f;
 #pragma unroll
@@ -311,7 +327,11 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
             const int k = c * 128 + lane * 4;
             zz[q][c] = make_float4(0.f, 0.f, 0.f, 0.f);
             du[q][c] = zz[q][c];
+            t0[q][c] = zz[q][c];
+            t1[q][c] = zz[q][c];
             if (k < D) {
+                if (nsplit > 0) t0[q][c] = slot(0, r, k);
+                if (nsplit > 1) t1[q][c] = slot(1, r, k);
                 if (jac) zz[q][c] = Elem<TZ>::ld4(z_rows + r * D + k);
                 if (pc[q] != 0.f) {
                     const float4 u = Elem<TOp>::ld4(U + pos[q] * D + k);
@@ -338,38 +358,43 @@ bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict
             }
         }
     }
-    // ... then the partials of each row tile, added in slot order (deterministic)
+    // the partials of the row tile, added in slot order (deterministic); slots past the second (small
+    // row blocks against many columns) a slot at a time, all rows' loads before the adds
 #pragma unroll
-    for (int q = 0; q < kRows; ++q) {
-        const int64_t r = min(r0 + q, p.a_count - 1);
-        int nsplit = p.nsplit;
-        if (p.sk_ctas > 0) {  // CTAs whose tile ranges touch this row tile (tc_kernels.cu, BwdUnit)
-            const int64_t first = (r / 128) * p.sk_col_tiles;
-            nsplit = (int)(((first + p.sk_col_tiles) * p.sk_ctas - 1) / p.sk_total -
-                           ((first + 1) * p.sk_ctas - 1) / p.sk_total) + 1;
+    for (int q = 0; q < kRows; ++q)
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            t0[q][c].x += t1[q][c].x; t0[q][c].y += t1[q][c].y;
+            t0[q][c].z += t1[q][c].z; t0[q][c].w += t1[q][c].w;
         }
-        float4 acc[kChunks];
+    for (int sp = 2; sp < nsplit; ++sp) {
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int sp = 0; sp < nsplit; ++sp) {
+        for (int q = 0; q < kRows; ++q) {
+            const int64_t r = min(r0 + q, p.a_count - 1);
 #pragma unroll
             for (int c = 0; c < kChunks; ++c) {
                 const int k = c * 128 + lane * 4;
-                if (k < D) {
-                    const float4 t =
-                        *reinterpret_cast<const float4*>(p.acc + ((int64_t)sp * p.a_count + r) * D + k);
-                    acc[c].x += t.x; acc[c].y += t.y; acc[c].z += t.z; acc[c].w += t.w;
-                }
+                t1[q][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (k < D) t1[q][c] = slot(sp, r, k);
             }
         }
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) {
-            du[q][c].x = (du[q][c].x + acc[c].x) * p.scale;
-            du[q][c].y = (du[q][c].y + acc[c].y) * p.scale;
-            du[q][c].z = (du[q][c].z + acc[c].z) * p.scale;
-            du[q][c].w = (du[q][c].w + acc[c].w) * p.scale;
-        }
+        for (int q = 0; q < kRows; ++q)
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                t0[q][c].x += t1[q][c].x; t0[q][c].y += t1[q][c].y;
+                t0[q][c].z += t1[q][c].z; t0[q][c].w += t1[q][c].w;
+            }
     }
+#pragma unroll
+    for (int q = 0; q < kRows; ++q)
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+            du[q][c].x = (du[q][c].x + t0[q][c].x) * p.scale;
+            du[q][c].y = (du[q][c].y + t0[q][c].y) * p.scale;
+            du[q][c].z = (du[q][c].z + t0[q][c].z) * p.scale;
+            du[q][c].w = (du[q][c].w + t0[q][c].w) * p.scale;
+        }
 #pragma unroll
     for (int q = 0; q < kRows; ++q) {
         const int64_t r = r0 + q;
@@ -471,7 +496,7 @@ pos_dot_kernel(const T* __restrict__ U, int64_t M, int D, int64_t row_begin, int
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const int64_t i = row_begin + min(r0 + q, row_count - 1);
-        const int64_t pi = pos_index ? (int64_t)pos_index[i] : (i + M / 2) % M;
+        const int64_t pi = pos_index ? (int64_t)pos_index[i] : pair_row(i, M);
         const T* ui = U + i * D;
         const T* up = U + pi * D;
         for (int k = lane * 4; k < D; k += 128) {

@@ -191,7 +191,7 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, float k_s
         // ragged end of the range, and the half tiles that hold the positives of this row tile
         // (columns (a0 + N + r) mod M: one run of 128 columns, or two when it wraps around M)
         const int hj_ragged = (int)(M / 64);
-        const int p0 = (int)((a0 + M / 2) % M);
+        const int p0 = (int)pair_row(a0, M);
         const int hj_pos_lo = p0 / 64, hj_pos_hi = (min(p0 + kTile, (int)M) - 1) / 64;
         const int hj_wrap_hi = p0 + kTile > (int)M ? (p0 + kTile - (int)M - 1) / 64 : -1;
         // column partials of tile (i, j): cpart[(j (j-1)/2 + i) * 512 + quad * 128 + column]

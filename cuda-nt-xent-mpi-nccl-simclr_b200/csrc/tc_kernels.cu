@@ -300,7 +300,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, int64_t M, int64_t row_b
                         lse2_merge(m, s, __ldcg(part_m + (int64_t)sp * row_count + r),
                                    __ldcg(part_s + (int64_t)sp * row_count + r));
                     // the positive logit: fp32 dot of the two operand rows (both in L2)
-                    const int64_t pi = tail.pos_index ? (int64_t)tail.pos_index[row] : (row + M / 2) % M;
+                    const int64_t pi = tail.pos_index ? (int64_t)tail.pos_index[row] : pair_row(row, M);
                     float dot = 0.f;
                     if (TF32) {
                         const float4* ua = reinterpret_cast<const float4*>(static_cast<const float*>(U_raw) + row * D);
