@@ -16,6 +16,17 @@
 #include "tc_kernels.cuh"
 
 namespace ntxent_b200 {
+// ntxent_b200_backward_rows_dz with a caller-owned ticket array for the in-kernel epilogue (capi.cu)
+int backward_rows_dz_tickets(const void* u_all, const float* lse_all, int64_t M, int64_t D, int64_t row_begin,
+                             int64_t row_count, float tau, int dtype, unsigned flags, void* workspace,
+                             size_t workspace_bytes, const void* z_rows, const float* inv_norm_rows,
+                             const float* grad_out, void* dz_out, const ntxent_peer_wait* lse_ready,
+                             const float* loss_parts, int loss_parts_count, float* loss_out, unsigned* tickets,
+                             cudaStream_t stream);
+}  // namespace ntxent_b200
+
+
+namespace ntxent_b200 {
 
 int device_sm_count() {
     int dev = 0, sms = 0;
@@ -146,8 +157,22 @@ Plans make_plans(int64_t M, int64_t D, int64_t row_count, bool op_bf16, unsigned
     return p;
 }
 
-// Tickets of the in-kernel forward finalize: one for the loss, one per 128-row tile.
-inline size_t ticket_words(int64_t row_count) { return 1 + (size_t)((row_count + 127) / 128); }
+// Tickets: [0] the loss (fused forward finalize), [1, 1+T) the in-kernel forward finalize, one per
+// 128-row tile, [1+T, 1+2T) the in-kernel backward epilogue (bwd_tickets).
+inline size_t ticket_words(int64_t row_count) { return 1 + 2 * (size_t)((row_count + 127) / 128); }
+inline unsigned* bwd_tickets(unsigned* counter, int64_t row_count) {
+    return counter + 1 + (size_t)((row_count + 127) / 128);
+}
+// The backward epilogue runs inside the tile kernel when that kernel has the code for it (bf16
+// operands, D <= 128), nothing but dz is asked for, and a row tile is shared by at most two CTAs:
+// then the epilogues are spread over the kernel's run (C4 on one GPU: -7 us of 645).  Row blocks
+// that many CTAs share (small shards: 5-6 partials per row tile) finish all at once at the end of
+// the kernel, where the separate, fully parallel epilogue kernel is the faster one (4096 rows:
+// 29.5 against 32.8 us).  NTXENT_NO_BWD_TAIL=1 keeps the separate kernel everywhere.
+inline bool bwd_tail_enabled(const Plans& p, int64_t D, bool op_bf16) {
+    static const bool env_off = [] { const char* v = getenv("NTXENT_NO_BWD_TAIL"); return v && v[0] == '1'; }();
+    return !env_off && p.tc && tc_bwd_tail_supported(D, op_bf16) && p.bwd_rows.sk_ctas > 0 && p.bwd_rows.nsplit <= 2;
+}
 
 struct RowsWs {
     float* pos_t;  // positive logits (base-2 units): captured by the upper-triangle forward, or dot products
@@ -373,11 +398,11 @@ bool to_peer_wait(const ntxent_peer_wait* in, PeerWait* out) {
 int run_bwd_tiles(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                   int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count, float tau,
                   int mode, const Plans& p, const SplitPlan& plan, float* acc, float* ut,
-                  cudaStream_t st, const PeerWait& lse_ready = PeerWait{}) {
+                  cudaStream_t st, const PeerWait& lse_ready = PeerWait{}, const BwdTail* tail = nullptr) {
     g_timer.start(1, st);
     if (p.tc)
         NTX_TRY(tc_launch_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, p.cross ? M / 2 : b_count,
-                              tau, mode, p.flags, plan, acc, ut, lse_ready, st, p.cross));
+                              tau, mode, p.flags, plan, acc, ut, lse_ready, st, p.cross, tail));
     else
         NTX_TRY(launch_simt_bwd(u_all, op_bf16, lse_all, M, D, a_begin, a_count, b_begin, b_count,
                                 tau, mode, plan, acc, lse_ready, st, p.cross ? M / 2 : 0));
@@ -428,6 +453,14 @@ int run_backward_device(const void* z, bool z_bf16, const DeviceWs& w, bool op_b
                         void* dz_out, float* pos_prob_out, cudaStream_t st,
                         float* tau_grad_rows_out = nullptr, const int* pos_index = nullptr,
                         const int* inv_ptr = nullptr, const int* inv_idx = nullptr) {
+    if (bwd_tail_enabled(p, D, op_bf16) && !pos_prob_out && !tau_grad_rows_out && !pos_index) {
+        BwdTail t{};
+        t.tickets = bwd_tickets(w.rows.counter, M);  // (zeroed by this call's normalise launch)
+        t.z_rows = z; t.z_bf16 = z_bf16; t.inv_norm = w.inv_norm; t.grad_out = grad_out; t.dz_out = dz_out;
+        t.pos_coeff = 2.f; t.scale = 1.0f / (tau * (float)M);
+        return run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows, w.rows.acc_rows,
+                             w.rows.ut, st, PeerWait{}, &t);
+    }
     int rc = run_bwd_tiles(w.U, op_bf16, lse, M, D, 0, M, 0, M, tau, kSym, p, p.bwd_rows,
                            w.rows.acc_rows, w.rows.ut, st);
     if (rc != NTXENT_OK) return rc;
@@ -635,6 +668,22 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
                                  void* dz_out, const ntxent_peer_wait* lse_ready,
                                  const float* loss_parts, int loss_parts_count, float* loss_out,
                                  ntxent_stream_t stream) {
+    return ntxent_b200::backward_rows_dz_tickets(u_all, lse_all, M, D, row_begin, row_count, tau, dtype, flags,
+                                                 workspace, workspace_bytes, z_rows, inv_norm_rows, grad_out, dz_out,
+                                                 lse_ready, loss_parts, loss_parts_count, loss_out, nullptr, stream);
+}
+
+// The same with a ticket array for the in-kernel epilogue (one zeroed word per 128-row tile that
+// stays with the caller between calls: the communicator has one; the public entry point, whose
+// workspace may hold anything, passes none and gets the epilogue kernel).
+extern "C++" {
+int ntxent_b200::backward_rows_dz_tickets(const void* u_all, const float* lse_all, int64_t M, int64_t D,
+                                          int64_t row_begin, int64_t row_count, float tau, int dtype,
+                                          unsigned flags, void* workspace, size_t workspace_bytes,
+                                          const void* z_rows, const float* inv_norm_rows, const float* grad_out,
+                                          void* dz_out, const ntxent_peer_wait* lse_ready,
+                                          const float* loss_parts, int loss_parts_count, float* loss_out,
+                                          unsigned* tickets, cudaStream_t stream) {
     NTX_RANGE("ntxent_b200_backward_rows_dz");
     PeerWait wait{};
     if (!u_all || !lse_all || !workspace || !z_rows || !inv_norm_rows || !dz_out ||
@@ -652,6 +701,19 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
     const RowsWs w = carve_rows((char*)workspace, M, D, row_count, p, true);
     if (workspace_bytes < w.bytes) return NTXENT_ERR_WORKSPACE_TOO_SMALL;
     if (check_device() != NTXENT_OK) return NTXENT_ERR_UNSUPPORTED_DEVICE;
+    if (loss_out && (!loss_parts || loss_parts_count < 1 || loss_parts_count > kMaxPeers))
+        return NTXENT_ERR_INVALID_ARGUMENT;
+    if (tickets && bwd_tail_enabled(p, D, opb)) {
+        BwdTail t{};
+        t.tickets = tickets;
+        t.z_rows = z_rows; t.z_bf16 = (dtype == NTXENT_BF16); t.inv_norm = inv_norm_rows; t.grad_out = grad_out;
+        t.dz_out = dz_out; t.pos_coeff = 2.f; t.scale = 1.0f / (tau * (float)M);
+        if (loss_out) {
+            t.loss_parts = loss_parts; t.loss_n = loss_parts_count; t.loss_scale = 1.0f / (float)M; t.loss_out = loss_out;
+        }
+        return run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau, kSym, p, p.bwd_rows,
+                             w.acc_rows, w.ut, stream, wait, &t);
+    }
     rc = run_bwd_tiles(u_all, opb, lse_all, M, D, row_begin, row_count, 0, M, tau, kSym, p, p.bwd_rows,
                        w.acc_rows, w.ut, stream, wait);
     if (rc != NTXENT_OK) return rc;
@@ -665,12 +727,12 @@ int ntxent_b200_backward_rows_dz(const void* u_all, const float* lse_all, int64_
     e.du_out = nullptr; e.z_rows = z_rows; e.z_bf16 = (dtype == NTXENT_BF16); e.inv_norm = inv_norm_rows;
     e.grad_out = grad_out; e.dz_out = dz_out;
     if (loss_out) {
-        if (!loss_parts || loss_parts_count < 1 || loss_parts_count > kMaxPeers) return NTXENT_ERR_INVALID_ARGUMENT;
         e.loss_parts = loss_parts; e.loss_n = loss_parts_count; e.loss_scale = 1.0f / (float)M; e.loss_out = loss_out;
     }
     NTX_TRY(launch_bwd_epilogue(e, stream));
     return NTXENT_OK;
 }
+}  // extern "C++"
 
 int ntxent_b200_forward(const void* z, int64_t M, int64_t D, float tau, int dtype, unsigned flags,
                         void* workspace, size_t workspace_bytes, float* loss_out, float* lse_out,

@@ -28,6 +28,17 @@
 #include "common.cuh"
 
 namespace ntxent_b200 {
+// ntxent_b200_backward_rows_dz with a caller-owned ticket array for the in-kernel epilogue (capi.cu)
+int backward_rows_dz_tickets(const void* u_all, const float* lse_all, int64_t M, int64_t D, int64_t row_begin,
+                             int64_t row_count, float tau, int dtype, unsigned flags, void* workspace,
+                             size_t workspace_bytes, const void* z_rows, const float* inv_norm_rows,
+                             const float* grad_out, void* dz_out, const ntxent_peer_wait* lse_ready,
+                             const float* loss_parts, int loss_parts_count, float* loss_out, unsigned* tickets,
+                             cudaStream_t stream);
+}  // namespace ntxent_b200
+
+
+namespace ntxent_b200 {
 namespace {
 
 // ------------------------------------------------------------------- NCCL, late-bound ---
@@ -211,8 +222,9 @@ int alloc_comm(ntxent_comm* c, int rank, int nranks, int64_t M, int64_t D, int d
     c->ws_bytes = ntxent_b200_rows_workspace_bytes(M, D, c->rows, dtype, flags);
     NTX_CUDA(cudaMalloc(&c->ws, c->ws_bytes));
     NTX_CUDA(cudaMalloc((void**)&c->inv_norm, al(sizeof(float) * c->rows)));
-    // tickets: [0] the loss, [1 .. row tiles] the forward's row tiles, [last] the normalise kernel's signal
-    const size_t tick_bytes = al(sizeof(unsigned) * (2 + (size_t)((c->rows + 127) / 128)));
+    // tickets: [0] the loss, [1 .. T] the forward's row tiles, [1 + T] the normalise kernel's signal,
+    // [2 + T .. 2 + 2T) the backward's row tiles (in-kernel epilogue); every user leaves its words zero
+    const size_t tick_bytes = al(sizeof(unsigned) * (2 + 2 * (size_t)((c->rows + 127) / 128)));
     NTX_CUDA(cudaMalloc((void**)&c->tickets, tick_bytes));
     NTX_CUDA(cudaMemset(c->tickets, 0, tick_bytes));
     NTX_CUDA(cudaMalloc((void**)&c->loss_part, kAl));
@@ -440,9 +452,10 @@ int step_push(ntxent_comm* c, const void* z, const float* g, float tau, float* l
                                          multi ? &v.wait_u : nullptr, multi ? &v.sig_lse : nullptr, st));
     // (the backward tile kernel waits for every rank's l, hence for every partial loss: its
     // epilogue sums them)
-    NTX_RC(ntxent_b200_backward_rows_dz(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
-                                        c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out,
-                                        multi ? &v.wait_lse : nullptr, v.loss_parts, c->nranks, loss_out, st));
+    NTX_RC(backward_rows_dz_tickets(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
+                                    c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out,
+                                    multi ? &v.wait_lse : nullptr, v.loss_parts, c->nranks, loss_out,
+                                    c->tickets + 2 + (c->rows + 127) / 128, st));
     return NTXENT_OK;
 }
 
@@ -469,9 +482,9 @@ int step_nccl(ntxent_comm* c, const void* z, const float* g, float tau, int bwd_
                            (const float*)(multi ? c->loss_part + 1 : c->loss_part), 1, 1.0f / (float)c->M, loss_out));
     if (bwd_mode == NTXENT_BWD_SYMMETRIC) {
         if (multi) NTX_NCCL(n.AllGather(lse_mine, v.lse_all, (size_t)c->rows, ncclFloat32, c->nccl_comm, st));
-        NTX_RC(ntxent_b200_backward_rows_dz(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
-                                            c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out, nullptr,
-                                            nullptr, 0, nullptr, st));
+        NTX_RC(backward_rows_dz_tickets(v.u_all, v.lse_all, c->M, c->D, c->row_begin, c->rows, tau, c->dtype,
+                                        c->flags, c->ws, c->ws_bytes, z, c->inv_norm, g, dz_out, nullptr,
+                                        nullptr, 0, nullptr, c->tickets + 2 + (c->rows + 127) / 128, st));
     } else {
         // contract form: column term of every global row first, its reduce-scatter on the second
         // stream while the row term is computed on the first

@@ -279,8 +279,16 @@ struct BwdEpiDev {
 // (partials, u_pos, z) before the first use: kRows * kChunks 16-byte requests in flight per lane
 // and per operand.  (One row per warp, as this kernel used to work, left it latency-bound at
 // 19 % of the HBM peak.)
+// Rows per warp at D <= 128 and the resident CTAs asked of the compiler (A/B build switches).
+// Measured at 32768 x 128 (run Z): 4 rows / 2 CTAs (128 registers) 23.4 us, 2 rows / 4 CTAs 17.6 us.
+#ifndef NTX_EPI_ROWS
+#define NTX_EPI_ROWS 2
+#endif
+#ifndef NTX_EPI_MINB
+#define NTX_EPI_MINB 4
+#endif
 template <typename TOp, typename TZ, int kChunks, int kRows>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, kChunks == 1 ? NTX_EPI_MINB : 1)
 bwd_epilogue_kernel(BwdEpiDev p, const TOp* __restrict__ U, const TZ* __restrict__ z_rows,
                     TZ* __restrict__ dz_out) {
     pdl_trigger();
@@ -454,7 +462,7 @@ static cudaError_t launch_bwd_epilogue_t(const BwdEpiDev& p, const BwdEpilogueAr
 #define NTX_EPI(C, R)                                                                                   \
     launch_kernel(bwd_epilogue_kernel<TOp, TZ, C, R>, dim3((unsigned)((a.a_count + 8 * R - 1) / (8 * R))), \
                   block, 0, stream, p, (const TOp*)a.u_all, (const TZ*)a.z_rows, (TZ*)a.dz_out)
-    if (chunks <= 1) return NTX_EPI(1, 4);
+    if (chunks <= 1) return NTX_EPI(1, NTX_EPI_ROWS);
     if (chunks <= 2) return NTX_EPI(2, 2);
     if (chunks <= 4) return NTX_EPI(4, 1);
     return NTX_EPI(8, 1);

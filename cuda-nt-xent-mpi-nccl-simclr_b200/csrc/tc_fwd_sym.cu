@@ -394,25 +394,33 @@ fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_
     __shared__ double red[kSymFinThreads];
     pdl_trigger();
     pdl_wait();
-    const int j = blockIdx.x;  // row tile == column tile of these rows
+    // row tile == column tile of these rows; the tiles with the most partials (large j) go first,
+    // and sixteen loads are in flight per thread: the kernel was bound by the latency chain of its
+    // longest block (16.3 us at C4 for 67 MB)
+    const int j = (int)gridDim.x - 1 - (int)blockIdx.x;
     const int c = threadIdx.x & (kTile - 1), g = threadIdx.x >> 7;
     const int64_t r = (int64_t)j * kTile + c;
     const float* cp = cpart + (int64_t)j * (j - 1) / 2 * 512 + c;
-    float s2[2] = {0.f, 0.f};
+    float s4[4] = {0.f, 0.f, 0.f, 0.f};
     int i = g;
-    for (; i + 4 < j; i += 8) {
-        const float* q0 = cp + (int64_t)i * 512;
-        const float* q1 = q0 + 4 * 512;
-        const float a0 = q0[0], a1 = q0[128], a2 = q0[256], a3 = q0[384];
-        const float b0 = q1[0], b1 = q1[128], b2 = q1[256], b3 = q1[384];
-        s2[0] += (a0 + a1) + (a2 + a3);
-        s2[1] += (b0 + b1) + (b2 + b3);
+    for (; i + 12 < j; i += 16) {
+        float v[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float* q = cp + (int64_t)(i + 4 * u) * 512;
+            v[u][0] = q[0]; v[u][1] = q[128]; v[u][2] = q[256]; v[u][3] = q[384];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s4[u] += (v[u][0] + v[u][1]) + (v[u][2] + v[u][3]);
     }
-    if (i < j) {
-        const float* q0 = cp + (int64_t)i * 512;
-        s2[0] += (q0[0] + q0[128]) + (q0[256] + q0[384]);
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {  // up to three tile pairs left
+        if (i + 4 * u < j) {
+            const float* q = cp + (int64_t)(i + 4 * u) * 512;
+            s4[u] += (q[0] + q[128]) + (q[256] + q[384]);
+        }
     }
-    float s = s2[0] + s2[1];
+    float s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
     if (g > 0) part[g - 1][c] = s;
     __syncthreads();
     float contrib = 0.f;
@@ -430,7 +438,7 @@ fwd_sym_finalize_kernel(int64_t M, int T, int L, const float* __restrict__ part_
     }
     __syncthreads();
     if (threadIdx.x == 0)
-        block_partials[blockIdx.x] = (warp_contrib[0] + warp_contrib[1]) + (warp_contrib[2] + warp_contrib[3]);
+        block_partials[j] = (warp_contrib[0] + warp_contrib[1]) + (warp_contrib[2] + warp_contrib[3]);
     if (!counter) return;  // (the loss is then summed by a kernel of its own)
     // the loss: the last block to finish (ticket drawn after a fence) adds the per-tile partials in
     // a fixed order -- one launch less on the critical path, still run-to-run deterministic

@@ -556,7 +556,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
               const float* lse, int64_t M, int64_t a_begin, int64_t a_count,
               int64_t b_begin, int64_t b_count, float k_scale, int col_tiles, int64_t total_tiles,
               int cross_half, float* __restrict__ acc_out, unsigned long long* __restrict__ trace,
-              PeerWait lse_ready) {
+              PeerWait lse_ready, BwdTail tail) {
     using C = Cfg<D, TF32>;
     using B = BwdCfg<D, TF32>;
     constexpr int NS = B::kStages;
@@ -582,6 +582,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
     uint64_t* cc_full = acc_free + 1;  // [2] a block of column constants is staged
     uint64_t* cc_empty = cc_full + 2;  // [2] ... and all sixteen weight warps are done with it
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cc_empty + 2);
+    volatile uint32_t* tail_flag = tmem_slot + 1;  // in-kernel epilogue: "this CTA took the last ticket"
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     pdl_trigger();
@@ -778,6 +779,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                     if (lane == 0) mbar_arrive(&cc_full[cb & 1]);
                 }
             }
+            // in-kernel epilogue, multi-GPU form: the loss partials travel with l, so once every
+            // rank's flag has been seen CTA 0 adds them in rank order
+            if (tail.loss_out && blockIdx.x == 0) {
+                peer_wait_rows(lse_ready, 0, M, want, ready_mask);
+                if (lane == 0) {
+                    float acc = 0.f;
+                    for (int i = 0; i < tail.loss_n; ++i) acc += ld_f1_coherent(tail.loss_parts + i);
+                    *tail.loss_out = acc * tail.loss_scale;
+                }
+            }
         }
     } else {
         const int quad = warp & 3;
@@ -831,6 +842,104 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(q_full);
+        };
+
+        // The epilogue of a row tile, by the CTA whose unit completes it (BwdTail, tc_kernels.cuh).
+        // Called by all sixteen weight warps after the unit's partial has been stored: partials in
+        // slot order, the positive-pair term, the Jacobian of the normalisation, dz -- the arithmetic
+        // of bwd_epilogue_kernel (epilogue_kernels.cu), row for row.
+        auto tail_unit = [&](const BwdUnit& uu) {
+            const int64_t first = (int64_t)uu.rt * col_tiles;
+            const int nslots = (int)(bwd_cta_of_tile(first + col_tiles - 1, total_tiles, ctas) -
+                                     bwd_cta_of_tile(first, total_tiles, ctas)) + 1;
+            if (nslots > 1) {
+                __threadfence();  // this unit's partial, before its ticket
+                named_bar_sync(2, B::kWeightThreads);
+                if (wt == 0) {
+                    const bool last = atomicAdd(&tail.tickets[uu.rt], 1u) == (unsigned)(nslots - 1);
+                    if (last) tail.tickets[uu.rt] = 0u;  // left zero for the next launch
+                    *tail_flag = last ? 1u : 0u;
+                }
+                named_bar_sync(2, B::kWeightThreads);
+                if (*tail_flag == 0u) return;
+                __threadfence();  // the other units' partials, after their tickets
+            }
+            // warp w takes rows [8w, 8w + 8) of the tile, four at a time; a lane holds four columns
+            // of each (coalesced 512-byte rows); every load of a batch goes out before the first use
+            const int k = lane * 4;
+            const float g = tail.grad_out ? *tail.grad_out : 1.0f;
+            const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+            for (int batch = 0; batch < 2; ++batch) {
+                const int64_t rb = (int64_t)uu.rt * kTile + warp * 8 + batch * 4;
+                if (rb >= a_count) break;
+                float4 t0[4], t1[4], up[4], zz[4];
+                float inv[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int64_t r = min(rb + q, a_count - 1);  // rows past the end redo the last row, unstored
+                    t0[q] = t1[q] = up[q] = zz[q] = zero4;
+                    inv[q] = tail.inv_norm[r];
+                    if (k < D) {
+                        const float* src = acc_out + r * D + k;
+                        t0[q] = __ldcg(reinterpret_cast<const float4*>(src));
+                        if (nslots > 1) t1[q] = __ldcg(reinterpret_cast<const float4*>(src + a_count * D));
+                        const uint2 ur = __ldg(reinterpret_cast<const uint2*>(
+                            static_cast<const __nv_bfloat16*>(U_raw) + pair_row(a_begin + r, M) * D + k));
+                        up[q] = make_float4(__uint_as_float(ur.x << 16), __uint_as_float(ur.x & 0xffff0000u),
+                                            __uint_as_float(ur.y << 16), __uint_as_float(ur.y & 0xffff0000u));
+                        if (tail.z_bf16) {
+                            const uint2 zr = __ldg(reinterpret_cast<const uint2*>(
+                                static_cast<const __nv_bfloat16*>(tail.z_rows) + r * D + k));
+                            zz[q] = make_float4(__uint_as_float(zr.x << 16), __uint_as_float(zr.x & 0xffff0000u),
+                                                __uint_as_float(zr.y << 16), __uint_as_float(zr.y & 0xffff0000u));
+                        } else {
+                            zz[q] = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(tail.z_rows) + r * D + k));
+                        }
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    t0[q].x += t1[q].x; t0[q].y += t1[q].y; t0[q].z += t1[q].z; t0[q].w += t1[q].w;
+                }
+                for (int sp = 2; sp < nslots; ++sp) {  // (small row blocks against many columns)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int64_t r = min(rb + q, a_count - 1);
+                        t1[q] = zero4;
+                        if (k < D) t1[q] = __ldcg(reinterpret_cast<const float4*>(acc_out + ((int64_t)sp * a_count + r) * D + k));
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        t0[q].x += t1[q].x; t0[q].y += t1[q].y; t0[q].z += t1[q].z; t0[q].w += t1[q].w;
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int64_t r = rb + q;
+                    float4 du;
+                    du.x = (-tail.pos_coeff * up[q].x + t0[q].x) * tail.scale;
+                    du.y = (-tail.pos_coeff * up[q].y + t0[q].y) * tail.scale;
+                    du.z = (-tail.pos_coeff * up[q].z + t0[q].z) * tail.scale;
+                    du.w = (-tail.pos_coeff * up[q].w + t0[q].w) * tail.scale;
+                    float4 uu4 = zz[q];
+                    uu4.x *= inv[q]; uu4.y *= inv[q]; uu4.z *= inv[q]; uu4.w *= inv[q];
+                    const float dot = warp_sum(du.x * uu4.x + du.y * uu4.y + du.z * uu4.z + du.w * uu4.w);
+                    const float gi = g * inv[q];
+                    if (r < a_count && k < D) {
+                        const float4 o = make_float4(gi * (du.x - dot * uu4.x), gi * (du.y - dot * uu4.y),
+                                                     gi * (du.z - dot * uu4.z), gi * (du.w - dot * uu4.w));
+                        if (tail.z_bf16) {
+                            uint2 pk;
+                            pk.x = pack_bf16(o.x, o.y);
+                            pk.y = pack_bf16(o.z, o.w);
+                            *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(tail.dz_out) + r * D + k) = pk;
+                        } else {
+                            *reinterpret_cast<float4*>(static_cast<float*>(tail.dz_out) + r * D + k) = o;
+                        }
+                    }
+                }
+            }
         };
 
         bool have = bwd_next_unit(t_next, t_end, col_tiles, total_tiles, ctas, u);
@@ -1002,6 +1111,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                 }
             }
             NTX_TRACE_U(un, 5, clock64());
+            if (!TF32 && D <= 128 && tail.tickets) tail_unit(u);
             u = nu;
             have = have_next;
             ++un;
@@ -1104,7 +1214,7 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, const SplitPlan& plan, int col_tiles, int cross_half, float* acc,
-                         const PeerWait& lse_ready, cudaStream_t stream) {
+                         const PeerWait& lse_ready, const BwdTail& tail, cudaStream_t stream) {
     using B = BwdCfg<D, TF32>;
     const int smem = max(B::kSmem, 120 * 1024);
     auto kern = tc_bwd_kernel<D, TF32, MODE, kTwoExp>;
@@ -1115,7 +1225,7 @@ cudaError_t launch_bwd_t(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
     if (plan.sk_ctas < 1 || plan.sk_ctas > total_tiles) return cudaErrorInvalidValue;
     return launch_kernel(kern, dim3((unsigned)plan.sk_ctas), dim3(B::kThreads), smem, stream, tmap, tmap_t,
                          u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, col_tiles, total_tiles,
-                         cross_half, acc, g_trace, lse_ready);
+                         cross_half, acc, g_trace, lse_ready, tail);
 }
 
 template <int D, bool TF32>
@@ -1123,10 +1233,11 @@ cudaError_t launch_bwd_d(const CUtensorMap& tmap, const CUtensorMap& tmap_t, con
                          const float* lse, int64_t M,
                          int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                          float k_scale, int mode, bool two_exp, const SplitPlan& plan, int col_tiles,
-                         int cross_half, float* acc, const PeerWait& lse_ready, cudaStream_t stream) {
+                         int cross_half, float* acc, const PeerWait& lse_ready, const BwdTail& tail,
+                         cudaStream_t stream) {
 #define NTX_BWD(MODE, TWO)                                                                               \
     launch_bwd_t<D, TF32, MODE, TWO>(tmap, tmap_t, u_all, lse, M, a_begin, a_count, b_begin, b_count, k_scale, \
-                                     plan, col_tiles, cross_half, acc, lse_ready, stream)
+                                     plan, col_tiles, cross_half, acc, lse_ready, tail, stream)
     if (mode == kRow) return NTX_BWD(kRow, false);
     if (mode == kCol) return NTX_BWD(kCol, false);
     return two_exp ? NTX_BWD(kSym, true) : NTX_BWD(kSym, false);
@@ -1190,6 +1301,8 @@ int64_t tc_ut_cols(int64_t M) { return (M + 3) / 4 * 4; }
 size_t tc_bwd_scratch_bytes(int64_t M, int64_t D, bool op_bf16) {
     return op_bf16 ? 0 : (size_t)tc_ut_cols(M) * D * sizeof(float);
 }
+
+bool tc_bwd_tail_supported(int64_t D, bool op_bf16) { return op_bf16 && (D == 64 || D == 128); }
 
 bool tc_supported(int64_t M, int64_t D, bool op_bf16) {
     if (op_bf16) return D == 64 || D == 128 || D == 192 || D == 256;
@@ -1266,7 +1379,13 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
-                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream, bool cross_view) {
+                          float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream, bool cross_view,
+                          const BwdTail* tail_in) {
+    BwdTail tail{};
+    if (tail_in) {
+        if (!tc_bwd_tail_supported(D, op_bf16) || mode != kSym || !tail_in->tickets) return cudaErrorInvalidValue;
+        tail = *tail_in;
+    }
     // cross-view form: the caller passes b_begin = 0, b_count = M/2 (a multiple of 128) and mode kSym
     if (cross_view && ((M / 2) % kTile != 0 || b_begin != 0 || b_count != M / 2 || mode != kSym || lse_ready.flags))
         return cudaErrorInvalidValue;
@@ -1290,7 +1409,7 @@ cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all,
     const int col_tiles = (int)((b_count + kTile - 1) / kTile);
 #define NTX_BWD_D(DD, TF)                                                                                   \
     launch_bwd_d<DD, TF>(tmap, tmap_t, u_all, lse_all, M, a_begin, a_count, b_begin, b_count, k_scale, mode, \
-                         two_exp, plan, col_tiles, cross_half, acc, lse_ready, stream)
+                         two_exp, plan, col_tiles, cross_half, acc, lse_ready, tail, stream)
     if (!op_bf16) {
         switch (D) {
             case 64: return NTX_BWD_D(64, true);

@@ -34,11 +34,33 @@ cudaError_t tc_launch_fwd(const void* u_all, bool op_bf16, int64_t M, int64_t D,
                           float* part_m, float* part_s, const PeerWait& u_ready,
                           cudaStream_t stream, bool cross_view = false, const FwdTail* tail = nullptr);
 
+// Backward epilogue inside the tile kernel (bf16 operands, D <= 128, symmetric form, default
+// positives): every unit leaves its partial and takes a ticket on its row tile; the CTA that
+// takes the last one adds the partials in slot order, subtracts the positive-pair term, applies
+// the normalisation Jacobian and stores dz -- the work of bwd_epilogue_kernel without its launch,
+// spread over the kernel's run instead of 3.5 latency-bound waves at its end.
+// tickets: one device word per row tile, zero before the launch; the kernel leaves them zero.
+struct BwdTail {
+    unsigned* tickets;
+    const void* z_rows;     // [a_count, D], bf16 or fp32
+    int z_bf16;
+    const float* inv_norm;  // [a_count]
+    const float* grad_out;  // device scalar or nullptr (= 1)
+    void* dz_out;           // [a_count, D] in z's type
+    float pos_coeff;        // 2 for the symmetric form
+    float scale;            // 1 / (tau M)
+    const float* loss_parts;  // optional: CTA 0 adds loss_n partials in order -> loss_out
+    int loss_n;
+    float loss_scale;
+    float* loss_out;
+};
+bool tc_bwd_tail_supported(int64_t D, bool op_bf16);
+
 cudaError_t tc_launch_bwd(const void* u_all, bool op_bf16, const float* lse_all, int64_t M, int64_t D,
                           int64_t a_begin, int64_t a_count, int64_t b_begin, int64_t b_count,
                           float tau, int mode, unsigned flags, const SplitPlan& plan, float* acc,
                           float* ut_scratch, const PeerWait& lse_ready, cudaStream_t stream,
-                          bool cross_view = false);
+                          bool cross_view = false, const BwdTail* tail = nullptr);
 
 // ---- forward over the upper triangle (tc_fwd_sym.cu): whole-batch calls on one device, bf16
 // operands, fixed-max regime (log2(e)/tau <= 50), M >= kSymMinRows.
