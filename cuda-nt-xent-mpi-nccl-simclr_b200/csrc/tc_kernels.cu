@@ -863,6 +863,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ 
                 named_bar_sync(2, B::kWeightThreads);
                 if (*tail_flag == 0u) return;
                 __threadfence();  // the other units' partials, after their tickets
+            } else {
+                // the only partial is this CTA's own, but it was stored by other threads than the
+                // ones that read it below (thread-per-row there, warp-per-rows here)
+                named_bar_sync(2, B::kWeightThreads);
             }
             // warp w takes rows [8w, 8w + 8) of the tile, four at a time; a lane holds four columns
             // of each (coalesced 512-byte rows); every load of a batch goes out before the first use

@@ -196,6 +196,30 @@ def test_config_c4_full_size(oracle):
     assert (pp > 0).all() and (pp < 1).all()
 
 
+@pytest.mark.parametrize("M,D,dtype,mp", [(32768, 128, torch.bfloat16, False), (19200, 128, torch.bfloat16, False),
+                                          (20482, 64, torch.bfloat16, False), (19202, 128, torch.float32, True)])
+def test_in_kernel_epilogue_equals_epilogue_kernel(M, D, dtype, mp):
+    """The fused call finishes dz inside the backward tile kernel when a row tile has at most two
+    partials (M >= 148 tiles of 128 rows: sizes the small cases never reach); backward() with
+    pos_prob asked for runs the epilogue kernel.  Same arithmetic row for row: bitwise equal, and
+    bitwise equal from run to run -- a missing barrier between the partial's store and the rows'
+    epilogue showed as a few wrong rows per run, different ones every time."""
+    tau = 0.1
+    z_t = dev(seeded_z(M, D, seed=31), dtype)
+    g = torch.tensor([0.75], device="cuda")
+    loss, lse = capi.forward(z_t, tau, mp)
+    dz_ref, _ = capi.backward(z_t, lse, g, tau, mp)  # want_pos_prob: the separate epilogue kernel
+    first = None
+    for _ in range(4):
+        l2, lse2, dz2 = capi.forward_backward(z_t, tau, g, mp)
+        torch.cuda.synchronize()
+        assert torch.equal(lse2, lse) and torch.equal(l2, loss)
+        bad = (dz2 != dz_ref).any(dim=1).nonzero().flatten()
+        assert bad.numel() == 0, f"{bad.numel()} rows differ, first {bad[:8].tolist()}"
+        first = dz2 if first is None else first
+        assert torch.equal(dz2, first)
+
+
 def test_config_c5_full_size(oracle):
     """configs[4] at full size on one GPU (2N=131072, D=256, bf16; the dense fp32 logits would be
     68.7 GB and are never formed by the library).
