@@ -163,14 +163,20 @@ inline size_t ticket_words(int64_t row_count) { return 1 + 2 * (size_t)((row_cou
 inline unsigned* bwd_tickets(unsigned* counter, int64_t row_count) {
     return counter + 1 + (size_t)((row_count + 127) / 128);
 }
-// The backward epilogue runs inside the tile kernel when that kernel has the code for it (bf16
-// operands, D <= 128), nothing but dz is asked for, and a row tile is shared by at most two CTAs:
-// then the epilogues are spread over the kernel's run (C4 on one GPU: -7 us of 645).  Row blocks
-// that many CTAs share (small shards: 5-6 partials per row tile) finish all at once at the end of
-// the kernel, where the separate, fully parallel epilogue kernel is the faster one (4096 rows:
-// 29.5 against 32.8 us).  NTXENT_NO_BWD_TAIL=1 keeps the separate kernel everywhere.
+// The backward epilogue CAN run inside the tile kernel (NTXENT_BWD_TAIL=1) when that kernel has
+// the code for it (bf16 operands, D <= 128), nothing but dz is asked for, and a row tile is shared
+// by at most two CTAs: then the epilogues are spread over the kernel's run.  Measured at C4 on one
+// GPU, interleaved on one box: step 0.6404 against 0.6476 ms (-1.1 %), tile kernel +10 us, side
+// kernels -17 us.  Off by default: the gain is inside the box-to-box spread (+-2 %), it exists only
+// for that shape class (row blocks that many CTAs share finish all at once at the end of the kernel,
+// where the separate, fully parallel epilogue kernel is the faster one: 4096 rows 29.5 against
+// 32.8 us), and it keeps a second copy of the epilogue arithmetic that must stay bit-identical
+// (tests/test_parity_gpu.py pins it).  Read per call so that a test can switch it.
 inline bool bwd_tail_enabled(const Plans& p, int64_t D, bool op_bf16) {
-    static const bool env_off = [] { const char* v = getenv("NTXENT_NO_BWD_TAIL"); return v && v[0] == '1'; }();
+    const char* v = getenv("NTXENT_BWD_TAIL");
+    return v && v[0] == '1' && p.tc && tc_bwd_tail_supported(D, op_bf16) && p.bwd_rows.sk_ctas > 0 &&
+           p.bwd_rows.nsplit <= 2;
+}();
     return !env_off && p.tc && tc_bwd_tail_supported(D, op_bf16) && p.bwd_rows.sk_ctas > 0 && p.bwd_rows.nsplit <= 2;
 }
 

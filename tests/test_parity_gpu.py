@@ -7,6 +7,7 @@ accumulation -- loss 2e-3 relative (dz is not given a bound there; 3e-2 in the s
 used and stated).  Every property the reference's own tests assert is checked as well.
 """
 import math
+import os
 
 import numpy as np
 import pytest
@@ -199,9 +200,9 @@ def test_config_c4_full_size(oracle):
 @pytest.mark.parametrize("M,D,dtype,mp", [(32768, 128, torch.bfloat16, False), (19200, 128, torch.bfloat16, False),
                                           (20482, 64, torch.bfloat16, False), (19202, 128, torch.float32, True)])
 def test_in_kernel_epilogue_equals_epilogue_kernel(M, D, dtype, mp):
-    """The fused call finishes dz inside the backward tile kernel when a row tile has at most two
-    partials (M >= 148 tiles of 128 rows: sizes the small cases never reach); backward() with
-    pos_prob asked for runs the epilogue kernel.  Same arithmetic row for row: bitwise equal, and
+    """With NTXENT_BWD_TAIL=1 the fused call finishes dz inside the backward tile kernel when a row
+    tile has at most two partials (M >= 148 tiles of 128 rows: sizes the small cases never reach);
+    backward() with pos_prob asked for runs the epilogue kernel.  Same arithmetic row for row: bitwise equal, and
     bitwise equal from run to run -- a missing barrier between the partial's store and the rows'
     epilogue showed as a few wrong rows per run, different ones every time."""
     tau = 0.1
@@ -210,14 +211,22 @@ def test_in_kernel_epilogue_equals_epilogue_kernel(M, D, dtype, mp):
     loss, lse = capi.forward(z_t, tau, mp)
     dz_ref, _ = capi.backward(z_t, lse, g, tau, mp)  # want_pos_prob: the separate epilogue kernel
     first = None
-    for _ in range(4):
-        l2, lse2, dz2 = capi.forward_backward(z_t, tau, g, mp)
-        torch.cuda.synchronize()
-        assert torch.equal(lse2, lse) and torch.equal(l2, loss)
-        bad = (dz2 != dz_ref).any(dim=1).nonzero().flatten()
-        assert bad.numel() == 0, f"{bad.numel()} rows differ, first {bad[:8].tolist()}"
-        first = dz2 if first is None else first
-        assert torch.equal(dz2, first)
+    old = os.environ.get("NTXENT_BWD_TAIL")
+    os.environ["NTXENT_BWD_TAIL"] = "1"  # (the library reads it on every call)
+    try:
+        for _ in range(4):
+            l2, lse2, dz2 = capi.forward_backward(z_t, tau, g, mp)
+            torch.cuda.synchronize()
+            assert torch.equal(lse2, lse) and torch.equal(l2, loss)
+            bad = (dz2 != dz_ref).any(dim=1).nonzero().flatten()
+            assert bad.numel() == 0, f"{bad.numel()} rows differ, first {bad[:8].tolist()}"
+            first = dz2 if first is None else first
+            assert torch.equal(dz2, first)
+    finally:
+        if old is None:
+            del os.environ["NTXENT_BWD_TAIL"]
+        else:
+            os.environ["NTXENT_BWD_TAIL"] = old
 
 
 def test_config_c5_full_size(oracle):

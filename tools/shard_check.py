@@ -41,11 +41,11 @@ for rep in range(a.repeat):  # run-to-run: the whole-batch call must repeat itse
 # the other epilogue form in a child process
 tmp = "/tmp/shard_check_other.pt"
 env = dict(os.environ)
-other = "tail" if env.get("NTXENT_NO_BWD_TAIL") == "1" else "no tail"
-if other == "tail":
-    env.pop("NTXENT_NO_BWD_TAIL")
+other = "no tail" if env.get("NTXENT_BWD_TAIL") == "1" else "tail"
+if other == "no tail":
+    env.pop("NTXENT_BWD_TAIL")
 else:
-    env["NTXENT_NO_BWD_TAIL"] = "1"
+    env["NTXENT_BWD_TAIL"] = "1"
 subprocess.run([sys.executable, __file__, "--M", str(a.M), "--D", str(a.D), "--tau", str(a.tau), "--dump", tmp],
                env=env, check=True)
 o = torch.load(tmp)
