@@ -176,8 +176,6 @@ inline bool bwd_tail_enabled(const Plans& p, int64_t D, bool op_bf16) {
     const char* v = getenv("NTXENT_BWD_TAIL");
     return v && v[0] == '1' && p.tc && tc_bwd_tail_supported(D, op_bf16) && p.bwd_rows.sk_ctas > 0 &&
            p.bwd_rows.nsplit <= 2;
-}();
-    return !env_off && p.tc && tc_bwd_tail_supported(D, op_bf16) && p.bwd_rows.sk_ctas > 0 && p.bwd_rows.nsplit <= 2;
 }
 
 struct RowsWs {
