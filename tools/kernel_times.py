@@ -3,6 +3,12 @@ CUPTI activity records torch.profiler collects: what `ncu` cannot show, since it
 launches and flushes the caches between them.
 
     python tools/kernel_times.py [--M 32768] [--D 128] [--tau 0.1] [--steps 20] [--dtype bf16]
+    NTXENT_NO_PDL=1 python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 \
+        tools/kernel_times.py --dist [--comm push|nccl]      # the row-partitioned step, rank 0 prints
+
+(With programmatic dependent launch a kernel is resident while it still waits for its predecessor,
+and that wait counts into its duration: NTXENT_NO_PDL=1 gives the kernels' own times.  Under --dist a
+kernel that waits for a peer's flag counts that wait as well: the table is a critical-path view.)
 """
 import argparse
 import collections
@@ -24,18 +30,46 @@ ap.add_argument("--tau", type=float, default=0.1)
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--dtype", default="bf16")
 ap.add_argument("--flags", type=int, default=0)
+ap.add_argument("--dist", action="store_true")
+ap.add_argument("--comm", default="push")
 a = ap.parse_args()
 dt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+rank, world, engine = 0, 1, None
+if a.dist:
+    import torch.distributed as dist
+    from ntxent_b200.distributed import RowPartitionedNTXent
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    engine = RowPartitionedNTXent(a.M, a.D, a.tau, dt, torch.device("cuda", torch.cuda.current_device()), comm=a.comm)
 z = torch.from_numpy(np.random.default_rng(2).standard_normal((a.M, a.D)).astype(np.float32)).cuda().to(dt)
-ws = capi.workspace(a.M, a.D, z, a.flags)
-out = (torch.empty(1, device="cuda"), torch.empty(a.M, device="cuda"), torch.empty_like(z))
+if engine is None:
+    ws = capi.workspace(a.M, a.D, z, a.flags)
+    out = (torch.empty(1, device="cuda"), torch.empty(a.M, device="cuda"), torch.empty_like(z))
+
+    def step():
+        capi.forward_backward(z, a.tau, None, False, a.flags, ws=ws, out=out)
+else:
+    shard = z[rank * (a.M // world):(rank + 1) * (a.M // world)].contiguous()
+
+    def step():
+        engine.forward_backward(shard)
 for _ in range(5):
-    capi.forward_backward(z, a.tau, None, False, a.flags, ws=ws, out=out)
+    step()
 torch.cuda.synchronize()
+if engine is not None:
+    dist.barrier()
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(a.steps):
-        capi.forward_backward(z, a.tau, None, False, a.flags, ws=ws, out=out)
+        step()
     torch.cuda.synchronize()
+if engine is not None:
+    dist.barrier()
+    engine.release()
+    dist.destroy_process_group()
+    if rank != 0:
+        sys.exit(0)
+    print(f"rank 0 of {world}, comm={a.comm}, {a.M // world} rows x {a.M} columns")
 ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 ev.sort(key=lambda e: e.time_range.start)
 by = collections.OrderedDict()
